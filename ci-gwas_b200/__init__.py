@@ -1,0 +1,16 @@
+"""cusk-b200: B200-native (sm_100a) CI-GWAS skeleton hot path.
+
+Host-side Python mirror of the reference's operator interface (``Skeleton``, ``hetcor_skeleton``,
+``cu_corr_pearson_npn`` ...) over the C ABI of ``libcusk_b200.so`` (``include/cusk_b200.h``).
+There is no CPU fallback: every compute call raises when the CUDA library or a device is missing.
+"""
+from .lib import (  # noqa: F401
+    CuskError,
+    Context,
+    Stats,
+    build_library,
+    hetcor_threshold,
+    library_path,
+    load_library,
+    threshold_array,
+)

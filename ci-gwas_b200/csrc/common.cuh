@@ -1,0 +1,96 @@
+// common.cuh -- shared host/device helpers of libcusk_b200 (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/cusk_b200.h"
+
+typedef unsigned long long u64;
+
+#define CUSK_SAT ((u64)1 << 62)  // saturation value of 64-bit binomials
+#define CUSK_KEY_NONE (~(u64)0)
+
+// ---- error plumbing ------------------------------------------------------------------------
+void cusk_set_error(const char *fmt, ...);
+
+#define CUSK_CUDA(call)                                                                         \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            cusk_set_error("%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return CUSK_E_CUDA;                                                                 \
+        }                                                                                       \
+    } while (0)
+
+// ---- context -------------------------------------------------------------------------------
+// A grow-only device arena: the skeleton engines and the correlation front end carve their
+// buffers from it so that repeated calls (one per LD block) never cudaMalloc in steady state.
+struct ArenaBlock {
+    char *base = nullptr;
+    size_t cap = 0;
+    size_t off = 0;
+};
+struct Arena {
+    std::vector<ArenaBlock> blocks;
+};
+
+struct cusk_ctx {
+    int device = 0;
+    int sm_count = 148;
+    int max_smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    Arena arena;  // engine scratch, rewound by every engine call
+    Arena io;     // device copies of host-buffer arguments, rewound by every host-buffer entry point
+    // pinned staging for small control blocks / statistics
+    void *h_pinned = nullptr;
+    size_t h_pinned_bytes = 0;
+    cudaEvent_t ev[2 * (CUSK_ML + 2) + 4];
+    bool ev_ready = false;
+};
+
+void arena_reset(Arena &a);                // rewind: all earlier takes become invalid
+void *arena_take(Arena &a, size_t bytes);  // 256-byte aligned; grows by whole blocks; nullptr + error on failure
+void arena_free(Arena &a);
+inline void arena_reset(cusk_ctx *ctx) { arena_reset(ctx->arena); }
+inline void *arena_take(cusk_ctx *ctx, size_t bytes) { return arena_take(ctx->arena, bytes); }
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ---- combinatorics (64-bit, saturating; the reference's BINOM / IthCombination are int32,
+//      src/cuPC-S.cu:6453-6506) --------------------------------------------------------------
+__host__ __device__ inline u64 binom64(int n, int k)
+{
+    if (k < 0 || k > n) return 0;
+    if (k > n - k) k = n - k;
+    u64 c = 1;
+    for (int i = 1; i <= k; i++) {
+        // c * (n - k + i) / i is always integral; widen the product
+        const unsigned __int128 t = (unsigned __int128)c * (unsigned)(n - k + i);
+        const unsigned __int128 q = t / (unsigned)i;
+        if (q >= (unsigned __int128)CUSK_SAT) return CUSK_SAT;
+        c = (u64)q;
+    }
+    return c;
+}
+
+// 0-based lexicographic rank -> strictly increasing positions pos[0..k) out of {0..N-1}.
+__host__ __device__ inline void unrank_comb(u64 rank, int N, int k, int *pos)
+{
+    int x = 0;
+    for (int i = 0; i < k; i++) {
+        for (;; x++) {
+            const u64 c = binom64(N - 1 - x, k - 1 - i);  // sets that start with x at slot i
+            if (rank < c) break;
+            rank -= c;
+        }
+        pos[i] = x;
+        x++;
+    }
+}

@@ -1,0 +1,18 @@
+// engine.h -- internal C++ entry points of the skeleton engines (device-resident inputs).
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+// Individual-level engine.  seps != nullptr: all separating-set records, sorted by (x, y).
+int skeleton_engine(cusk_ctx *ctx, const float *dC, int n, uint32_t *dbits, const float *Th, int maxlevel,
+                    int *l_out, float *d_pMax, std::vector<cusk_sepset> *seps, cusk_stats *stats);
+
+// Summary-statistic engine.  Candidate edges: dG_dense (int n*n, ==1 is a candidate), or the
+// bitmap itself (bits_are_input), or every pair when both are absent.  dN == nullptr: uniform
+// effective sample size n_uniform.
+int hetcor_engine(cusk_ctx *ctx, const float *dC, int n, uint32_t *dbits, const int *dG_dense, bool bits_are_input,
+                  const float *dN, float n_uniform, float th, int maxlevel, const int *d_time, int *l_out,
+                  cusk_stats *stats);
+
+void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, int *G);

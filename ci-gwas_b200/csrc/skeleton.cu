@@ -1,0 +1,331 @@
+// skeleton.cu -- host drivers of the two skeleton engines: the level loop of Skeleton()
+// (src/cuPC-S.cu:61-450) and hetcor_skeleton() (src/hetcor-cuPC-S.cu:75-341), re-designed so that
+// the whole call is one stream of asynchronous launches with a single mid-call synchronisation
+// (the directed edge count after level 0, which sizes the compacted adjacency).
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#include "skeleton.cuh"
+
+// launch wrappers (skeleton_kernels.cu, ci_level.cu)
+void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, float n_uniform, const int *G_in,
+                   int n, int rw, double th, uint32_t *bits, float *pMax);
+void launch_degree(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, const LevelCtl *prev);
+void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int *itemstart, u64 *chunk,
+                 LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
+                 int *work_counter);
+void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
+                    u64 *minkey, const LevelCtl *ctl);
+void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
+                    const int *rowptr, const int *adj, const u64 *minkey, float *pMax, cusk_sepset *seps,
+                    unsigned long long *sep_count, u64 sep_cap, const LevelCtl *ctl);
+void launch_pmax_final(cudaStream_t st, const uint32_t *bits, int n, int rw, float *pMax);
+void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, int *G);
+void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits);
+void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
+int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
+
+extern "C" size_t cusk_row_words(int n) { return (size_t)(n + 31) / 32; }
+
+namespace {
+
+struct EngineArgs {
+    bool het;
+    const float *dC;
+    int n;
+    uint32_t *dbits;       // in/out
+    const int *dG_in;      // het: dense candidate matrix on the device, or nullptr
+    bool bits_are_input;   // het: dbits already holds the candidate edges
+    bool all_ones;         // het: every pair is a candidate
+    const float *dN;       // het: nullptr -> uniform n_uniform
+    float n_uniform;
+    const float *Th;       // non-het: 15 thresholds (host)
+    float th_het;
+    int maxlevel;
+    const int *d_time;     // het
+    float *d_pMax;         // non-het, may be nullptr
+    bool want_seps;
+};
+
+struct EngineOut {
+    int last_level = 0;
+    cusk_sepset *d_seps = nullptr;
+    u64 sep_count = 0;
+};
+
+// Runs levels 0..maxlevel on device-resident inputs.  Scratch comes from ctx's arena (taken after
+// whatever the caller already took).
+int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *stats)
+{
+    const int n = a.n;
+    const int rw = (int)cusk_row_words(n);
+    cudaStream_t st = ctx->stream;
+    const int maxl = std::min(a.maxlevel, CUSK_ML);
+    if (n < 1 || a.maxlevel < 0) {
+        cusk_set_error("skeleton: invalid n=%d maxlevel=%d", n, a.maxlevel);
+        return CUSK_E_ARG;
+    }
+
+    int *d_deg = (int *)arena_take(ctx, sizeof(int) * (size_t)n);
+    int *d_rowptr = (int *)arena_take(ctx, sizeof(int) * ((size_t)n + 1));
+    int *d_itemstart = (int *)arena_take(ctx, sizeof(int) * ((size_t)n + 1));
+    u64 *d_chunk = (u64 *)arena_take(ctx, sizeof(u64) * (size_t)n);
+    LevelCtl *d_ctl = (LevelCtl *)arena_take(ctx, sizeof(LevelCtl) * (CUSK_ML + 2));
+    int *d_work = (int *)arena_take(ctx, sizeof(int) * (CUSK_ML + 2));
+    unsigned long long *d_sepcount = (unsigned long long *)arena_take(ctx, sizeof(unsigned long long));
+    int *d_minmax = (int *)arena_take(ctx, 2 * sizeof(int));
+    if (!d_deg || !d_rowptr || !d_itemstart || !d_chunk || !d_ctl || !d_work || !d_sepcount || !d_minmax)
+        return CUSK_E_CUDA;
+    CUSK_CUDA(cudaMemsetAsync(d_ctl, 0, sizeof(LevelCtl) * (CUSK_ML + 2), st));
+    CUSK_CUDA(cudaMemsetAsync(d_work, 0, sizeof(int) * (CUSK_ML + 2), st));
+    CUSK_CUDA(cudaMemsetAsync(d_sepcount, 0, sizeof(unsigned long long), st));
+
+    // het engine: uniform effective sample sizes take the constant-threshold fast path
+    const float *dN = a.dN;
+    float n_uniform = a.n_uniform;
+    if (a.het && dN) {
+        int init[2] = {2147483647, -2147483647 - 1};
+        CUSK_CUDA(cudaMemcpyAsync(d_minmax, init, sizeof(init), cudaMemcpyHostToDevice, st));
+        launch_ess_minmax(st, dN, n, d_minmax, d_minmax + 1, ctx->sm_count);
+        int mm[2];
+        CUSK_CUDA(cudaMemcpyAsync(mm, d_minmax, sizeof(mm), cudaMemcpyDeviceToHost, st));
+        CUSK_CUDA(cudaStreamSynchronize(st));
+        if (mm[0] == mm[1] && n > 1) {
+            memcpy(&n_uniform, &mm[0], sizeof(float));
+            dN = nullptr;
+        }
+    }
+
+    cudaEvent_t *ev = ctx->ev;
+    CUSK_CUDA(cudaEventRecord(ev[0], st));
+    // ---- level 0 -----------------------------------------------------------------------------
+    if (a.het && a.bits_are_input) {
+        // candidates given as a bitmap: expand to the level-0 kernel's input via a dense pass
+        // (only used by the device-resident API; the bitmap is both input and output)
+        int *dG_tmp = (int *)arena_take(ctx, sizeof(int) * (size_t)n * n);
+        if (!dG_tmp) return CUSK_E_CUDA;
+        launch_expand_bits(st, a.dbits, n, rw, dG_tmp);
+        launch_level0(st, true, a.dC, dN, n_uniform, dG_tmp, n, rw, (double)a.th_het, a.dbits, nullptr);
+    } else if (a.het) {
+        launch_level0(st, true, a.dC, dN, n_uniform, a.all_ones ? nullptr : a.dG_in, n, rw, (double)a.th_het,
+                      a.dbits, nullptr);
+    } else {
+        launch_level0(st, false, a.dC, nullptr, 0.f, nullptr, n, rw, (double)a.Th[0], a.dbits, a.d_pMax);
+    }
+    CUSK_CUDA(cudaGetLastError());
+
+    int *d_adj = nullptr;
+    u64 *d_minkey = nullptr;
+    cusk_sepset *d_seps = nullptr;
+    u64 sep_cap = 0;
+    const int grid = ctx->sm_count;
+    const int smem_bytes = ctx->max_smem_optin - 1024;  // leave room for static shared memory
+
+    for (int l = 1; l <= maxl; l++) {
+        CUSK_CUDA(cudaEventRecord(ev[l], st));
+        LevelCtl *ctl = d_ctl + l;
+        const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
+        launch_degree(st, a.dbits, n, rw, d_deg, prev);
+        launch_plan(st, d_deg, n, l, d_rowptr, d_itemstart, d_chunk, ctl, prev, a.het ? -1.0 : (double)a.Th[l],
+                    (double)a.th_het, n_uniform, d_work + l);
+        if (l == 1) {
+            // the only mid-call synchronisation: directed edge count after level 0
+            LevelCtl h;
+            CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
+            CUSK_CUDA(cudaStreamSynchronize(st));
+            const size_t nnz = (size_t)h.nnz;
+            d_adj = (int *)arena_take(ctx, sizeof(int) * std::max<size_t>(nnz, 1));
+            if (!d_adj) return CUSK_E_CUDA;
+            if (!a.het) {
+                d_minkey = (u64 *)arena_take(ctx, sizeof(u64) * std::max<size_t>(nnz, 1));
+                if (!d_minkey) return CUSK_E_CUDA;
+                if (a.want_seps) {
+                    sep_cap = nnz;
+                    d_seps = (cusk_sepset *)arena_take(ctx, sizeof(cusk_sepset) * std::max<size_t>(nnz, 1));
+                    if (!d_seps) return CUSK_E_CUDA;
+                }
+            }
+        }
+        launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl);
+        CiParams p;
+        p.C = a.dC;
+        p.N = a.het ? dN : nullptr;
+        p.time_index = a.het ? a.d_time : nullptr;
+        p.n = n;
+        p.l = l;
+        p.rw = rw;
+        p.bits = a.dbits;
+        p.deg = d_deg;
+        p.rowptr = d_rowptr;
+        p.adj = d_adj;
+        p.itemstart = d_itemstart;
+        p.chunk = d_chunk;
+        p.ctl = ctl;
+        p.work_counter = d_work + l;
+        p.minkey = d_minkey;
+        p.th_het = (double)a.th_het;
+        p.smem_bytes = smem_bytes;
+        int rc = launch_ci_level(st, a.het, p, grid);
+        if (rc) return rc;
+        if (!a.het)
+            launch_resolve(st, a.dC, n, rw, l, a.dbits, d_deg, d_rowptr, d_adj, d_minkey, a.d_pMax, d_seps,
+                           d_sepcount, sep_cap, ctl);
+        CUSK_CUDA(cudaGetLastError());
+    }
+    // final degrees (edge count) and pMax post-processing
+    launch_degree(st, a.dbits, n, rw, d_deg, nullptr);
+    launch_plan(st, d_deg, n, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1, nullptr, 1.0, 1.0,
+                n_uniform, d_work + CUSK_ML + 1);
+    if (!a.het && a.d_pMax) launch_pmax_final(st, a.dbits, n, rw, a.d_pMax);
+    CUSK_CUDA(cudaEventRecord(ev[maxl + 1], st));
+    CUSK_CUDA(cudaGetLastError());
+
+    // ---- read back the control blocks --------------------------------------------------------
+    LevelCtl *h_ctl = (LevelCtl *)ctx->h_pinned;
+    unsigned long long *h_sepcount = (unsigned long long *)(h_ctl + CUSK_ML + 2);
+    CUSK_CUDA(cudaMemcpyAsync(h_ctl, d_ctl, sizeof(LevelCtl) * (CUSK_ML + 2), cudaMemcpyDeviceToHost, st));
+    CUSK_CUDA(cudaMemcpyAsync(h_sepcount, d_sepcount, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CUSK_CUDA(cudaStreamSynchronize(st));
+
+    // last level as the reference reports it (src/cuPC-S.cu:99,154-159): the first level that
+    // finds max_degree - 1 < l stops the loop with l - 1; otherwise the loop counter runs out.
+    int last = maxl + 1;
+    int levels_run = 1;
+    int infeasible = 0;
+    for (int l = 1; l <= maxl; l++) {
+        if (h_ctl[l].infeasible) infeasible = std::max(infeasible, h_ctl[l].infeasible);
+        if (h_ctl[l].done) {
+            last = l - 1;
+            break;
+        }
+        levels_run++;
+    }
+    out->last_level = last;
+    out->d_seps = d_seps;
+    out->sep_count = std::min<u64>(*h_sepcount, sep_cap);
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        stats->tests_canonical[0] = stats->tests_executed[0] = (int64_t)n * (n - 1) / 2;
+        stats->edges_after[0] = (int64_t)(h_ctl[1].nnz / 2);
+        for (int l = 1; l <= maxl; l++) {
+            if (h_ctl[l].done) break;
+            stats->tests_canonical[l] = (int64_t)h_ctl[l].canon;
+            stats->tests_executed[l] = (int64_t)h_ctl[l].executed;
+            stats->max_degree[l] = h_ctl[l].maxdeg;
+            stats->singular_pivots += (int64_t)h_ctl[l].singular;
+            // plan(l+1) ran (level l was not "done") and recorded nnz before deciding about l+1
+            stats->edges_after[l] = (int64_t)(((l < maxl) ? h_ctl[l + 1].nnz : h_ctl[CUSK_ML + 1].nnz) / 2);
+        }
+        if (maxl == 0) stats->edges_after[0] = (int64_t)(h_ctl[CUSK_ML + 1].nnz / 2);
+        for (int l = 0; l <= maxl; l++) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, ev[l], ev[l + 1]) == cudaSuccess) stats->level_ms[l] = ms;
+        }
+        float tot = 0.f;
+        if (cudaEventElapsedTime(&tot, ev[0], ev[maxl + 1]) == cudaSuccess) stats->total_ms = tot;
+        stats->last_level = last;
+        stats->levels_run = levels_run;
+    }
+    if (infeasible == 1) {
+        cusk_set_error("skeleton: a row needs >= 2^48 conditioning sets at some level (degree too large)");
+        return CUSK_E_INFEASIBLE;
+    }
+    if (infeasible == 2) {
+        cusk_set_error("skeleton: a row's per-warp state does not fit in shared memory at some level");
+        return CUSK_E_INFEASIBLE;
+    }
+    return CUSK_OK;
+}
+
+}  // namespace
+
+// ---- engine entry points used by api.cu and the correlation -> skeleton pipeline ----------------
+int skeleton_engine(cusk_ctx *ctx, const float *dC, int n, uint32_t *dbits, const float *Th, int maxlevel,
+                    int *l_out, float *d_pMax, std::vector<cusk_sepset> *seps, cusk_stats *stats)
+{
+    arena_reset(ctx);
+    EngineArgs a = {};
+    a.het = false;
+    a.dC = dC;
+    a.n = n;
+    a.dbits = dbits;
+    a.Th = Th;
+    a.maxlevel = maxlevel;
+    a.d_pMax = d_pMax;
+    a.want_seps = seps != nullptr;
+    EngineOut eo;
+    int rc = run_engine(ctx, a, &eo, stats);
+    if (rc) return rc;
+    if (l_out) *l_out = eo.last_level;
+    if (seps) {
+        seps->resize((size_t)eo.sep_count);
+        if (eo.sep_count) {
+            CUSK_CUDA(cudaMemcpyAsync(seps->data(), eo.d_seps, (size_t)eo.sep_count * sizeof(cusk_sepset),
+                                      cudaMemcpyDeviceToHost, ctx->stream));
+            CUSK_CUDA(cudaStreamSynchronize(ctx->stream));
+            // the device appends in scheduling order; the contents are deterministic, the order is made so
+            std::sort(seps->begin(), seps->end(), [](const cusk_sepset &p, const cusk_sepset &q) {
+                return p.x != q.x ? p.x < q.x : p.y < q.y;
+            });
+        }
+    }
+    return CUSK_OK;
+}
+
+int hetcor_engine(cusk_ctx *ctx, const float *dC, int n, uint32_t *dbits, const int *dG_dense, bool bits_are_input,
+                  const float *dN, float n_uniform, float th, int maxlevel, const int *d_time, int *l_out,
+                  cusk_stats *stats)
+{
+    arena_reset(ctx);
+    EngineArgs a = {};
+    a.het = true;
+    a.dC = dC;
+    a.n = n;
+    a.dbits = dbits;
+    a.dG_in = dG_dense;
+    a.bits_are_input = bits_are_input;
+    a.all_ones = !bits_are_input && dG_dense == nullptr;
+    a.dN = dN;
+    a.n_uniform = n_uniform;
+    a.th_het = th;
+    a.maxlevel = maxlevel;
+    a.d_time = d_time;
+    EngineOut eo;
+    int rc = run_engine(ctx, a, &eo, stats);
+    if (rc) return rc;
+    if (l_out) *l_out = eo.last_level;
+    return CUSK_OK;
+}
+
+extern "C" int cusk_skeleton_dev(cusk_ctx *ctx, const float *dC, int n, uint32_t *dG_bits, const float *Th,
+                                 int maxlevel, int *l_out, float *d_pMax, cusk_sepset *sep, int64_t sep_cap,
+                                 int64_t *sep_n, cusk_stats *stats)
+{
+    if (!ctx || !dC || !dG_bits || !Th) {
+        cusk_set_error("cusk_skeleton_dev: NULL argument");
+        return CUSK_E_ARG;
+    }
+    CUSK_CUDA(cudaSetDevice(ctx->device));
+    std::vector<cusk_sepset> seps;
+    const bool want = sep != nullptr || sep_n != nullptr;
+    int rc = skeleton_engine(ctx, dC, n, dG_bits, Th, maxlevel, l_out, d_pMax, want ? &seps : nullptr, stats);
+    if (rc) return rc;
+    if (sep_n) *sep_n = (int64_t)seps.size();
+    if (sep && sep_cap > 0)
+        memcpy(sep, seps.data(), std::min<size_t>(seps.size(), (size_t)sep_cap) * sizeof(cusk_sepset));
+    return CUSK_OK;
+}
+
+extern "C" int cusk_hetcor_skeleton_dev(cusk_ctx *ctx, const float *dC, int n, uint32_t *dG_bits,
+                                        int G_in_all_ones, const float *dN, float n_uniform, float th,
+                                        int maxlevel, const int *d_time_index, int *l_out, cusk_stats *stats)
+{
+    if (!ctx || !dC || !dG_bits) {
+        cusk_set_error("cusk_hetcor_skeleton_dev: NULL argument");
+        return CUSK_E_ARG;
+    }
+    CUSK_CUDA(cudaSetDevice(ctx->device));
+    return hetcor_engine(ctx, dC, n, dG_bits, nullptr, !G_in_all_ones, dN, n_uniform, th, maxlevel, d_time_index,
+                         l_out, stats);
+}

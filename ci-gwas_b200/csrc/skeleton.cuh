@@ -1,0 +1,41 @@
+// skeleton.cuh -- device-side control block and kernel parameter structs of the skeleton engines.
+#pragma once
+#include "common.cuh"
+
+#define CI_NWARPS 16
+#define CI_NTHREADS (CI_NWARPS * 32)
+#define CI_ZB 4                 // leaf (z) register blocking
+#define CI_PIVOT_TOL 1e-10      // |pivot| below this: the direction is dropped (pseudo-inverse)
+#define CI_MAX_COMB ((u64)1 << 48)  // per-row conditioning-set count above which a level is infeasible
+
+// One per level, written by plan_kernel, read by every other kernel of the level and copied
+// back to the host at the end of the call.
+struct LevelCtl {
+    int done;        // 1: this level (and all later ones) does not run
+    int maxdeg;      // max degree at level start
+    int nitems;      // work items of the CI kernel
+    int infeasible;  // 1: some row has >= CI_MAX_COMB sets; 2: a row does not fit in shared memory
+    u64 canon;       // canonical test count (per-row C(d,l) capped at 2^40 as the oracle does)
+    u64 executed;    // tests evaluated
+    u64 nnz;         // directed edges at level start
+    u64 singular;    // dropped pivots
+    double T2;       // tanh(threshold)^2 of the level (non-het and uniform-N het)
+};
+
+struct CiParams {
+    const float *C;
+    const float *N;          // het, general N; nullptr when uniform
+    const int *time_index;   // het; nullptr when all equal
+    int n, l, rw;
+    uint32_t *bits;
+    const int *deg;
+    const int *rowptr;
+    const int *adj;
+    const int *itemstart;
+    const u64 *chunk;
+    LevelCtl *ctl;
+    int *work_counter;
+    u64 *minkey;             // non-het
+    double th_het;
+    int smem_bytes;
+};

@@ -1,0 +1,454 @@
+// skeleton_kernels.cu -- level-0 tests, adjacency compaction, level planning, separating-set
+// resolution and output expansion kernels of the two skeleton engines (sm_100a).
+//
+// Device data layout:
+//   C      float [n][n]     correlations, symmetric, row-major (as the reference passes them)
+//   bits   u32   [n][rw]    adjacency bitmap, rw = ceil(n/32); bit (y&31) of word y>>5 of row x
+//   deg    int   [n]        row degrees at level start
+//   rowptr int   [n+1]      CSR offsets of the compacted adjacency (the reference's GPrime)
+//   adj    int   [nnz]      sorted neighbour ids per row
+//   minkey u64   [nnz]      individual-level engine: lowest separating-set rank found per slot
+#include "skeleton.cuh"
+
+__device__ __forceinline__ double fisher_z(double rho)
+{
+    return fabs(0.5 * log(fabs((1.0 + rho) / (1.0 - rho))));
+}
+
+// ---------------------------------------------------------------------------------------------
+// Level 0 (src/cuPC-S.cu:458-484, src/hetcor-cuPC-S.cu:343-377).  One warp produces one 32-bit
+// adjacency word with a ballot: lane c of the warp tests pair (row, 32*word + c).
+// Algorithmic bytes: 4 n^2 (C) [+ 4 n^2 N, + 4 n^2 G_in for the het engine] read, n^2/8 written.
+// ---------------------------------------------------------------------------------------------
+template <bool HET>
+__global__ void __launch_bounds__(256) level0_kernel(const float *__restrict__ C,
+                                                     const float *__restrict__ N, float n_uniform,
+                                                     const int *__restrict__ G_in, int n, int rw,
+                                                     double th, uint32_t *__restrict__ bits,
+                                                     float *__restrict__ pMax)
+{
+    const int lane = threadIdx.x & 31;
+    const int word = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int r = blockIdx.y;
+    if (word >= rw) return;
+    const int c = word * 32 + lane;
+    bool keep = false;
+    if (c < n && c != r) {
+        // the reference evaluates the pair once, from the upper-triangle entry
+        const size_t ix = (r < c) ? (size_t)r * n + c : (size_t)c * n + r;
+        const double z = fisher_z((double)C[ix]);
+        if (HET) {
+            const bool cand = G_in ? (G_in[(size_t)r * n + c] == 1) : true;
+            const double nn = N ? (double)N[ix] : (double)n_uniform;
+            const double loc_th = th / sqrt(nn - 3.0);
+            keep = cand && !(z < loc_th);
+        } else {
+            keep = !(z < th);
+            if (pMax) pMax[(size_t)r * n + c] = keep ? 0.f : (float)z;
+        }
+    } else if (!HET && pMax && c == r && c < n) {
+        pMax[(size_t)r * n + c] = 0.f;
+    }
+    const uint32_t w = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) bits[(size_t)r * rw + word] = w;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Degrees: one warp per row, popcount over the bitmap row.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) degree_kernel(const uint32_t *__restrict__ bits, int n, int rw,
+                                                     int *__restrict__ deg, const LevelCtl *prev)
+{
+    if (prev && prev->done) return;
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= n) return;
+    int c = 0;
+    for (int w = lane; w < rw; w += 32) c += __popc(bits[(size_t)r * rw + w]);
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) deg[r] = c;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Level plan: a single CTA scans the degrees into CSR offsets, decides whether the level runs
+// (src/cuPC-S.cu:154-159: a level l runs iff max_degree - 1 >= l), sizes the work items of the
+// CI kernel and computes the level's decision constant.
+//   th_level >= 0 : fixed threshold of the level (individual-level engine)
+//   th_level <  0 : het engine; uniform N -> threshold th_het / sqrt(trunc(N) - l - 3)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ u64 block_scan_excl_u64(u64 v, u64 *s_warp, u64 *total)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    u64 inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        const u64 t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        u64 w = (lane < (int)(blockDim.x >> 5)) ? s_warp[lane] : 0;
+        u64 winc = w;
+        for (int o = 1; o < 32; o <<= 1) {
+            const u64 t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += t;
+        }
+        s_warp[lane] = winc - w;
+        if (lane == 31) s_warp[32] = winc;
+    }
+    __syncthreads();
+    *total = s_warp[32];
+    return s_warp[wid] + inc - v;
+}
+
+__global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg, int n, int l,
+                                                    int *__restrict__ rowptr, int *__restrict__ itemstart,
+                                                    u64 *__restrict__ chunk, LevelCtl *ctl,
+                                                    const LevelCtl *prev, double th_level, double th_het,
+                                                    float n_uniform, int *work_counter)
+{
+    __shared__ u64 s_warp[33];
+    __shared__ int s_maxdeg;
+    __shared__ u64 s_target;
+    __shared__ int s_infeasible;
+    const int tid = threadIdx.x;
+    if (prev && prev->done) {
+        if (tid == 0) {
+            ctl->done = 1;
+            ctl->nitems = 0;
+        }
+        return;
+    }
+    if (tid == 0) {
+        s_maxdeg = 0;
+        s_infeasible = 0;
+    }
+    __syncthreads();
+    // pass 1: CSR offsets, max degree, canonical test count
+    u64 carry = 0, tests_sum = 0, canon_sum = 0;
+    int mx = 0;
+    for (int base = 0; base < n; base += blockDim.x) {
+        const int r = base + tid;
+        const int d = (r < n) ? deg[r] : 0;
+        mx = max(mx, d);
+        u64 tot;
+        const u64 ex = block_scan_excl_u64((u64)d, s_warp, &tot);
+        if (r < n) rowptr[r] = (int)(carry + ex);
+        carry += tot;
+        if (r < n && d > l) {
+            const u64 c = binom64(d, l);
+            if (c >= CI_MAX_COMB)
+                atomicExch(&s_infeasible, 1);
+            else
+                tests_sum += c * (u64)(d - l);
+            canon_sum += (c > ((u64)1 << 40) ? ((u64)1 << 40) : c) * (u64)(d - l);
+        }
+    }
+    if (tid == 0) rowptr[n] = (int)carry;
+    atomicMax(&s_maxdeg, mx);
+    u64 tot_tests, tot_canon;
+    block_scan_excl_u64(tests_sum, s_warp, &tot_tests);
+    block_scan_excl_u64(canon_sum, s_warp, &tot_canon);
+    __syncthreads();
+    const bool runs = (s_maxdeg - 1 >= l) && !s_infeasible;
+    if (tid == 0) {
+        ctl->maxdeg = s_maxdeg;
+        ctl->nnz = carry;
+        ctl->canon = (s_maxdeg - 1 >= l) ? tot_canon : 0;
+        ctl->executed = 0;
+        ctl->singular = 0;
+        ctl->infeasible = s_infeasible;
+        ctl->done = runs ? 0 : 1;
+        double th = th_level;
+        if (th_level < 0) {
+            const double m = (double)__float2int_rz(n_uniform);
+            th = th_het / sqrt(m - (double)l - 3.0);
+        }
+        const double t = tanh(th);
+        ctl->T2 = t * t;
+        u64 target = tot_tests / 4096;
+        if (target < ((u64)1 << 14)) target = (u64)1 << 14;
+        s_target = target;
+        *work_counter = 0;
+    }
+    __syncthreads();
+    if (!runs) {
+        if (tid == 0) ctl->nitems = 0;
+        return;
+    }
+    // pass 2: work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks.
+    const u64 target = s_target;
+    carry = 0;
+    for (int base = 0; base < n; base += blockDim.x) {
+        const int r = base + tid;
+        const int d = (r < n) ? deg[r] : 0;
+        u64 items = 0;
+        if (r < n && d > l) {
+            const u64 c = binom64(d, l);
+            const u64 tests = c * (u64)(d - l);
+            items = (tests + target - 1) / target;
+            if (items > c) items = c;
+            if (items < 1) items = 1;
+            const u64 ch = (c + items - 1) / items;
+            items = (c + ch - 1) / ch;
+            chunk[r] = ch;
+        } else if (r < n) {
+            chunk[r] = 0;
+        }
+        u64 tot;
+        const u64 ex = block_scan_excl_u64(items, s_warp, &tot);
+        if (r < n) itemstart[r] = (int)(carry + ex);
+        carry += tot;
+    }
+    if (tid == 0) {
+        itemstart[n] = (int)carry;
+        ctl->nitems = (int)carry;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Compaction (replaces scan_compact, src/cuPC-S.cu:6355-6432): one warp per row; each lane
+// popcounts one bitmap word, a warp prefix sum gives its output offset, set bits are expanded
+// to ascending neighbour ids.  Bytes: n^2/8 read + 4 nnz written (+ 8 nnz for minkey).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) compact_kernel(const uint32_t *__restrict__ bits, int n, int rw,
+                                                      const int *__restrict__ rowptr, int *__restrict__ adj,
+                                                      u64 *__restrict__ minkey, const LevelCtl *ctl)
+{
+    if (ctl->done) return;
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= n) return;
+    int out = rowptr[r];
+    for (int w0 = 0; w0 < rw; w0 += 32) {
+        const int w = w0 + lane;
+        uint32_t word = (w < rw) ? bits[(size_t)r * rw + w] : 0u;
+        const int cnt = __popc(word);
+        int inc = cnt;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        int pos = out + inc - cnt;
+        while (word) {
+            const int b = __ffs(word) - 1;
+            word &= word - 1;
+            adj[pos] = w * 32 + b;
+            if (minkey) minkey[pos] = CUSK_KEY_NONE;
+            pos++;
+        }
+        out += __shfl_sync(0xffffffffu, inc, 31);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Individual-level engine, end of a level: every slot with a recorded rank becomes a separating
+// set (lowest lexicographic rank of row X; the deterministic reading of src/cuPC-S.cu:568-577),
+// its Z statistic is recomputed directly and both adjacency bits are cleared.
+// ---------------------------------------------------------------------------------------------
+__device__ double partial_corr_z_direct(const float *__restrict__ C, int n, int X, int Y, const int *S, int l)
+{
+    // incremental LDL^T over S, tracking only the later pivots and the two targets x, y
+    double u[CUSK_ML][CUSK_ML + 2];  // u[j][t]: t < l -> S[t], t = l -> X, t = l+1 -> Y
+    double dinv[CUSK_ML];
+    for (int j = 0; j < l; j++) {
+        double D = 1.0;
+        for (int i = 0; i < j; i++) D -= u[i][j] * u[i][j] * dinv[i];
+        const bool drop = fabs(D) < CI_PIVOT_TOL;
+        for (int t = 0; t < l + 2; t++) {
+            const int v = (t < l) ? S[t] : (t == l ? X : Y);
+            double acc = (t == j) ? 1.0 : (double)C[(size_t)S[j] * n + v];
+            for (int i = 0; i < j; i++) acc -= u[i][j] * u[i][t] * dinv[i];
+            u[j][t] = drop ? 0.0 : acc;
+        }
+        dinv[j] = drop ? 0.0 : 1.0 / D;
+    }
+    double h00 = 1.0, h11 = 1.0, h01 = (double)C[(size_t)X * n + Y];
+    for (int j = 0; j < l; j++) {
+        h00 -= u[j][l] * u[j][l] * dinv[j];
+        h11 -= u[j][l + 1] * u[j][l + 1] * dinv[j];
+        h01 -= u[j][l] * u[j][l + 1] * dinv[j];
+    }
+    const double rho = h01 / sqrt(fabs(h00 * h11));
+    return fisher_z(rho);
+}
+
+__global__ void __launch_bounds__(128) resolve_kernel(const float *__restrict__ C, int n, int rw, int l,
+                                                      uint32_t *bits, const int *__restrict__ deg,
+                                                      const int *__restrict__ rowptr,
+                                                      const int *__restrict__ adj,
+                                                      const u64 *__restrict__ minkey, float *pMax,
+                                                      cusk_sepset *seps, unsigned long long *sep_count,
+                                                      u64 sep_cap, const LevelCtl *ctl)
+{
+    if (ctl->done) return;
+    const int lane = threadIdx.x & 31;
+    const int X = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (X >= n) return;
+    const int d = deg[X];
+    if (d <= l) return;
+    const int *a = adj + rowptr[X];
+    for (int yp = lane; yp < d; yp += 32) {
+        const u64 key = minkey[rowptr[X] + yp];
+        if (key == CUSK_KEY_NONE) continue;
+        int pos[CUSK_ML], S[CUSK_ML];
+        unrank_comb(key, d, l, pos);
+        for (int i = 0; i < l; i++) S[i] = a[pos[i]];
+        const int Y = a[yp];
+        const double z = partial_corr_z_direct(C, n, X, Y, S, l);
+        if (pMax) pMax[(size_t)X * n + Y] = (float)z;
+        atomicAnd(&bits[(size_t)X * rw + (Y >> 5)], ~(1u << (Y & 31)));
+        atomicAnd(&bits[(size_t)Y * rw + (X >> 5)], ~(1u << (X & 31)));
+        if (seps) {
+            const u64 slot = atomicAdd(sep_count, 1ULL);
+            if (slot < sep_cap) {
+                cusk_sepset rec;
+                rec.x = X;
+                rec.y = Y;
+                rec.level = l;
+                rec.pmax = (float)z;
+                for (int i = 0; i < CUSK_ML; i++) rec.s[i] = (i < l) ? S[i] : -1;
+                seps[slot] = rec;
+            }
+        }
+    }
+}
+
+// pMax post-processing of src/cuPC-S.cu:424-442: diagonal 1, kept edges -100000, removed edges
+// the larger of the two directed entries.
+__global__ void __launch_bounds__(256) pmax_final_kernel(const uint32_t *__restrict__ bits, int n, int rw,
+                                                         float *pMax)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= n || j < i) return;
+    if (i == j) {
+        pMax[(size_t)i * n + i] = 1.f;
+        return;
+    }
+    const bool alive = (bits[(size_t)i * rw + (j >> 5)] >> (j & 31)) & 1u;
+    float v;
+    if (alive)
+        v = -100000.f;
+    else
+        v = fmaxf(pMax[(size_t)j * n + i], pMax[(size_t)i * n + j]);
+    pMax[(size_t)j * n + i] = v;
+    pMax[(size_t)i * n + j] = v;
+}
+
+// bitmap -> dense int adjacency (the reference's G[n*n] output)
+__global__ void __launch_bounds__(256) expand_bits_kernel(const uint32_t *__restrict__ bits, int n, int rw,
+                                                          int *__restrict__ G)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y;
+    if (c >= n) return;
+    G[(size_t)r * n + c] = (bits[(size_t)r * rw + (c >> 5)] >> (c & 31)) & 1u;
+}
+
+// dense int adjacency -> bitmap (G == 1 is an edge, src/cuPC-S.cu:6379)
+__global__ void __launch_bounds__(256) pack_bits_kernel(const int *__restrict__ G, int n, int rw,
+                                                        uint32_t *__restrict__ bits)
+{
+    const int lane = threadIdx.x & 31;
+    const int word = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int r = blockIdx.y;
+    if (word >= rw) return;
+    const int c = word * 32 + lane;
+    const bool e = (c < n) && (G[(size_t)r * n + c] == 1);
+    const uint32_t w = __ballot_sync(0xffffffffu, e);
+    if (lane == 0) bits[(size_t)r * rw + word] = w;
+}
+
+// reduce trunc(N[i,j]) over i != j to (min, max): uniform sample sizes take the fast path
+__global__ void __launch_bounds__(256) ess_minmax_kernel(const float *__restrict__ N, int n, int *mn, int *mx)
+{
+    // min / max of the float bit patterns (ordered like the values for f >= 0); a NaN or a
+    // negative entry poisons the result so that the general path is taken.  Uniform <=> mn == mx.
+    int lo = 2147483647, hi = -2147483647 - 1;
+    const size_t total = (size_t)n * n;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / n, c = i - r * n;
+        if (r == c) continue;
+        const float f = N[i];
+        if (!(f >= 0.f)) {
+            lo = -2147483647 - 1;
+            hi = 2147483647;
+        } else {
+            const int v = __float_as_int(f);
+            lo = min(lo, v);
+            hi = max(hi, v);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(mn, lo);
+        atomicMax(mx, hi);
+    }
+}
+
+// ---- host-callable launch wrappers (defined here so that skeleton.cu stays host-only logic) ---
+void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, float n_uniform, const int *G_in,
+                   int n, int rw, double th, uint32_t *bits, float *pMax)
+{
+    dim3 grid((rw + 7) / 8, n);
+    if (het)
+        level0_kernel<true><<<grid, 256, 0, st>>>(C, N, n_uniform, G_in, n, rw, th, bits, pMax);
+    else
+        level0_kernel<false><<<grid, 256, 0, st>>>(C, N, n_uniform, G_in, n, rw, th, bits, pMax);
+}
+
+void launch_degree(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, const LevelCtl *prev)
+{
+    degree_kernel<<<(n + 7) / 8, 256, 0, st>>>(bits, n, rw, deg, prev);
+}
+
+void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int *itemstart, u64 *chunk,
+                 LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
+                 int *work_counter)
+{
+    plan_kernel<<<1, 1024, 0, st>>>(deg, n, l, rowptr, itemstart, chunk, ctl, prev, th_level, th_het,
+                                    n_uniform, work_counter);
+}
+
+void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
+                    u64 *minkey, const LevelCtl *ctl)
+{
+    compact_kernel<<<(n + 7) / 8, 256, 0, st>>>(bits, n, rw, rowptr, adj, minkey, ctl);
+}
+
+void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
+                    const int *rowptr, const int *adj, const u64 *minkey, float *pMax, cusk_sepset *seps,
+                    unsigned long long *sep_count, u64 sep_cap, const LevelCtl *ctl)
+{
+    resolve_kernel<<<(n + 3) / 4, 128, 0, st>>>(C, n, rw, l, bits, deg, rowptr, adj, minkey, pMax, seps,
+                                                sep_count, sep_cap, ctl);
+}
+
+void launch_pmax_final(cudaStream_t st, const uint32_t *bits, int n, int rw, float *pMax)
+{
+    dim3 grid((n + 255) / 256, n);
+    pmax_final_kernel<<<grid, 256, 0, st>>>(bits, n, rw, pMax);
+}
+
+void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, int *G)
+{
+    dim3 grid((n + 255) / 256, n);
+    expand_bits_kernel<<<grid, 256, 0, st>>>(bits, n, rw, G);
+}
+
+void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits)
+{
+    dim3 grid((rw + 7) / 8, n);
+    pack_bits_kernel<<<grid, 256, 0, st>>>(G, n, rw, bits);
+}
+
+void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count)
+{
+    ess_minmax_kernel<<<sm_count * 8, 256, 0, st>>>(N, n, mn, mx);
+}

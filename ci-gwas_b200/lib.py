@@ -1,0 +1,214 @@
+"""ctypes binding of libcusk_b200.so (see include/cusk_b200.h for the contract of every symbol)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ML = 14
+
+c_float_p = C.POINTER(C.c_float)
+c_int_p = C.POINTER(C.c_int)
+c_i64_p = C.POINTER(C.c_int64)
+c_u32_p = C.POINTER(C.c_uint32)
+c_ubyte_p = C.POINTER(C.c_ubyte)
+
+
+class CuskError(RuntimeError):
+    pass
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("tests_canonical", C.c_int64 * (ML + 1)),
+        ("tests_executed", C.c_int64 * (ML + 1)),
+        ("level_ms", C.c_float * (ML + 1)),
+        ("max_degree", C.c_int32 * (ML + 1)),
+        ("edges_after", C.c_int64 * (ML + 1)),
+        ("singular_pivots", C.c_int64),
+        ("last_level", C.c_int32),
+        ("levels_run", C.c_int32),
+        ("total_ms", C.c_float),
+        ("h2d_ms", C.c_float),
+        ("d2h_ms", C.c_float),
+    ]
+
+    def as_dict(self):
+        return dict(
+            tests_canonical=list(self.tests_canonical),
+            tests_executed=list(self.tests_executed),
+            level_ms=[float(x) for x in self.level_ms],
+            max_degree=list(self.max_degree),
+            edges_after=list(self.edges_after),
+            singular_pivots=int(self.singular_pivots),
+            last_level=int(self.last_level),
+            levels_run=int(self.levels_run),
+            total_ms=float(self.total_ms),
+            h2d_ms=float(self.h2d_ms),
+            d2h_ms=float(self.d2h_ms),
+        )
+
+
+SEPSET_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("level", "<i4"), ("pmax", "<f4"), ("s", "<i4", (ML,))])
+
+_LIB = None
+
+
+def library_path():
+    return os.path.join(_HERE, "libcusk_b200.so")
+
+
+def build_library(verbose=False):
+    """nvcc -gencode arch=compute_100a,code=sm_100a build of csrc/ (cross-compiles without a GPU)."""
+    cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-j8"]
+    if not verbose:
+        cmd.insert(1, "-s")
+    subprocess.check_call(cmd)
+    return library_path()
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+def load_library():
+    """Loads the CUDA library; raises CuskError when it has not been built (no fallback)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if not os.path.exists(path):
+        raise CuskError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    lib.cusk_last_error.restype = C.c_char_p
+    lib.cusk_version.restype = C.c_char_p
+    lib.cusk_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.cusk_ctx_destroy.argtypes = [C.c_void_p]
+    lib.cusk_ctx_stream.restype = C.c_void_p
+    lib.cusk_ctx_stream.argtypes = [C.c_void_p]
+    lib.cusk_ctx_sync.argtypes = [C.c_void_p]
+    lib.cusk_threshold_array.argtypes = [C.c_int, C.c_float, c_float_p]
+    lib.cusk_hetcor_threshold.restype = C.c_float
+    lib.cusk_hetcor_threshold.argtypes = [C.c_float]
+    lib.cusk_row_words.restype = C.c_size_t
+    lib.cusk_row_words.argtypes = [C.c_int]
+    lib.cusk_skeleton.argtypes = [C.c_void_p, c_float_p, C.c_int, c_int_p, c_float_p, C.c_int, c_int_p,
+                                  c_float_p, c_int_p, C.c_void_p, C.c_int64, c_i64_p, C.POINTER(Stats)]
+    lib.cusk_hetcor_skeleton.argtypes = [C.c_void_p, c_float_p, C.c_int, c_int_p, C.c_int, c_float_p,
+                                         C.c_float, C.c_int, c_int_p, c_int_p, C.POINTER(Stats)]
+    lib.cusk_hetcor_skeleton_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                             C.c_float, C.c_float, C.c_int, C.c_void_p, c_int_p,
+                                             C.POINTER(Stats)]
+    lib.cusk_skeleton_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, c_float_p, C.c_int, c_int_p,
+                                      C.c_void_p, C.c_void_p, C.c_int64, c_i64_p, C.POINTER(Stats)]
+    _LIB = lib
+    return lib
+
+
+def threshold_array(n, alpha):
+    """cuPC_call_prep.cpp:13-23"""
+    out = np.zeros(15, np.float32)
+    load_library().cusk_threshold_array(int(n), C.c_float(alpha), _p(out, c_float_p))
+    return out
+
+
+def hetcor_threshold(alpha):
+    """cuPC_call_prep.cpp:25-28"""
+    return float(load_library().cusk_hetcor_threshold(C.c_float(alpha)))
+
+
+class Context:
+    """One device + stream + reusable workspace (cusk_ctx)."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.cusk_ctx_create(int(device), C.byref(h))
+        if rc != 0:
+            raise CuskError(self.lib.cusk_last_error().decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cusk_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise CuskError(f"rc={rc}: {self.lib.cusk_last_error().decode()}")
+
+    @property
+    def stream(self):
+        return self.lib.cusk_ctx_stream(self.h)
+
+    def sync(self):
+        self._check(self.lib.cusk_ctx_sync(self.h))
+
+    # -- Skeleton(), src/cuPC-S.cu:61 ------------------------------------------------------------
+    def skeleton(self, Cm, Th, maxlevel, want_pmax=True, want_dense_sepset=True):
+        Cm = np.ascontiguousarray(Cm, np.float32)
+        n = Cm.shape[0]
+        G = np.zeros((n, n), np.int32)
+        Th = np.ascontiguousarray(Th, np.float32)
+        pMax = np.zeros((n, n), np.float32) if want_pmax else None
+        Sep = np.zeros((n, n, ML), np.int32) if want_dense_sepset else None
+        l = C.c_int(0)
+        st = Stats()
+        cap = max(1024, n * 64)
+        while True:
+            recs = np.zeros(cap, SEPSET_DTYPE)
+            nsep = C.c_int64(0)
+            self._check(self.lib.cusk_skeleton(self.h, _p(Cm, c_float_p), n, _p(G, c_int_p), _p(Th, c_float_p),
+                                               int(maxlevel), C.byref(l), _p(pMax, c_float_p), _p(Sep, c_int_p),
+                                               recs.ctypes.data_as(C.c_void_p), cap, C.byref(nsep),
+                                               C.byref(st)))
+            if nsep.value <= cap:
+                break
+            cap = int(nsep.value)
+        return dict(G=G, l=l.value, pMax=pMax, SepSet=Sep, seps=recs[: nsep.value], stats=st.as_dict())
+
+    # -- hetcor_skeleton(), src/hetcor-cuPC-S.cu:75 ---------------------------------------------
+    def hetcor_skeleton(self, Cm, G, N, th, maxlevel, time_index=None):
+        Cm = np.ascontiguousarray(Cm, np.float32)
+        n = Cm.shape[0]
+        all_ones = G is None
+        Gw = np.ones((n, n), np.int32) if all_ones else np.array(G, np.int32, copy=True).reshape(n, n)
+        N = np.ascontiguousarray(N, np.float32)
+        ti = None if time_index is None else np.ascontiguousarray(time_index, np.int32)
+        l = C.c_int(0)
+        st = Stats()
+        self._check(self.lib.cusk_hetcor_skeleton(self.h, _p(Cm, c_float_p), n, _p(Gw, c_int_p), int(all_ones),
+                                                  _p(N, c_float_p), C.c_float(th), int(maxlevel),
+                                                  _p(ti, c_int_p), C.byref(l), C.byref(st)))
+        return dict(G=Gw, l=l.value, stats=st.as_dict())
+
+    # -- device-resident variants (pointers are ints, e.g. torch.Tensor.data_ptr()) -----------------
+    def row_words(self, n):
+        return int(self.lib.cusk_row_words(int(n)))
+
+    def hetcor_skeleton_dev(self, dC, n, dbits, all_ones, dN, n_uniform, th, maxlevel, d_time=None):
+        l = C.c_int(0)
+        st = Stats()
+        self._check(self.lib.cusk_hetcor_skeleton_dev(self.h, dC, int(n), dbits, int(all_ones), dN,
+                                                      C.c_float(n_uniform), C.c_float(th), int(maxlevel),
+                                                      d_time, C.byref(l), C.byref(st)))
+        return l.value, st.as_dict()
+
+    def skeleton_dev(self, dC, n, dbits, Th, maxlevel, d_pmax=None, want_seps=False):
+        Th = np.ascontiguousarray(Th, np.float32)
+        l = C.c_int(0)
+        st = Stats()
+        nsep = C.c_int64(0)
+        self._check(self.lib.cusk_skeleton_dev(self.h, dC, int(n), dbits, _p(Th, c_float_p), int(maxlevel),
+                                               C.byref(l), d_pmax, None, 0,
+                                               C.byref(nsep) if want_seps else None, C.byref(st)))
+        return l.value, st.as_dict(), nsep.value

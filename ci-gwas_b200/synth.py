@@ -1,0 +1,134 @@
+"""Deterministic synthetic inputs of the shapes BASELINE.json names.
+
+All generators are numpy-only and seeded (PCG64, master seed 20261104 + stream id) so that the
+parity tests, the bench and the reference arm see bit-identical inputs.
+"""
+import numpy as np
+
+MASTER_SEED = 20261104
+
+
+def rng_for(stream):
+    return np.random.Generator(np.random.PCG64([MASTER_SEED, int(stream)]))
+
+
+def sem_correlation(m, p, stream=2, sub_block=50, window=8, max_parents=3, causal_per_trait=30,
+                    trait_density=0.3, num_samples=None, dtype=np.float32):
+    """Population correlation matrix of a linear SEM: m markers in LD sub-blocks followed by p traits.
+
+    Markers: each marker has 1..max_parents parents among the previous `window` markers of its
+    sub-block (weights U(0.3,0.7), random sign, rescaled so that the explained variance stays
+    below 0.9); the first marker of a sub-block depends on the last marker of the previous one
+    with weight 0.3.  Traits: `causal_per_trait` causal markers (|beta| ~ U(0.01,0.05)) and
+    lower-triangular trait-trait effects U(-0.3,0.3) with density `trait_density`.  All variables
+    have unit variance, so the covariance A A' is the correlation matrix (exactly PSD).
+    num_samples: if given, symmetric N(0, 1/num_samples) sampling noise is added off the diagonal.
+    Returns C [m+p, m+p] with unit diagonal, markers first (the order cusk's square matrix uses,
+    cli.cpp:597-649).
+    """
+    rng = rng_for(stream)
+    nv = m + p
+    A = np.zeros((nv, nv), np.float64)  # x = A e, e iid N(0,1)
+    for i in range(m):
+        first_of_block = (i % sub_block) == 0
+        row = np.zeros(nv, np.float64)
+        if i > 0:
+            if first_of_block:
+                par = np.array([i - 1])
+                w = np.array([0.3])
+            else:
+                lo = max(i - window, i - (i % sub_block))
+                k = int(rng.integers(1, max_parents + 1))
+                k = min(k, i - lo)
+                par = rng.choice(np.arange(lo, i), size=k, replace=False)
+                w = rng.uniform(0.3, 0.7, size=k) * rng.choice([-1.0, 1.0], size=k)
+            row = w @ A[par]
+            v = float(row @ row)
+            if v > 0.9:
+                row *= np.sqrt(0.9 / v)
+                v = 0.9
+        else:
+            v = 0.0
+        row[i] = np.sqrt(1.0 - v)
+        A[i] = row
+    for t in range(p):
+        i = m + t
+        k = min(causal_per_trait, m)
+        par = rng.choice(np.arange(m), size=k, replace=False)
+        w = rng.uniform(0.01, 0.05, size=k) * rng.choice([-1.0, 1.0], size=k)
+        row = w @ A[par]
+        for u in range(t):
+            if rng.random() < trait_density:
+                row = row + rng.uniform(-0.3, 0.3) * A[m + u]
+        v = float(row @ row)
+        if v > 0.9:
+            row *= np.sqrt(0.9 / v)
+            v = 0.9
+        row[i] = np.sqrt(1.0 - v)
+        A[i] = row
+    Cm = A @ A.T
+    if num_samples:
+        E = rng.standard_normal((nv, nv)) / np.sqrt(float(num_samples))
+        E = np.triu(E, 1)
+        Cm = Cm + E + E.T
+    np.fill_diagonal(Cm, 1.0)
+    Cm = np.clip(Cm, -0.999999, 0.999999)
+    np.fill_diagonal(Cm, 1.0)
+    Cm = Cm.astype(dtype)
+    # exact symmetry after the cast
+    Cm = np.triu(Cm) + np.triu(Cm, 1).T
+    return np.ascontiguousarray(Cm)
+
+
+def c2_single_block(m=3000, p=17, num_samples=458000, stream=2):
+    """BASELINE.json configs[1]: cuskss single LD block, 3k markers + 17 traits."""
+    return sem_correlation(m, p, stream=stream, num_samples=num_samples)
+
+
+def het_sample_sizes(nv, m, num_samples, stream=5, lo=50000, na_rate=0.005):
+    """Effective sample sizes of a heterologous-correlation run: marker-marker entries are the
+    nominal sample size, marker-trait / trait-trait entries are U(lo, num_samples) and a fraction
+    is NaN (missing SE), symmetric."""
+    rng = rng_for(stream + 1000)
+    N = np.full((nv, nv), float(num_samples), np.float64)
+    blk = rng.uniform(lo, num_samples, size=(nv, nv - m))
+    N[:, m:] = blk
+    N[m:, :] = N[:, m:].T
+    N = np.triu(N) + np.triu(N, 1).T
+    mask = rng.random((nv, nv)) < na_rate
+    mask[:, :m] &= False
+    mask = np.triu(mask, 1)
+    mask = mask | mask.T
+    N[mask] = np.nan
+    return N.astype(np.float32)
+
+
+def random_bed(n_samples, m, stream=3, missing_rate=0.0, sub_block=50, copy_prob=0.95):
+    """Packed PLINK BED columns (no magic bytes) of an LD-structured genotype block.
+
+    Haplotype Markov chain along markers within sub-blocks (copy the previous marker's allele with
+    prob `copy_prob`), MAF ~ U(0.01, 0.5), two haplotypes summed (HWE).  Returns uint8
+    [m, ceil(n/4)].  Coding (bed_lut_gpu.h): 00 -> 2, 01 -> missing, 10 -> 1, 11 -> 0.
+    """
+    rng = rng_for(stream)
+    nb = (n_samples + 3) // 4
+    out = np.zeros((m, nb), np.uint8)
+    code_of = np.array([3, 2, 0], np.uint8)  # genotype 0,1,2 -> 2-bit code
+    hap = None
+    for j in range(m):
+        maf = rng.uniform(0.01, 0.5)
+        fresh = (rng.random((2, n_samples)) < maf)
+        if hap is None or (j % sub_block) == 0:
+            hap = fresh
+        else:
+            keep = rng.random((2, n_samples)) < copy_prob
+            hap = np.where(keep, hap, fresh)
+        g = hap[0].astype(np.uint8) + hap[1].astype(np.uint8)
+        codes = code_of[g]
+        if missing_rate > 0:
+            miss = rng.random(n_samples) < missing_rate
+            codes = np.where(miss, np.uint8(1), codes)
+        pad = np.full(nb * 4 - n_samples, 0, np.uint8)  # padding bits 00
+        c4 = np.concatenate([codes, pad]).reshape(nb, 4)
+        out[j] = c4[:, 0] | (c4[:, 1] << 2) | (c4[:, 2] << 4) | (c4[:, 3] << 6)
+    return out

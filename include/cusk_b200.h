@@ -1,0 +1,121 @@
+/* cusk_b200.h -- C ABI of libcusk_b200.so, the B200 (sm_100a) implementation of the CI-GWAS
+ * skeleton hot path.  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to
+ * /root/reference/cusk/).  Two families:
+ *
+ *   1. the reference's own host-function signatures (drop-in: same names, same argument
+ *      meaning, host buffers in / host buffers out, device 0, blocking), and
+ *   2. an explicit-context API (device id, reusable workspace, status codes, statistics,
+ *      sparse separating-set output, device-resident inputs) which the drop-in wrappers and
+ *      the `mps`-compatible host binary are built on.
+ *
+ * Error convention: family 2 returns 0 on success and a negative CUSK_E_* code otherwise;
+ * cusk_last_error() returns a thread-local message.  Family 1 mirrors the reference
+ * (include/mps/gpuerrors.h:6-35): print the message to stderr and exit(EXIT_FAILURE).
+ * There is no CPU fallback anywhere: without a CUDA device every compute call fails.
+ */
+#ifndef CUSK_B200_H_
+#define CUSK_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CUSK_ML 14 /* include/mps/cuPC-S.h:49  (#define ML 14) */
+
+enum {
+    CUSK_OK = 0,
+    CUSK_E_CUDA = -1,       /* a CUDA runtime call failed */
+    CUSK_E_ARG = -2,        /* invalid argument */
+    CUSK_E_INFEASIBLE = -3, /* a level needs >= 2^62 conditioning sets for one row */
+    CUSK_E_NODEVICE = -4    /* no CUDA device / wrong architecture */
+};
+
+typedef struct cusk_ctx cusk_ctx; /* opaque: one device, one stream, reusable workspace */
+
+/* Per-call statistics (all levels 0..14).  tests_canonical[l] = sum_X C(d_X,l)(d_X-l), the
+ * schedule independent full PC-stable enumeration; tests_executed[l] = CI tests
+ * actually evaluated by this implementation (early termination skips the rest). */
+typedef struct cusk_stats {
+    int64_t tests_canonical[CUSK_ML + 1];
+    int64_t tests_executed[CUSK_ML + 1];
+    float level_ms[CUSK_ML + 1]; /* device time of each level (CUDA events) */
+    int32_t max_degree[CUSK_ML + 1]; /* max degree at the START of level l (l >= 1) */
+    int64_t edges_after[CUSK_ML + 1]; /* undirected edges alive after level l */
+    int64_t singular_pivots; /* conditioning sets with a (near-)singular leading block */
+    int32_t last_level;      /* == *l of the reference API */
+    int32_t levels_run;      /* number of levels that executed CI tests (incl. level 0) */
+    float total_ms;          /* device time, level 0 .. last level, excluding copies */
+    float h2d_ms, d2h_ms;    /* copy times of the host-buffer entry points */
+} cusk_stats;
+
+/* One separating set of the individual-level engine: slot [x,y] of the reference's dense
+ * SepSet array (src/cuPC-S.cu:568-577), in sparse form. */
+typedef struct cusk_sepset {
+    int32_t x, y;
+    int32_t level;        /* |S| */
+    float pmax;           /* Z statistic of the recorded test (pMax[x*n+y]) */
+    int32_t s[CUSK_ML];   /* variable indices, ascending, -1 padded */
+} cusk_sepset;
+
+/* ---- context ---------------------------------------------------------------------------- */
+int cusk_ctx_create(int device_id, cusk_ctx **out);
+void cusk_ctx_destroy(cusk_ctx *ctx);
+const char *cusk_last_error(void);
+const char *cusk_version(void);
+int cusk_device_count(void);
+/* the CUDA stream the context launches on (a cudaStream_t), for callers that time with events */
+void *cusk_ctx_stream(cusk_ctx *ctx);
+int cusk_ctx_sync(cusk_ctx *ctx);
+
+/* ---- thresholds  (replaces src/cuPC_call_prep.cpp:13-28) --------------------------------- */
+/* Th[l] = |qnorm(alpha/2)| / sqrt(n-l-3), l = 0..14, same float/double type flow. */
+void cusk_threshold_array(int n, float alpha, float *out15);
+float cusk_hetcor_threshold(float alpha);
+
+/* ---- skeleton, individual-level engine  (replaces Skeleton(), src/cuPC-S.cu:61-450) ------ */
+/* Host buffers.  C[n*n] in; G[n*n] out (0/1, symmetric, input ignored); Th[15];
+ * pMax[n*n] out or NULL; SepSet[n*n*14] out (-1 padded) or NULL; *l_out = last level.
+ * sep/sep_cap/sep_n: optional sparse separating-set list (NULL/0/NULL to skip). */
+int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const float *Th, int maxlevel,
+                  int *l_out, float *pMax, int *SepSet, cusk_sepset *sep, int64_t sep_cap,
+                  int64_t *sep_n, cusk_stats *stats);
+
+/* ---- skeleton, summary-statistic engine  (replaces hetcor_skeleton(),
+ *      src/hetcor-cuPC-S.cu:75-341) -------------------------------------------------------- */
+/* Host buffers.  G[n*n] in/out (1 = candidate edge, only cleared), or G_in_all_ones != 0 to
+ * ignore the input values; N[n*n] effective sample sizes (may hold NaN); th = |qnorm(a/2)|;
+ * time_index[n] or NULL (all equal). */
+int cusk_hetcor_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, int G_in_all_ones,
+                         const float *N, float th, int maxlevel, const int *time_index,
+                         int *l_out, cusk_stats *stats);
+
+/* Device-resident variants: dC, dN are device pointers (float, n*n); dG_bits is the bit-packed
+ * adjacency in/out on the device: n rows of cusk_row_words(n) uint32 words, bit (y & 31) of word
+ * y >> 5 in row x is edge x-y.  Nothing is copied to or from the host except the statistics.
+ * These are what bench.py's device-resident `value` times, and what corr -> skeleton uses. */
+size_t cusk_row_words(int n);
+int cusk_hetcor_skeleton_dev(cusk_ctx *ctx, const float *dC, int n, uint32_t *dG_bits,
+                             int G_in_all_ones, const float *dN, float n_uniform, float th,
+                             int maxlevel, const int *d_time_index, int *l_out,
+                             cusk_stats *stats);
+int cusk_skeleton_dev(cusk_ctx *ctx, const float *dC, int n, uint32_t *dG_bits, const float *Th,
+                      int maxlevel, int *l_out, float *d_pMax, cusk_sepset *sep, int64_t sep_cap,
+                      int64_t *sep_n, cusk_stats *stats);
+
+/* ---- drop-in signatures of the reference -------------------------------------------------- */
+/* include/mps/cuPC-S.h:192-194 */
+void Skeleton(float *C, int *P, int *G, float *Th, int *l, const int *maxlevel, float *pMax,
+              int *SepSet);
+/* include/mps/hetcor-cuPC-S.h:46 */
+void hetcor_skeleton(float *C, int *P, int *G, float *N, float *Th, int *l, const int *maxlevel,
+                     const int *time_index);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUSK_B200_H_ */
