@@ -9,7 +9,7 @@ struct Timer {
     cudaEvent_t a, b;
     cudaStream_t st;
     Timer(cusk_ctx *ctx, int slot)
-        : a(ctx->ev[2 * (CUSK_ML + 2) + slot * 2]), b(ctx->ev[2 * (CUSK_ML + 2) + slot * 2 + 1]), st(ctx->stream)
+        : a(ctx->ev[3 * (CUSK_ML + 2) + slot * 2]), b(ctx->ev[3 * (CUSK_ML + 2) + slot * 2 + 1]), st(ctx->stream)
     {
     }
     void start() { cudaEventRecord(a, st); }

@@ -52,7 +52,8 @@ struct cusk_ctx {
     // pinned staging for small control blocks / statistics
     void *h_pinned = nullptr;
     size_t h_pinned_bytes = 0;
-    cudaEvent_t ev[2 * (CUSK_ML + 2) + 4];
+    // [0, ML+2): level boundaries; [ML+2, 3(ML+2)): CI kernel start/stop per level; last 4: copies
+    cudaEvent_t ev[3 * (CUSK_ML + 2) + 4];
     bool ev_ready = false;
 };
 

@@ -166,8 +166,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.minkey = d_minkey;
         p.th_het = (double)a.th_het;
         p.smem_bytes = smem_bytes;
+        CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = launch_ci_level(st, a.het, p, grid);
         if (rc) return rc;
+        CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
         if (!a.het)
             launch_resolve(st, a.dC, n, rw, l, a.dbits, d_deg, d_rowptr, d_adj, d_minkey, a.d_pMax, d_seps,
                            d_sepcount, sep_cap, ctl);
@@ -221,6 +223,9 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         for (int l = 0; l <= maxl; l++) {
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, ev[l], ev[l + 1]) == cudaSuccess) stats->level_ms[l] = ms;
+            if (l >= 1 && !h_ctl[l].done &&
+                cudaEventElapsedTime(&ms, ev[(CUSK_ML + 2) + 2 * l], ev[(CUSK_ML + 2) + 2 * l + 1]) == cudaSuccess)
+                stats->ci_kernel_ms[l] = ms;
         }
         float tot = 0.f;
         if (cudaEventElapsedTime(&tot, ev[0], ev[maxl + 1]) == cudaSuccess) stats->total_ms = tot;

@@ -24,6 +24,7 @@ class Stats(C.Structure):
         ("tests_canonical", C.c_int64 * (ML + 1)),
         ("tests_executed", C.c_int64 * (ML + 1)),
         ("level_ms", C.c_float * (ML + 1)),
+        ("ci_kernel_ms", C.c_float * (ML + 1)),
         ("max_degree", C.c_int32 * (ML + 1)),
         ("edges_after", C.c_int64 * (ML + 1)),
         ("singular_pivots", C.c_int64),
@@ -39,6 +40,7 @@ class Stats(C.Structure):
             tests_canonical=list(self.tests_canonical),
             tests_executed=list(self.tests_executed),
             level_ms=[float(x) for x in self.level_ms],
+            ci_kernel_ms=[float(x) for x in self.ci_kernel_ms],
             max_degree=list(self.max_degree),
             edges_after=list(self.edges_after),
             singular_pivots=int(self.singular_pivots),

@@ -44,6 +44,7 @@ typedef struct cusk_stats {
     int64_t tests_canonical[CUSK_ML + 1];
     int64_t tests_executed[CUSK_ML + 1];
     float level_ms[CUSK_ML + 1]; /* device time of each level (CUDA events) */
+    float ci_kernel_ms[CUSK_ML + 1]; /* device time of the level's CI-test kernel alone */
     int32_t max_degree[CUSK_ML + 1]; /* max degree at the START of level l (l >= 1) */
     int64_t edges_after[CUSK_ML + 1]; /* undirected edges alive after level l */
     int64_t singular_pivots; /* conditioning sets with a (near-)singular leading block */
