@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
 
         if (lane == 0) {
             int tmp[CUSK_ML];
-            unrank_comb(Rw0, d, l, tmp);
+            unrank_comb_fast(Rw0, d, l, tmp);
             for (int i = 0; i < l; i++) pos[i] = tmp[i];
         }
         __syncwarp();

@@ -81,6 +81,33 @@ __host__ __device__ inline u64 binom64(int n, int k)
     return c;
 }
 
+// Same mapping as unrank_comb below, for C(N,k) < 2^48 and N < 2^15 (what the CI kernel
+// guarantees): the binomial is updated incrementally with exact 64-bit mul/div instead of being
+// recomputed with 128-bit arithmetic for every candidate position.
+__host__ __device__ inline void unrank_comb_fast(u64 rank, int N, int k, int *pos)
+{
+    if (k <= 0) return;
+    int m = N - 1;      // current "top" of C(m, r): sets whose slot i holds x use C(N-1-x, k-1-i)
+    int r = k - 1;
+    u64 c = binom64(m, r);
+    int x = 0;
+    for (int i = 0; i < k; i++) {
+        while (rank >= c) {  // skip x: C(m-1, r) = C(m, r) (m - r) / m
+            rank -= c;
+            c = (m > 0) ? c * (u64)(m - r) / (u64)m : 0;
+            m--;
+            x++;
+        }
+        pos[i] = x;
+        // take x: next slot counts C(m-1, r-1) = C(m, r) r / m
+        c = (m > 0) ? c * (u64)r / (u64)m : 0;
+        m--;
+        r--;
+        x++;
+        if (r < 0) break;
+    }
+}
+
 // 0-based lexicographic rank -> strictly increasing positions pos[0..k) out of {0..N-1}.
 __host__ __device__ inline void unrank_comb(u64 rank, int N, int k, int *pos)
 {

@@ -167,8 +167,10 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         }
         const double t = tanh(th);
         ctl->T2 = t * t;
-        u64 target = tot_tests / 4096;
-        if (target < ((u64)1 << 14)) target = (u64)1 << 14;
+        // aim at ~16 items per SM; small levels are cut finer (they are latency-bound: the
+        // more warps share a hub row's conditioning sets the shorter the critical path)
+        u64 target = tot_tests / (148 * 16);
+        if (target < 512) target = 512;
         s_target = target;
         *work_counter = 0;
     }
@@ -187,7 +189,12 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         if (r < n && d > l) {
             const u64 c = binom64(d, l);
             const u64 tests = c * (u64)(d - l);
-            items = (tests + target - 1) / target;
+            // an item re-stages the row's d x d submatrix: keep at least ~4 tests per staged entry
+            u64 tgt = target;
+            // (rows too large to stage gather from L2 per test and have no such cost)
+            const u64 stage_cost = (d <= 200) ? 4 * (u64)d * (u64)d : 0;
+            if (tgt < stage_cost) tgt = stage_cost;
+            items = (tests + tgt - 1) / tgt;
             if (items > c) items = c;
             if (items < 1) items = 1;
             const u64 ch = (c + items - 1) / items;
@@ -293,7 +300,7 @@ __global__ void __launch_bounds__(128) resolve_kernel(const float *__restrict__ 
         const u64 key = minkey[rowptr[X] + yp];
         if (key == CUSK_KEY_NONE) continue;
         int pos[CUSK_ML], S[CUSK_ML];
-        unrank_comb(key, d, l, pos);
+        unrank_comb_fast(key, d, l, pos);
         for (int i = 0; i < l; i++) S[i] = a[pos[i]];
         const int Y = a[yp];
         const double z = partial_corr_z_direct(C, n, X, Y, S, l);

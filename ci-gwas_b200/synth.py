@@ -13,7 +13,7 @@ def rng_for(stream):
 
 
 def sem_correlation(m, p, stream=2, sub_block=50, window=8, max_parents=3, causal_per_trait=30,
-                    trait_density=0.3, num_samples=None, dtype=np.float32):
+                    trait_density=0.3, num_samples=None, dtype=np.float32, wlo=0.3, whi=0.7):
     """Population correlation matrix of a linear SEM: m markers in LD sub-blocks followed by p traits.
 
     Markers: each marker has 1..max_parents parents among the previous `window` markers of its
@@ -41,7 +41,7 @@ def sem_correlation(m, p, stream=2, sub_block=50, window=8, max_parents=3, causa
                 k = int(rng.integers(1, max_parents + 1))
                 k = min(k, i - lo)
                 par = rng.choice(np.arange(lo, i), size=k, replace=False)
-                w = rng.uniform(0.3, 0.7, size=k) * rng.choice([-1.0, 1.0], size=k)
+                w = rng.uniform(wlo, whi, size=k) * rng.choice([-1.0, 1.0], size=k)
             row = w @ A[par]
             v = float(row @ row)
             if v > 0.9:
