@@ -31,7 +31,10 @@ template <bool HET>
 __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams p)
 {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ int s_item;
+    __shared__ struct {
+        int item, X, d, row0;
+        u64 R0, R1;
+    } s_it;
     LevelCtl *ctl = p.ctl;
     if (ctl->done) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -46,27 +49,38 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
 
     for (;;) {
         __syncthreads();
-        if (tid == 0) s_item = atomicAdd(p.work_counter, 1);
-        __syncthreads();
-        const int item = s_item;
-        if (item >= nitems) break;
-        // row of this item: largest X with itemstart[X] <= item
-        int lo = 0, hi = n;
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (p.itemstart[mid] <= item)
-                lo = mid;
-            else
-                hi = mid;
+        if (tid == 0) {
+            // one thread decodes the item (row lookup, C(d,l), rank range) for the whole CTA
+            const int item = atomicAdd(p.work_counter, 1);
+            s_it.item = item;
+            if (item < nitems) {
+                int lo = 0, hi = n;  // largest X with itemstart[X] <= item
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (p.itemstart[mid] <= item)
+                        lo = mid;
+                    else
+                        hi = mid;
+                }
+                const int dd = p.deg[lo];
+                const u64 nc = binom64(dd, l);
+                const u64 chx = p.chunk[lo];
+                const u64 r0 = (u64)(item - p.itemstart[lo]) * chx;
+                s_it.X = lo;
+                s_it.d = dd;
+                s_it.row0 = p.rowptr[lo];
+                s_it.R0 = r0;
+                s_it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
+            }
         }
-        const int X = lo;
-        const int d = p.deg[X];
-        const int row0 = p.rowptr[X];
+        __syncthreads();
+        if (s_it.item >= nitems) break;
+        const int X = s_it.X;
+        const int d = s_it.d;
+        const int row0 = s_it.row0;
         const int *a_g = p.adj + row0;
-        const u64 ncomb = binom64(d, l);
-        const u64 ch = p.chunk[X];
-        const u64 R0 = (u64)(item - p.itemstart[X]) * ch;
-        const u64 R1 = (R0 + ch < ncomb) ? R0 + ch : ncomb;
+        const u64 R0 = s_it.R0;
+        const u64 R1 = s_it.R1;
         const int tX = use_time ? p.time_index[X] : 0;
 
         // ---- shared memory carve-up -------------------------------------------------------
@@ -86,7 +100,9 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         const size_t csub_bytes = (size_t)d * dpad * 4;
         int nw;
         bool staged;
-        if (csub_bytes + 8 * perwarp <= avail) {
+        // staging costs d^2 gathers: only worth it when the item runs a few times as many tests
+        const bool worth_staging = (R1 - R0) * (u64)(d - l) >= 3 * (u64)d * (u64)d;
+        if (worth_staging && csub_bytes + 8 * perwarp <= avail) {
             staged = true;
             const size_t q = (avail - csub_bytes) / perwarp;
             nw = q < CI_NWARPS ? (int)q : CI_NWARPS;

@@ -72,7 +72,12 @@ __host__ __device__ inline u64 binom64(int n, int k)
     if (k > n - k) k = n - k;
     u64 c = 1;
     for (int i = 1; i <= k; i++) {
-        // c * (n - k + i) / i is always integral; widen the product
+        // c * (n - k + i) / i is always integral
+        if (c < ((u64)1 << 32) && n < (1 << 30)) {  // product fits in 64 bits: plain division
+            c = c * (u64)(n - k + i) / (u64)i;
+            continue;
+        }
+        // widen the product
         const unsigned __int128 t = (unsigned __int128)c * (unsigned)(n - k + i);
         const unsigned __int128 q = t / (unsigned)i;
         if (q >= (unsigned __int128)CUSK_SAT) return CUSK_SAT;
