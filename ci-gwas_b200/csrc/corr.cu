@@ -1,0 +1,313 @@
+// corr.cu -- host drivers of the correlation front end (replaces cu_marker_phen_corr_pearson and
+// cu_corr_pearson_npn, src/corr_host.cu:1023-1197, and the statistics pass of prep-bed).
+#include <cuda.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "corr.cuh"
+
+// corr_kernels.cu
+void launch_bed_counts(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int *counts);
+void launch_bed_stats(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, const int *counts,
+                      float *means, float *stds, int *modes);
+void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int parts, int MI,
+                   size_t Kp, unsigned char *ind);
+void launch_mxp(cudaStream_t st, const unsigned char *bed, const float *phen, int m, int n, int p, size_t col_bytes,
+                const float *mean, const float *stdv, float *out, int ldo, size_t out_stride_marker);
+void launch_pxp(cudaStream_t st, const float *phen, int n, int p, float *out_upper, float *Csq, int ldc, int m_off);
+void launch_pack_upper(cudaStream_t st, const float *Csq, int m, int ldc, float *upper);
+void launch_set_diag(cudaStream_t st, float *Csq, int nvar, int ldc);
+// corr_gram.cu
+int launch_gram(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMap &map_b, const GramParams &p, int grid);
+int gram_make_maps(const unsigned char *ind, size_t rows, size_t Kp, CUtensorMap *map_a, CUtensorMap *map_b);
+cusk_ctx *cusk_default_ctx();
+
+namespace {
+
+__global__ void scatter_mxp_kernel(const float *__restrict__ mxp, int m, int p, float *__restrict__ Csq, int ldc)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= m * p) return;
+    const int i = idx / p, t = idx - i * p;
+    const float r = mxp[idx];
+    Csq[(size_t)i * ldc + (m + t)] = r;
+    Csq[(size_t)(m + t) * ldc + i] = r;
+}
+
+struct EvTimer {
+    cudaEvent_t a, b;
+    cudaStream_t st;
+    bool used = false;
+    EvTimer(cusk_ctx *ctx, int slot) : a(ctx->ev[2 * slot]), b(ctx->ev[2 * slot + 1]), st(ctx->stream) {}
+    void start()
+    {
+        cudaEventRecord(a, st);
+        used = true;
+    }
+    void stop() { cudaEventRecord(b, st); }
+    float ms()
+    {
+        if (!used) return 0.f;
+        float t = 0.f;
+        cudaEventSynchronize(b);
+        cudaEventElapsedTime(&t, a, b);
+        return t;
+    }
+};
+
+// Device-resident block: everything below works on device pointers; scratch from ctx->arena.
+// d_Csq may be nullptr when only mxp is wanted (the level-0 screen of cusk, cli.cpp:548-576).
+int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_phen, size_t m, size_t n, size_t p,
+                      const float *d_mean, const float *d_std, int mode, float *d_Csq, float *d_mxp_out,
+                      float *d_pxp_out, long long *d_tables, bool want_mxm, cusk_corr_stats *st)
+{
+    cudaStream_t s = ctx->stream;
+    const size_t col_bytes = (n + 3) / 4;
+    const int nvar = (int)(m + p);
+    EvTimer t_counts(ctx, 0), t_decode(ctx, 1), t_gram(ctx, 2), t_mxp(ctx, 3), t_pxp(ctx, 4);
+    if (m > 0x3fffffff || n > 0x7fffffff || p > 65535) {
+        cusk_set_error("corr: dimensions out of range");
+        return CUSK_E_ARG;
+    }
+    float *d_mxp = d_mxp_out;
+    if (p > 0 && !d_mxp) {
+        d_mxp = (float *)arena_take(ctx, sizeof(float) * m * p);
+        if (!d_mxp) return CUSK_E_CUDA;
+    }
+    // ---- marker x trait and trait x trait (CUDA cores, FP64 accumulation) --------------------------
+    if (p > 0 && m > 0) {
+        t_mxp.start();
+        launch_mxp(s, d_bed, d_phen, (int)m, (int)n, (int)p, col_bytes, d_mean, d_std, d_mxp, 1, p);
+        if (d_Csq) scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
+        t_mxp.stop();
+    }
+    if (p > 1 && (d_pxp_out || d_Csq)) {
+        t_pxp.start();
+        launch_pxp(s, d_phen, (int)n, (int)p, d_pxp_out, d_Csq, nvar, (int)m);
+        t_pxp.stop();
+    }
+    CUSK_CUDA(cudaGetLastError());
+    if (st) st->bed_bytes = (int64_t)(m * col_bytes);
+    // ---- marker x marker: indicator Gram on the tensor cores ----------------------------------------
+    if (want_mxm && m > 1) {
+        int *d_counts = (int *)arena_take(ctx, sizeof(int) * 4 * m);
+        if (!d_counts) return CUSK_E_CUDA;
+        t_counts.start();
+        launch_bed_counts(s, d_bed, (int)m, (int)n, col_bytes, d_counts);
+        t_counts.stop();
+        std::vector<int> h_counts(4 * m);
+        CUSK_CUDA(cudaMemcpyAsync(h_counts.data(), d_counts, sizeof(int) * 4 * m, cudaMemcpyDeviceToHost, s));
+        CUSK_CUDA(cudaStreamSynchronize(s));
+        bool any_missing = false;
+        for (size_t i = 0; i < m; i++) any_missing |= h_counts[4 * i + 3] != 0;
+        const int parts = any_missing ? 3 : 2;
+        const int MI = 128 / parts;
+        const size_t groups = (m + MI - 1) / MI;
+        const size_t rows = ((groups * 128 + 255) / 256) * 256;
+        const size_t Kp = ((n + 127) / 128) * 128;
+        unsigned char *d_ind = (unsigned char *)arena_take(ctx, rows * Kp);
+        if (!d_ind) return CUSK_E_CUDA;
+        t_decode.start();
+        // padding rows of every group and the tail of K must be zero
+        CUSK_CUDA(cudaMemsetAsync(d_ind, 0, rows * Kp, s));
+        launch_decode(s, d_bed, (int)m, (int)n, col_bytes, parts, MI, Kp, d_ind);
+        t_decode.stop();
+        // upper-triangle tile list: A block tm = group tm; B block tn = groups 2tn, 2tn+1
+        std::vector<int2> tiles;
+        const int n_tm = (int)groups, n_tn = (int)((groups + 1) / 2);
+        for (int tn = n_tn - 1; tn >= 0; tn--)  // long rows of the triangle first
+            for (int tm = 0; tm < n_tm; tm++)
+                if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m) tiles.push_back({tm, tn});
+        int2 *d_tiles = (int2 *)arena_take(ctx, sizeof(int2) * std::max<size_t>(tiles.size(), 1));
+        if (!d_tiles) return CUSK_E_CUDA;
+        CUSK_CUDA(cudaMemcpyAsync(d_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s));
+        float *d_out = d_Csq;
+        int ldc = nvar;
+        CUtensorMap map_a, map_b;
+        int rc = gram_make_maps(d_ind, rows, Kp, &map_a, &map_b);
+        if (rc) return rc;
+        GramParams gp = {};
+        gp.parts = parts;
+        gp.MI = MI;
+        gp.m = (int)m;
+        gp.n_samples = (int)n;
+        gp.num_k = (int)(Kp / 128);
+        gp.ntiles = (int)tiles.size();
+        gp.tiles = d_tiles;
+        gp.counts = d_counts;
+        gp.C = d_out;
+        gp.ldc = ldc;
+        gp.mode = mode;
+        gp.mean = d_mean;
+        gp.stdv = d_std;
+        gp.tables = d_tables;
+        t_gram.start();
+        rc = launch_gram(s, map_a, map_b, gp, std::min<int>(ctx->sm_count, (int)tiles.size()));
+        if (rc) return rc;
+        t_gram.stop();
+        CUSK_CUDA(cudaGetLastError());
+        CUSK_CUDA(cudaStreamSynchronize(s));  // the host tile list must outlive the copy
+        if (st) {
+            st->parts = parts;
+            st->gram_tiles = (int)tiles.size();
+            st->gram_int8_ops = (int64_t)tiles.size() * 2 * 128 * 256 * (int64_t)Kp;
+        }
+    }
+    if (d_Csq) launch_set_diag(s, d_Csq, nvar, nvar);
+    CUSK_CUDA(cudaGetLastError());
+    if (st) {
+        CUSK_CUDA(cudaStreamSynchronize(s));
+        st->counts_ms = t_counts.ms();
+        st->decode_ms = t_decode.ms();
+        st->gram_ms = t_gram.ms();
+        st->mxp_ms = t_mxp.ms();
+        st->pxp_ms = t_pxp.ms();
+    }
+    return CUSK_OK;
+}
+
+}  // namespace
+
+extern "C" int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_phen, size_t m, size_t n,
+                                   size_t p, const float *d_mean, const float *d_std, int mode, float *d_Csq,
+                                   cusk_corr_stats *stats)
+{
+    if (!ctx || !d_bed || !d_mean || !d_std || !d_Csq || (p > 0 && !d_phen)) {
+        cusk_set_error("cusk_corr_block_dev: NULL argument");
+        return CUSK_E_ARG;
+    }
+    CUSK_CUDA(cudaSetDevice(ctx->device));
+    arena_reset(ctx);
+    if (stats) memset(stats, 0, sizeof(*stats));
+    cudaEvent_t e0 = ctx->ev[20], e1 = ctx->ev[21];
+    cudaEventRecord(e0, ctx->stream);
+    int rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, mode, d_Csq, nullptr, nullptr, nullptr, true,
+                               stats);
+    if (rc) return rc;
+    cudaEventRecord(e1, ctx->stream);
+    CUSK_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (stats) cudaEventElapsedTime(&stats->total_ms, e0, e1);
+    return CUSK_OK;
+}
+
+extern "C" int cusk_corr_block(cusk_ctx *ctx, const unsigned char *bed, const float *phen, size_t m, size_t n, size_t p,
+                               const float *mean, const float *stdv, int mode, float *mxm, float *mxp, float *pxp,
+                               int64_t *tables, cusk_corr_stats *stats)
+{
+    if (!ctx || !bed || !mean || !stdv || (p > 0 && !phen)) {
+        cusk_set_error("cusk_corr_block: NULL argument");
+        return CUSK_E_ARG;
+    }
+    CUSK_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    arena_reset(ctx);
+    arena_reset(ctx->io);
+    cusk_corr_stats local;
+    cusk_corr_stats *st = stats ? stats : &local;
+    memset(st, 0, sizeof(*st));
+    const size_t col_bytes = (n + 3) / 4;
+    const size_t npairs = m * (m - (m > 0)) / 2, ppairs = p * (p - (p > 0)) / 2;
+    const int nvar = (int)(m + p);
+    const bool want_mxm = mxm != nullptr || tables != nullptr;
+    unsigned char *d_bed = (unsigned char *)arena_take(ctx->io, m * col_bytes);
+    float *d_phen = p ? (float *)arena_take(ctx->io, sizeof(float) * p * n) : nullptr;
+    float *d_mean = (float *)arena_take(ctx->io, sizeof(float) * m);
+    float *d_std = (float *)arena_take(ctx->io, sizeof(float) * m);
+    float *d_Csq = want_mxm ? (float *)arena_take(ctx->io, sizeof(float) * (size_t)nvar * nvar) : nullptr;
+    float *d_mxp = (p && mxp) ? (float *)arena_take(ctx->io, sizeof(float) * m * p) : nullptr;
+    float *d_pxp = (pxp && ppairs) ? (float *)arena_take(ctx->io, sizeof(float) * ppairs) : nullptr;
+    float *d_upper = (mxm && npairs) ? (float *)arena_take(ctx->io, sizeof(float) * npairs) : nullptr;
+    long long *d_tables = (tables && npairs) ? (long long *)arena_take(ctx->io, sizeof(long long) * 9 * npairs) : nullptr;
+    if (!d_bed || !d_mean || !d_std || (p && !d_phen) || (want_mxm && !d_Csq)) return CUSK_E_CUDA;
+    cudaEvent_t e0 = ctx->ev[20], e1 = ctx->ev[21], e2 = ctx->ev[22], e3 = ctx->ev[23];
+    cudaEventRecord(e0, s);
+    CUSK_CUDA(cudaMemcpyAsync(d_bed, bed, m * col_bytes, cudaMemcpyHostToDevice, s));
+    if (p) CUSK_CUDA(cudaMemcpyAsync(d_phen, phen, sizeof(float) * p * n, cudaMemcpyHostToDevice, s));
+    CUSK_CUDA(cudaMemcpyAsync(d_mean, mean, sizeof(float) * m, cudaMemcpyHostToDevice, s));
+    CUSK_CUDA(cudaMemcpyAsync(d_std, stdv, sizeof(float) * m, cudaMemcpyHostToDevice, s));
+    cudaEventRecord(e1, s);
+    int rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, mode, d_Csq, d_mxp, d_pxp, d_tables, want_mxm,
+                               st);
+    if (rc) return rc;
+    cudaEventRecord(e2, s);
+    if (d_upper) {
+        launch_pack_upper(s, d_Csq, (int)m, nvar, d_upper);
+        CUSK_CUDA(cudaMemcpyAsync(mxm, d_upper, sizeof(float) * npairs, cudaMemcpyDeviceToHost, s));
+    }
+    if (d_mxp) CUSK_CUDA(cudaMemcpyAsync(mxp, d_mxp, sizeof(float) * m * p, cudaMemcpyDeviceToHost, s));
+    if (d_pxp) CUSK_CUDA(cudaMemcpyAsync(pxp, d_pxp, sizeof(float) * ppairs, cudaMemcpyDeviceToHost, s));
+    if (d_tables)
+        CUSK_CUDA(cudaMemcpyAsync(tables, d_tables, sizeof(long long) * 9 * npairs, cudaMemcpyDeviceToHost, s));
+    cudaEventRecord(e3, s);
+    CUSK_CUDA(cudaStreamSynchronize(s));
+    cudaEventElapsedTime(&st->h2d_ms, e0, e1);
+    cudaEventElapsedTime(&st->d2h_ms, e2, e3);
+    cudaEventElapsedTime(&st->total_ms, e0, e3);
+    return CUSK_OK;
+}
+
+extern "C" int cusk_marker_phen_corr(cusk_ctx *ctx, const unsigned char *bed, const float *phen, size_t m, size_t n,
+                                     size_t p, const float *mean, const float *stdv, float *mxp,
+                                     cusk_corr_stats *stats)
+{
+    return cusk_corr_block(ctx, bed, phen, m, n, p, mean, stdv, 0, nullptr, mxp, nullptr, nullptr, stats);
+}
+
+extern "C" int cusk_bed_marker_stats(cusk_ctx *ctx, const unsigned char *bed, size_t m, size_t n, float *means,
+                                     float *stds, int *modes, int64_t *counts4)
+{
+    if (!ctx || !bed || !means || !stds) {
+        cusk_set_error("cusk_bed_marker_stats: NULL argument");
+        return CUSK_E_ARG;
+    }
+    CUSK_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    arena_reset(ctx->io);
+    const size_t col_bytes = (n + 3) / 4;
+    unsigned char *d_bed = (unsigned char *)arena_take(ctx->io, m * col_bytes);
+    int *d_counts = (int *)arena_take(ctx->io, sizeof(int) * 4 * m);
+    float *d_means = (float *)arena_take(ctx->io, sizeof(float) * m);
+    float *d_stds = (float *)arena_take(ctx->io, sizeof(float) * m);
+    int *d_modes = (int *)arena_take(ctx->io, sizeof(int) * m);
+    if (!d_bed || !d_counts || !d_means || !d_stds || !d_modes) return CUSK_E_CUDA;
+    CUSK_CUDA(cudaMemcpyAsync(d_bed, bed, m * col_bytes, cudaMemcpyHostToDevice, s));
+    launch_bed_counts(s, d_bed, (int)m, (int)n, col_bytes, d_counts);
+    launch_bed_stats(s, d_bed, (int)m, (int)n, col_bytes, d_counts, d_means, d_stds, d_modes);
+    CUSK_CUDA(cudaGetLastError());
+    std::vector<int> hc(4 * m), hm(m);
+    CUSK_CUDA(cudaMemcpyAsync(means, d_means, sizeof(float) * m, cudaMemcpyDeviceToHost, s));
+    CUSK_CUDA(cudaMemcpyAsync(stds, d_stds, sizeof(float) * m, cudaMemcpyDeviceToHost, s));
+    CUSK_CUDA(cudaMemcpyAsync(hm.data(), d_modes, sizeof(int) * m, cudaMemcpyDeviceToHost, s));
+    CUSK_CUDA(cudaMemcpyAsync(hc.data(), d_counts, sizeof(int) * 4 * m, cudaMemcpyDeviceToHost, s));
+    CUSK_CUDA(cudaStreamSynchronize(s));
+    if (modes) std::copy(hm.begin(), hm.end(), modes);
+    if (counts4)
+        for (size_t i = 0; i < 4 * m; i++) counts4[i] = hc[i];
+    return CUSK_OK;
+}
+
+// ---- the reference's own names (src/corr_host.cu:1023, :1094) ---------------------------------------
+extern "C" void cu_marker_phen_corr_pearson(const unsigned char *marker_vals, const float *phen_vals,
+                                            const size_t num_markers, const size_t num_individuals,
+                                            const size_t num_phen, const float *marker_mean, const float *marker_std,
+                                            float *marker_phen_corrs)
+{
+    if (cusk_marker_phen_corr(cusk_default_ctx(), marker_vals, phen_vals, num_markers, num_individuals, num_phen,
+                              marker_mean, marker_std, marker_phen_corrs, nullptr) != CUSK_OK) {
+        fprintf(stderr, "cusk_b200 cu_marker_phen_corr_pearson: %s\n", cusk_last_error());
+        exit(EXIT_FAILURE);
+    }
+}
+
+extern "C" void cu_corr_pearson_npn(const unsigned char *marker_vals, const float *phen_vals, const size_t num_markers,
+                                    const size_t num_individuals, const size_t num_phen, const float *marker_mean,
+                                    const float *marker_std, float *marker_corrs, float *marker_phen_corrs,
+                                    float *phen_corrs)
+{
+    if (cusk_corr_block(cusk_default_ctx(), marker_vals, phen_vals, num_markers, num_individuals, num_phen, marker_mean,
+                        marker_std, 0, marker_corrs, marker_phen_corrs, phen_corrs, nullptr, nullptr) != CUSK_OK) {
+        fprintf(stderr, "cusk_b200 cu_corr_pearson_npn: %s\n", cusk_last_error());
+        exit(EXIT_FAILURE);
+    }
+}

@@ -1,0 +1,52 @@
+// corr.cuh -- shared definitions of the correlation front end (BED decode, marker statistics,
+// indicator Gram on tcgen05, marker x trait and trait x trait correlations).
+#pragma once
+#include "common.cuh"
+
+// PLINK BED 2-bit codes (include/mps/bed_lut_gpu.h:3,1030): 00 -> genotype 2, 01 -> missing,
+// 10 -> genotype 1, 11 -> genotype 0; sample j of a marker sits in bits 2(j&3).. of byte j>>2.
+
+struct GramParams {
+    int parts;        // indicator rows per marker: 2 (no missing call in the block) or 3
+    int MI;           // markers per 128-row group: 64 (parts 2) or 42 (parts 3)
+    int m;            // markers
+    int n_samples;
+    int num_k;        // K stages of 128 bytes
+    int ntiles;
+    const int2 *tiles;   // (tm, tn): A rows [128 tm, +128), B rows [256 tn, +256)
+    const int *counts;   // [m][4]: n0, n1, n2, nmissing
+    float *C;            // dense output, row-major, leading dimension ldc; both triangles written
+    int ldc;
+    int mode;            // 0: sin(pi/2 tau_b) (cusk), 1: Pearson with the given means / stds
+    const float *mean, *stdv;
+    long long *tables;   // optional [m*(m-1)/2][9] exact contingency tables (tests), or nullptr
+};
+
+// row of (marker i, part a) in the padded indicator matrix
+__host__ __device__ inline size_t ind_row(int i, int a, int parts, int MI)
+{
+    return (size_t)(i / MI) * 128 + (size_t)(i % MI) * parts + a;
+}
+
+// src/corr_kernels.cu:548-563: Kendall tau_b from the 3x3 table s[3a+b], then sin(pi/2 tau).
+__host__ __device__ inline double npn_from_table(const double *s)
+{
+    const double p = s[0] * (s[4] + s[5] + s[7] + s[8]) + s[1] * (s[5] + s[8]) + s[3] * (s[7] + s[8]) + s[4] * s[8];
+    const double q = s[1] * (s[3] + s[6]) + s[2] * (s[3] + s[4] + s[6] + s[7]) + s[4] * s[6] + s[5] * (s[6] + s[7]);
+    const double t = s[0] * (s[1] + s[2]) + s[1] * s[2] + s[3] * (s[4] + s[5]) + s[4] * s[5] + s[6] * (s[7] + s[8]) +
+                     s[7] * s[8];
+    const double u = s[0] * (s[3] + s[6]) + s[1] * (s[4] + s[7]) + s[2] * (s[5] + s[8]) + s[3] * s[6] + s[4] * s[7] +
+                     s[5] * s[8];
+    const double kendall = (p - q) / sqrt((p + q + t) * (p + q + u));
+    return sin(1.57079632679489661923 * kendall);
+}
+
+// src/corr_kernels.cu:346-403 (bed_marker_corr_pearson): (sum v a b / sum v - mu_a mu_b) / (sd_a sd_b)
+__host__ __device__ inline double pearson_from_table(const double *s, double mu_a, double mu_b, double sd_a,
+                                                     double sd_b)
+{
+    const double sab = s[4] + 2.0 * (s[5] + s[7]) + 4.0 * s[8];
+    double nv = 0;
+    for (int i = 0; i < 9; i++) nv += s[i];
+    return (sab / nv - mu_a * mu_b) / (sd_a * sd_b);
+}

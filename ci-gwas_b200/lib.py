@@ -52,6 +52,15 @@ class Stats(C.Structure):
         )
 
 
+class CorrStats(C.Structure):
+    _fields_ = [(k, C.c_float) for k in ("h2d_ms", "counts_ms", "decode_ms", "gram_ms", "mxp_ms", "pxp_ms",
+                                         "d2h_ms", "total_ms")] + [
+        ("parts", C.c_int32), ("gram_tiles", C.c_int32), ("gram_int8_ops", C.c_int64), ("bed_bytes", C.c_int64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
 SEPSET_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("level", "<i4"), ("pmax", "<f4"), ("s", "<i4", (ML,))])
 
 _LIB = None
@@ -105,6 +114,15 @@ def load_library():
                                              C.POINTER(Stats)]
     lib.cusk_skeleton_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, c_float_p, C.c_int, c_int_p,
                                       C.c_void_p, C.c_void_p, C.c_int64, c_i64_p, C.POINTER(Stats)]
+    lib.cusk_bed_marker_stats.argtypes = [C.c_void_p, c_ubyte_p, C.c_size_t, C.c_size_t, c_float_p, c_float_p,
+                                          c_int_p, c_i64_p]
+    lib.cusk_corr_block.argtypes = [C.c_void_p, c_ubyte_p, c_float_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                    c_float_p, c_float_p, C.c_int, c_float_p, c_float_p, c_float_p, c_i64_p,
+                                    C.POINTER(CorrStats)]
+    lib.cusk_marker_phen_corr.argtypes = [C.c_void_p, c_ubyte_p, c_float_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                          c_float_p, c_float_p, c_float_p, C.POINTER(CorrStats)]
+    lib.cusk_corr_block_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                        C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(CorrStats)]
     _LIB = lib
     return lib
 
@@ -192,6 +210,42 @@ class Context:
                                                   _p(N, c_float_p), C.c_float(th), int(maxlevel),
                                                   _p(ti, c_int_p), C.byref(l), C.byref(st)))
         return dict(G=Gw, l=l.value, stats=st.as_dict())
+
+    # -- correlation front end ---------------------------------------------------------------------
+    def bed_marker_stats(self, bed, m, n):
+        """prep-bed statistics (prep.cpp:15-77) -> means, stds, modes, counts[m,4]"""
+        bed = np.ascontiguousarray(bed, np.uint8).reshape(-1)
+        means = np.zeros(m, np.float32)
+        stds = np.zeros(m, np.float32)
+        modes = np.zeros(m, np.int32)
+        counts = np.zeros((m, 4), np.int64)
+        self._check(self.lib.cusk_bed_marker_stats(self.h, _p(bed, c_ubyte_p), m, n, _p(means, c_float_p),
+                                                   _p(stds, c_float_p), _p(modes, c_int_p), _p(counts, c_i64_p)))
+        return means, stds, modes, counts
+
+    def corr_block(self, bed, phen, m, n, p, mean, std, mode=0, want_mxm=True, want_tables=False):
+        """cu_corr_pearson_npn (corr_host.cu:1094) -> dict(mxm, mxp, pxp[, tables], stats)"""
+        bed = np.ascontiguousarray(bed, np.uint8).reshape(-1)
+        phen = np.ascontiguousarray(phen, np.float32).reshape(-1) if p else None
+        mean = np.ascontiguousarray(mean, np.float32)
+        std = np.ascontiguousarray(std, np.float32)
+        npairs = m * (m - 1) // 2
+        mxm = np.zeros(npairs, np.float32) if want_mxm else None
+        mxp = np.zeros(m * p, np.float32) if p else None
+        pxp = np.zeros(p * (p - 1) // 2, np.float32) if p > 1 else None
+        tables = np.zeros((npairs, 9), np.int64) if want_tables else None
+        st = CorrStats()
+        self._check(self.lib.cusk_corr_block(self.h, _p(bed, c_ubyte_p), _p(phen, c_float_p), m, n, p,
+                                             _p(mean, c_float_p), _p(std, c_float_p), int(mode), _p(mxm, c_float_p),
+                                             _p(mxp, c_float_p), _p(pxp, c_float_p), _p(tables, c_i64_p),
+                                             C.byref(st)))
+        return dict(mxm=mxm, mxp=mxp, pxp=pxp, tables=tables, stats=st.as_dict())
+
+    def corr_block_dev(self, d_bed, d_phen, m, n, p, d_mean, d_std, d_Csq, mode=0):
+        st = CorrStats()
+        self._check(self.lib.cusk_corr_block_dev(self.h, d_bed, d_phen, m, n, p, d_mean, d_std, int(mode), d_Csq,
+                                                 C.byref(st)))
+        return st.as_dict()
 
     # -- device-resident variants (pointers are ints, e.g. torch.Tensor.data_ptr()) -----------------
     def row_words(self, n):

@@ -108,7 +108,56 @@ int cusk_skeleton_dev(cusk_ctx *ctx, const float *dC, int n, uint32_t *dG_bits, 
                       int maxlevel, int *l_out, float *d_pMax, cusk_sepset *sep, int64_t sep_cap,
                       int64_t *sep_n, cusk_stats *stats);
 
+/* ---- correlation front end ------------------------------------------------------------------ */
+/* bed: packed PLINK SNP-major genotype columns WITHOUT the 3 magic bytes, m * ceil(n/4) bytes
+ * (what read_block_from_bed returns, src/io.cpp:238); phen: float [p][n] column-major per trait,
+ * NaN = missing (src/phen.cpp:27-74); mean/std: per-marker values as read from .means/.stds. */
+typedef struct cusk_corr_stats {
+    float h2d_ms, counts_ms, decode_ms, gram_ms, mxp_ms, pxp_ms, d2h_ms, total_ms;
+    int32_t parts;        /* indicator rows per marker in the tensor-core Gram: 2 or 3 */
+    int32_t gram_tiles;   /* 128 x 256 indicator-row tiles computed (upper triangle) */
+    int64_t gram_int8_ops;/* 2 * 128 * 256 * K_padded per tile, summed */
+    int64_t bed_bytes;    /* packed genotype bytes of the block */
+} cusk_corr_stats;
+
+/* prep-bed statistics (replaces compute_bed_col_stats_no_impute, src/prep.cpp:15-77): means, stds
+ * (float, population, missing excluded, the reference's sequential float accumulation order),
+ * modes, and exact genotype counts counts4[m][4] = n0, n1, n2, nmissing (may be NULL). */
+int cusk_bed_marker_stats(cusk_ctx *ctx, const unsigned char *bed, size_t m, size_t n, float *means,
+                          float *stds, int *modes, int64_t *counts4);
+
+/* marker x trait Pearson (replaces cu_marker_phen_corr_pearson, src/corr_host.cu:1023). mxp[m*p] */
+int cusk_marker_phen_corr(cusk_ctx *ctx, const unsigned char *bed, const float *phen, size_t m, size_t n,
+                          size_t p, const float *mean, const float *std, float *mxp,
+                          cusk_corr_stats *stats);
+
+/* all three correlation sets of a block (replaces cu_corr_pearson_npn, src/corr_host.cu:1094):
+ * mxm[m(m-1)/2] upper triangle row-major, sin(pi/2 tau_b) from the 3x3 genotype table (mode 0) or
+ * Pearson with the given means/stds (mode 1; bed_marker_corr_pearson, src/corr_kernels.cu:346);
+ * mxp[m*p]; pxp[p(p-1)/2].  Any output may be NULL.  tables (may be NULL): the exact contingency
+ * tables [m(m-1)/2][9] the correlations were computed from (integer dot products; for tests). */
+int cusk_corr_block(cusk_ctx *ctx, const unsigned char *bed, const float *phen, size_t m, size_t n,
+                    size_t p, const float *mean, const float *std, int mode, float *mxm, float *mxp,
+                    float *pxp, int64_t *tables, cusk_corr_stats *stats);
+
+/* Device-resident variant: d_bed, d_phen, d_mean, d_std are device pointers; writes the dense
+ * symmetric (m+p) x (m+p) correlation matrix d_Csq (unit diagonal, markers first then traits --
+ * the layout cli.cpp:597-649 assembles on the host) that cusk_skeleton_dev consumes directly. */
+int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_phen, size_t m,
+                        size_t n, size_t p, const float *d_mean, const float *d_std, int mode,
+                        float *d_Csq, cusk_corr_stats *stats);
+
 /* ---- drop-in signatures of the reference -------------------------------------------------- */
+/* include/mps/corr_host.h: cu_marker_phen_corr_pearson / cu_corr_pearson_npn (C++ linkage in the
+ * reference; exported here with C linkage and the same argument order) */
+void cu_marker_phen_corr_pearson(const unsigned char *marker_vals, const float *phen_vals,
+                                 const size_t num_markers, const size_t num_individuals,
+                                 const size_t num_phen, const float *marker_mean,
+                                 const float *marker_std, float *marker_phen_corrs);
+void cu_corr_pearson_npn(const unsigned char *marker_vals, const float *phen_vals,
+                         const size_t num_markers, const size_t num_individuals, const size_t num_phen,
+                         const float *marker_mean, const float *marker_std, float *marker_corrs,
+                         float *marker_phen_corrs, float *phen_corrs);
 /* include/mps/cuPC-S.h:192-194 */
 void Skeleton(float *C, int *P, int *G, float *Th, int *l, const int *maxlevel, float *pMax,
               int *SepSet);
