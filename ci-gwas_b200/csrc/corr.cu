@@ -13,8 +13,8 @@ void launch_bed_stats(cudaStream_t st, const unsigned char *bed, int m, int n, s
                       float *means, float *stds, int *modes);
 void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int parts, int MI,
                    size_t Kp, unsigned char *ind);
-void launch_mxp(cudaStream_t st, const unsigned char *bed, const float *phen, int m, int n, int p, size_t col_bytes,
-                const float *mean, const float *stdv, float *out, int ldo, size_t out_stride_marker);
+int launch_mxp(cudaStream_t st, const unsigned char *bed, const float *phen, int m, int n, int p, size_t col_bytes,
+               const float *mean, const float *stdv, float *out, bool any_missing, double *d_Ty, int *d_cnty);
 void launch_pxp(cudaStream_t st, const float *phen, int n, int p, float *out_upper, float *Csq, int ldc, int m_off);
 void launch_pack_upper(cudaStream_t st, const float *Csq, int m, int ldc, float *upper);
 void launch_set_diag(cudaStream_t st, float *Csq, int nvar, int ldc);
@@ -75,10 +75,29 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         d_mxp = (float *)arena_take(ctx, sizeof(float) * m * p);
         if (!d_mxp) return CUSK_E_CUDA;
     }
-    // ---- marker x trait and trait x trait (CUDA cores, FP64 accumulation) --------------------------
+    // ---- exact genotype counts (also tell whether the block has any missing call) ------------------
+    bool any_missing = false;
+    int *d_counts = nullptr;
+    if (m > 0) {
+        d_counts = (int *)arena_take(ctx, sizeof(int) * 4 * m);
+        if (!d_counts) return CUSK_E_CUDA;
+        t_counts.start();
+        launch_bed_counts(s, d_bed, (int)m, (int)n, col_bytes, d_counts);
+        t_counts.stop();
+        std::vector<int> h_counts(4 * m);
+        CUSK_CUDA(cudaMemcpyAsync(h_counts.data(), d_counts, sizeof(int) * 4 * m, cudaMemcpyDeviceToHost, s));
+        CUSK_CUDA(cudaStreamSynchronize(s));
+        for (size_t i = 0; i < m; i++) any_missing |= h_counts[4 * i + 3] != 0;
+    }
+    // ---- marker x trait and trait x trait (CUDA cores) -------------------------------------------------
     if (p > 0 && m > 0) {
+        double *d_Ty = (double *)arena_take(ctx, sizeof(double) * p);
+        int *d_cnty = (int *)arena_take(ctx, sizeof(int) * p);
+        if (!d_Ty || !d_cnty) return CUSK_E_CUDA;
         t_mxp.start();
-        launch_mxp(s, d_bed, d_phen, (int)m, (int)n, (int)p, col_bytes, d_mean, d_std, d_mxp, 1, p);
+        int rc = launch_mxp(s, d_bed, d_phen, (int)m, (int)n, (int)p, col_bytes, d_mean, d_std, d_mxp, any_missing, d_Ty,
+                            d_cnty);
+        if (rc) return rc;
         if (d_Csq) scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
         t_mxp.stop();
     }
@@ -91,16 +110,6 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
     if (st) st->bed_bytes = (int64_t)(m * col_bytes);
     // ---- marker x marker: indicator Gram on the tensor cores ----------------------------------------
     if (want_mxm && m > 1) {
-        int *d_counts = (int *)arena_take(ctx, sizeof(int) * 4 * m);
-        if (!d_counts) return CUSK_E_CUDA;
-        t_counts.start();
-        launch_bed_counts(s, d_bed, (int)m, (int)n, col_bytes, d_counts);
-        t_counts.stop();
-        std::vector<int> h_counts(4 * m);
-        CUSK_CUDA(cudaMemcpyAsync(h_counts.data(), d_counts, sizeof(int) * 4 * m, cudaMemcpyDeviceToHost, s));
-        CUSK_CUDA(cudaStreamSynchronize(s));
-        bool any_missing = false;
-        for (size_t i = 0; i < m; i++) any_missing |= h_counts[4 * i + 3] != 0;
         const int parts = any_missing ? 3 : 2;
         const int MI = 128 / parts;
         const size_t groups = (m + MI - 1) / MI;

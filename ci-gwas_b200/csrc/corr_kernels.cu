@@ -278,8 +278,10 @@ void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size
     dim3 grid((unsigned)((Kp / 16 + 255) / 256), m);
     decode_indicators_kernel<<<grid, 256, 0, st>>>(bed, m, n, col_bytes, parts, MI, Kp, ind);
 }
-void launch_mxp(cudaStream_t st, const unsigned char *bed, const float *phen, int m, int n, int p, size_t col_bytes,
-                const float *mean, const float *stdv, float *out, int ldo, size_t out_stride_marker)
+// first (simple) version, kept for A/B checks; the product path uses corr_mxp.cu
+void launch_mxp_simple(cudaStream_t st, const unsigned char *bed, const float *phen, int m, int n, int p,
+                       size_t col_bytes, const float *mean, const float *stdv, float *out, int ldo,
+                       size_t out_stride_marker)
 {
     constexpr int PT = 6;
     for (int t0 = 0; t0 < p; t0 += PT)
