@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         __syncthreads();
         if (tid == 0) {
             // one thread decodes the item (row lookup, C(d,l), rank range) for the whole CTA
-            const int item = atomicAdd(p.work_counter, 1);
+            const int item = p.shard_rank + p.shard_world * atomicAdd(p.work_counter, 1);
             s_it.item = item;
             if (item < nitems) {
                 int lo = 0, hi = n;  // largest X with itemstart[X] <= item

@@ -42,8 +42,23 @@ struct Arena {
     std::vector<ArenaBlock> blocks;
 };
 
+// Edge-sharded execution of ONE skeleton over several GPUs (cuskss-merged): set on the
+// context for the duration of a call.  The level-l work items are dealt round-robin to the ranks;
+// after the CI kernel of a level the ranks exchange what they removed.
+struct ShardLink {
+    int rank = 0, world = 1;
+    // gather `bytes` from every rank's d_send into d_recv[world][bytes] (ncclAllGather semantics)
+    int (*allgather)(void *user, const void *d_send, void *d_recv, size_t bytes, cudaStream_t st) = nullptr;
+    // element-wise minimum over ranks, in place (ncclAllReduce, ncclUint64, ncclMin)
+    int (*allreduce_min_u64)(void *user, void *d_buf, size_t count, cudaStream_t st) = nullptr;
+    void *user = nullptr;
+    double exchange_ms = 0.0;   // host-measured time spent in the exchanges of the last call
+    size_t exchange_bytes = 0;  // bytes received by this rank in the exchanges of the last call
+};
+
 struct cusk_ctx {
     int device = 0;
+    ShardLink *shard = nullptr;
     int sm_count = 148;
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;

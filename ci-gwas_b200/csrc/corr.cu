@@ -56,11 +56,15 @@ struct EvTimer {
     }
 };
 
+}  // namespace
+
 // Device-resident block: everything below works on device pointers; scratch from ctx->arena.
 // d_Csq may be nullptr when only mxp is wanted (the level-0 screen of cusk, cli.cpp:548-576).
+// mxp_ready: d_mxp_out already holds the block's marker x trait correlations (the screen computed
+// them; the reference runs that kernel twice, corr_host.cu:1070,1164).
 int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_phen, size_t m, size_t n, size_t p,
                       const float *d_mean, const float *d_std, int mode, float *d_Csq, float *d_mxp_out,
-                      float *d_pxp_out, long long *d_tables, bool want_mxm, cusk_corr_stats *st)
+                      float *d_pxp_out, long long *d_tables, bool want_mxm, cusk_corr_stats *st, bool mxp_ready)
 {
     cudaStream_t s = ctx->stream;
     const size_t col_bytes = (n + 3) / 4;
@@ -95,9 +99,11 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         int *d_cnty = (int *)arena_take(ctx, sizeof(int) * p);
         if (!d_Ty || !d_cnty) return CUSK_E_CUDA;
         t_mxp.start();
-        int rc = launch_mxp(s, d_bed, d_phen, (int)m, (int)n, (int)p, col_bytes, d_mean, d_std, d_mxp, any_missing, d_Ty,
-                            d_cnty);
-        if (rc) return rc;
+        if (!mxp_ready) {
+            int rc = launch_mxp(s, d_bed, d_phen, (int)m, (int)n, (int)p, col_bytes, d_mean, d_std, d_mxp, any_missing,
+                                d_Ty, d_cnty);
+            if (rc) return rc;
+        }
         if (d_Csq) scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
         t_mxp.stop();
     }
@@ -176,8 +182,6 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
     return CUSK_OK;
 }
 
-}  // namespace
-
 extern "C" int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_phen, size_t m, size_t n,
                                    size_t p, const float *d_mean, const float *d_std, int mode, float *d_Csq,
                                    cusk_corr_stats *stats)
@@ -192,7 +196,7 @@ extern "C" int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, co
     cudaEvent_t e0 = ctx->ev[20], e1 = ctx->ev[21];
     cudaEventRecord(e0, ctx->stream);
     int rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, mode, d_Csq, nullptr, nullptr, nullptr, true,
-                               stats);
+                               stats, false);
     if (rc) return rc;
     cudaEventRecord(e1, ctx->stream);
     CUSK_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -237,7 +241,7 @@ extern "C" int cusk_corr_block(cusk_ctx *ctx, const unsigned char *bed, const fl
     CUSK_CUDA(cudaMemcpyAsync(d_std, stdv, sizeof(float) * m, cudaMemcpyHostToDevice, s));
     cudaEventRecord(e1, s);
     int rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, mode, d_Csq, d_mxp, d_pxp, d_tables, want_mxm,
-                               st);
+                               st, false);
     if (rc) return rc;
     cudaEventRecord(e2, s);
     if (d_upper) {

@@ -16,3 +16,11 @@ int hetcor_engine(cusk_ctx *ctx, const float *dC, int n, uint32_t *dbits, const 
                   cusk_stats *stats);
 
 void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, int *G);
+
+// correlation front end on device pointers (corr.cu); scratch from ctx->arena (caller resets it)
+int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_phen, size_t m, size_t n, size_t p,
+                      const float *d_mean, const float *d_std, int mode, float *d_Csq, float *d_mxp_out,
+                      float *d_pxp_out, long long *d_tables, bool want_mxm, cusk_corr_stats *st, bool mxp_ready);
+void launch_bed_counts(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int *counts);
+void launch_bed_stats(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, const int *counts,
+                      float *means, float *stds, int *modes);

@@ -3,6 +3,7 @@
 // the whole call is one stream of asynchronous launches with a single mid-call synchronisation
 // (the directed edge count after level 0, which sizes the compacted adjacency).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <vector>
 
@@ -14,7 +15,7 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
 void launch_degree(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, const LevelCtl *prev);
 void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int *itemstart, u64 *chunk,
                  LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
-                 int *work_counter);
+                 int *work_counter, int world);
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
                     u64 *minkey, const LevelCtl *ctl);
 void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
@@ -25,6 +26,7 @@ void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, in
 void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits);
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
+void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits);
 
 extern "C" size_t cusk_row_words(int n) { return (size_t)(n + 31) / 32; }
 
@@ -97,6 +99,20 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         }
     }
 
+    // edge-sharded mode: every rank holds the whole problem and takes every world-th work item
+    ShardLink *sh = (ctx->shard && ctx->shard->world > 1) ? ctx->shard : nullptr;
+    uint32_t *d_gather = nullptr;
+    const size_t bit_words = (size_t)n * rw;
+    if (sh) {
+        sh->exchange_ms = 0.0;
+        sh->exchange_bytes = 0;
+        if (a.het) {
+            d_gather = (uint32_t *)arena_take(ctx, bit_words * 4 * (size_t)sh->world);
+            if (!d_gather) return CUSK_E_CUDA;
+        }
+    }
+    size_t nnz0 = 0;
+
     cudaEvent_t *ev = ctx->ev;
     CUSK_CUDA(cudaEventRecord(ev[0], st));
     // ---- level 0 -----------------------------------------------------------------------------
@@ -128,13 +144,14 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
         launch_degree(st, a.dbits, n, rw, d_deg, prev);
         launch_plan(st, d_deg, n, l, d_rowptr, d_itemstart, d_chunk, ctl, prev, a.het ? -1.0 : (double)a.Th[l],
-                    (double)a.th_het, n_uniform, d_work + l);
+                    (double)a.th_het, n_uniform, d_work + l, sh ? sh->world : 1);
         if (l == 1) {
             // the only mid-call synchronisation: directed edge count after level 0
             LevelCtl h;
             CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
             CUSK_CUDA(cudaStreamSynchronize(st));
             const size_t nnz = (size_t)h.nnz;
+            nnz0 = nnz;
             d_adj = (int *)arena_take(ctx, sizeof(int) * std::max<size_t>(nnz, 1));
             if (!d_adj) return CUSK_E_CUDA;
             if (!a.het) {
@@ -146,6 +163,13 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
                     if (!d_seps) return CUSK_E_CUDA;
                 }
             }
+        }
+        if (sh) {
+            // the ranks must agree on when to stop exchanging: read the level's verdict
+            int done = 0;
+            CUSK_CUDA(cudaMemcpyAsync(&done, &ctl->done, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CUSK_CUDA(cudaStreamSynchronize(st));
+            if (done) break;
         }
         launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl);
         CiParams p;
@@ -166,10 +190,33 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.minkey = d_minkey;
         p.th_het = (double)a.th_het;
         p.smem_bytes = smem_bytes;
+        p.shard_rank = sh ? sh->rank : 0;
+        p.shard_world = sh ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = launch_ci_level(st, a.het, p, grid);
         if (rc) return rc;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
+        if (sh) {
+            // exchange step of the level: removed edges (het: AND of the bitmaps; individual-level:
+            // minimum of the separating-set ranks), after which every rank holds the same graph again
+            CUSK_CUDA(cudaStreamSynchronize(st));
+            const auto t0 = std::chrono::steady_clock::now();
+            int xrc;
+            if (a.het) {
+                xrc = sh->allgather(sh->user, a.dbits, d_gather, bit_words * 4, st);
+                if (!xrc) launch_and_reduce(st, d_gather, sh->world, bit_words, a.dbits);
+                sh->exchange_bytes += bit_words * 4 * (size_t)sh->world;
+            } else {
+                xrc = sh->allreduce_min_u64(sh->user, d_minkey, nnz0, st);
+                sh->exchange_bytes += nnz0 * 8;
+            }
+            if (xrc) {
+                cusk_set_error("skeleton: exchange step of level %d failed (rc %d)", l, xrc);
+                return CUSK_E_CUDA;
+            }
+            CUSK_CUDA(cudaStreamSynchronize(st));
+            sh->exchange_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        }
         if (!a.het)
             launch_resolve(st, a.dC, n, rw, l, a.dbits, d_deg, d_rowptr, d_adj, d_minkey, a.d_pMax, d_seps,
                            d_sepcount, sep_cap, ctl);
@@ -178,7 +225,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     // final degrees (edge count) and pMax post-processing
     launch_degree(st, a.dbits, n, rw, d_deg, nullptr);
     launch_plan(st, d_deg, n, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1, nullptr, 1.0, 1.0,
-                n_uniform, d_work + CUSK_ML + 1);
+                n_uniform, d_work + CUSK_ML + 1, 1);
     if (!a.het && a.d_pMax) launch_pmax_final(st, a.dbits, n, rw, a.d_pMax);
     CUSK_CUDA(cudaEventRecord(ev[maxl + 1], st));
     CUSK_CUDA(cudaGetLastError());

@@ -38,4 +38,5 @@ struct CiParams {
     u64 *minkey;             // non-het
     double th_het;
     int smem_bytes;
+    int shard_rank, shard_world;  // this launch takes items rank, rank + world, ... (1 GPU: 0, 1)
 };

@@ -8,6 +8,8 @@
 //   rowptr int   [n+1]      CSR offsets of the compacted adjacency (the reference's GPrime)
 //   adj    int   [nnz]      sorted neighbour ids per row
 //   minkey u64   [nnz]      individual-level engine: lowest separating-set rank found per slot
+#include <algorithm>
+
 #include "skeleton.cuh"
 
 __device__ __forceinline__ double fisher_z(double rho)
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
                                                     int *__restrict__ rowptr, int *__restrict__ itemstart,
                                                     u64 *__restrict__ chunk, LevelCtl *ctl,
                                                     const LevelCtl *prev, double th_level, double th_het,
-                                                    float n_uniform, int *work_counter)
+                                                    float n_uniform, int *work_counter, int world)
 {
     __shared__ u64 s_warp[33];
     __shared__ int s_maxdeg;
@@ -169,7 +171,7 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         ctl->T2 = t * t;
         // aim at ~16 items per SM; small levels are cut finer (they are latency-bound: the
         // more warps share a hub row's conditioning sets the shorter the critical path)
-        u64 target = tot_tests / (148 * 16);
+        u64 target = tot_tests / ((u64)148 * 16 * (u64)world);
         if (target < 512) target = 512;
         s_target = target;
         *work_counter = 0;
@@ -417,10 +419,10 @@ void launch_degree(cudaStream_t st, const uint32_t *bits, int n, int rw, int *de
 
 void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int *itemstart, u64 *chunk,
                  LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
-                 int *work_counter)
+                 int *work_counter, int world)
 {
     plan_kernel<<<1, 1024, 0, st>>>(deg, n, l, rowptr, itemstart, chunk, ctl, prev, th_level, th_het,
-                                    n_uniform, work_counter);
+                                    n_uniform, work_counter, world);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
@@ -458,4 +460,20 @@ void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bi
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count)
 {
     ess_minmax_kernel<<<sm_count * 8, 256, 0, st>>>(N, n, mn, mx);
+}
+
+// edge-sharded mode: bits = AND over the ranks' bitmaps (each rank only ever clears bits)
+__global__ void __launch_bounds__(256) and_reduce_kernel(const uint32_t *__restrict__ gathered, int world,
+                                                         size_t words, uint32_t *__restrict__ bits)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (size_t)gridDim.x * blockDim.x) {
+        uint32_t v = 0xffffffffu;
+        for (int r = 0; r < world; r++) v &= gathered[(size_t)r * words + i];
+        bits[i] = v;
+    }
+}
+void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits)
+{
+    const int grid = (int)std::min<size_t>((words + 255) / 256, 148 * 8);
+    and_reduce_kernel<<<grid, 256, 0, st>>>(gathered, world, words, bits);
 }

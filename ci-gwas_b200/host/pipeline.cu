@@ -1,0 +1,553 @@
+// pipeline.cu -- orchestration of one `mps cusk` / `mps cuskss` / `mps prep` run on one context
+// (replaces cusk(), cuskss(), run_cusk(), reduced_gcs_cusk(), prep_bed_no_impute(): cusk/src/cli.cpp:29-87,
+// 194-346, 432-678; cusk/src/prep.cpp:157-201).  Differences from the reference's flow, none of which
+// change a written byte: correlations stay on the device and feed the skeleton directly; the
+// adjacency travels as a bitmap; separating sets come back sparse; the marker x trait screen is
+// computed once instead of twice.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <iostream>
+#include <unordered_map>
+
+#include "../csrc/engine.h"
+#include "host.hpp"
+
+namespace cuskhost {
+
+namespace {
+
+double now_s()
+{
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+#define HOST_CUDA(call)                                                                          \
+    do {                                                                                         \
+        cudaError_t e__ = (call);                                                                \
+        if (e__ != cudaSuccess) {                                                                \
+            cusk_set_error("%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return CUSK_E_CUDA;                                                                  \
+        }                                                                                        \
+    } while (0)
+
+// out[i][j] = in[sel[i]][sel[j]]
+__global__ void __launch_bounds__(256) gather_square_kernel(const float *__restrict__ in, int n,
+                                                            const int *__restrict__ sel, int ns,
+                                                            float *__restrict__ out)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= ns) return;
+    out[(size_t)i * ns + j] = in[(size_t)sel[i] * n + sel[j]];
+}
+
+std::vector<int> expand_bits(const std::vector<uint32_t> &bits, size_t nv, size_t rw, const std::vector<int> &sel)
+{
+    const size_t ns = sel.size();
+    std::vector<int> G(ns * ns);
+    for (size_t i = 0; i < ns; i++) {
+        const uint32_t *row = bits.data() + (size_t)sel[i] * rw;
+        for (size_t j = 0; j < ns; j++) G[i * ns + j] = (row[sel[j] >> 5] >> (sel[j] & 31)) & 1u;
+    }
+    (void)nv;
+    return G;
+}
+
+struct Pinned {  // page-locked staging buffer, falls back to pageable memory when pinning fails
+    void *p = nullptr;
+    bool pinned = false;
+    size_t bytes = 0;
+    ~Pinned() { release(); }
+    void release()
+    {
+        if (!p) return;
+        if (pinned)
+            cudaFreeHost(p);
+        else
+            free(p);
+        p = nullptr;
+    }
+    void *get(size_t n)
+    {
+        if (n <= bytes && p) return p;
+        release();
+        if (cudaMallocHost(&p, n) == cudaSuccess) {
+            pinned = true;
+        } else {
+            cudaGetLastError();
+            p = malloc(n);
+            pinned = false;
+        }
+        bytes = n;
+        return p;
+    }
+};
+
+}  // namespace
+
+// parent_set.cpp:8-53.  The reference runs one BFS per trait over marker nodes; the union over
+// traits of "within max_depth hops" equals one multi-source BFS from all traits.
+std::vector<int> subset_variables(const uint32_t *bits, size_t nv, size_t rw, size_t num_markers, int max_depth)
+{
+    std::vector<char> in(nv, 0);
+    std::vector<int> frontier, next;
+    for (size_t t = num_markers; t < nv; t++) {
+        in[t] = 1;
+        frontier.push_back((int)t);
+    }
+    for (int depth = 0; depth < max_depth && !frontier.empty(); depth++) {
+        next.clear();
+        for (int node : frontier) {
+            const uint32_t *row = bits + (size_t)node * rw;
+            for (size_t w = 0; w < rw; w++) {
+                uint32_t word = row[w];
+                while (word) {
+                    const int b = __builtin_ctz(word);
+                    word &= word - 1;
+                    const size_t c = w * 32 + (size_t)b;
+                    if (c < num_markers && !in[c]) {
+                        in[c] = 1;
+                        next.push_back((int)c);
+                    }
+                }
+            }
+        }
+        frontier.swap(next);
+    }
+    std::vector<int> sel;
+    for (size_t i = 0; i < nv; i++)
+        if (in[i]) sel.push_back((int)i);
+    return sel;
+}
+
+// ------------------------------------------------------------------------------------------------
+// cuskss: one stage of run_cusk() (cli.cpp:29-60) on a ReducedGC held on the host
+// ------------------------------------------------------------------------------------------------
+static int cuskss_stage(cusk_ctx *ctx, Reduced &gc, bool first_stage, float th, int depth, int max_level,
+                        const std::vector<int> &time_index_traits, cusk_stats *stats)
+{
+    const size_t nv = gc.num_var, m = gc.num_markers();
+    const size_t rw = cusk_row_words((int)nv);
+    cudaStream_t st = (cudaStream_t)cusk_ctx_stream(ctx);
+    HOST_CUDA(cudaSetDevice(ctx->device));
+    arena_reset(ctx->io);
+    float *dC = (float *)arena_take(ctx->io, nv * nv * 4);
+    float *dN = gc.uniform ? nullptr : (float *)arena_take(ctx->io, nv * nv * 4);
+    uint32_t *dbits = (uint32_t *)arena_take(ctx->io, nv * rw * 4);
+    int *dG = first_stage ? nullptr : (int *)arena_take(ctx->io, nv * nv * 4);
+    int *dT = (int *)arena_take(ctx->io, nv * 4);
+    if (!dC || (!gc.uniform && !dN) || !dbits || (!first_stage && !dG) || !dT) return CUSK_E_CUDA;
+    // markers are time 0, traits carry their time index (cli.cpp:37-42)
+    std::vector<int> time_index(nv, 0);
+    for (size_t i = m, r = 0; i < nv; i++, r++) time_index[i] = time_index_traits[r];
+    bool use_time = false;
+    for (size_t i = 1; i < nv; i++) use_time |= time_index[i] != time_index[0];
+    HOST_CUDA(cudaMemcpyAsync(dC, gc.C.data(), nv * nv * 4, cudaMemcpyHostToDevice, st));
+    if (dN) HOST_CUDA(cudaMemcpyAsync(dN, gc.N.data(), nv * nv * 4, cudaMemcpyHostToDevice, st));
+    if (dG) HOST_CUDA(cudaMemcpyAsync(dG, gc.G.data(), nv * nv * 4, cudaMemcpyHostToDevice, st));
+    if (use_time) HOST_CUDA(cudaMemcpyAsync(dT, time_index.data(), nv * 4, cudaMemcpyHostToDevice, st));
+    int last = 0;
+    int rc = hetcor_engine(ctx, dC, (int)nv, dbits, dG, false, dN, gc.n_uniform, th, max_level, use_time ? dT : nullptr,
+                           &last, stats);
+    if (rc) return rc;
+    std::vector<uint32_t> bits(nv * rw);
+    HOST_CUDA(cudaMemcpyAsync(bits.data(), dbits, nv * rw * 4, cudaMemcpyDeviceToHost, st));
+    HOST_CUDA(cudaStreamSynchronize(st));
+    // subset_variables + reduce_gc(G, C, S, P, num_var, num_phen, ML, new_to_old)  (cli.cpp:56-59)
+    const std::vector<int> sel = subset_variables(bits.data(), nv, rw, m, depth);
+    Reduced out;
+    const size_t ns = sel.size();
+    out.num_var = ns;
+    out.num_phen = gc.num_phen;
+    out.max_level = CUSK_ML;
+    out.uniform = gc.uniform;
+    out.n_uniform = gc.n_uniform;
+    out.new_to_old.resize(ns);
+    for (size_t i = 0; i < ns; i++) out.new_to_old[i] = gc.new_to_old[sel[i]];
+    out.G = expand_bits(bits, nv, rw, sel);
+    out.C.resize(ns * ns);
+    if (!gc.uniform) out.N.resize(ns * ns);
+    for (size_t i = 0; i < ns; i++)
+        for (size_t j = 0; j < ns; j++) {
+            out.C[i * ns + j] = gc.C[(size_t)sel[i] * nv + sel[j]];
+            if (!gc.uniform) out.N[i * ns + j] = gc.N[(size_t)sel[i] * nv + sel[j]];
+        }
+    gc = std::move(out);
+    return CUSK_OK;
+}
+
+void load_cuskss_shared(const CuskssArgs &a, CuskssShared *s)
+{
+    s->blocks = read_blocks(a.block_path);
+    s->pxp = load_pxp(a.pxp_path, a.hetcor ? a.pxp_se_path : std::string(), a.pearson_sample_size);
+    s->time_index_traits.assign(s->pxp.num_phen, 1);
+    if (a.time_indexed) s->time_index_traits = read_ints_from_lines(a.time_index_path);
+    s->mxp_all = load_mxp(a.mxp_path, a.hetcor ? a.mxp_se_path : std::string(), true, 0, (size_t)-1, {});
+}
+
+int run_cuskss(cusk_ctx *ctx, const CuskssArgs &a, bool verbose, RunReport *rep, const CuskssShared *shared)
+{
+    RunReport local;
+    if (!rep) rep = &local;
+    *rep = RunReport();
+    const double t0 = now_s();
+    auto say = [&](const char *s) {
+        if (verbose) std::cout << s << std::endl;
+    };
+    say("Loading input files");
+    MarkerBlock block;
+    std::vector<int> marker_ixs;
+    if (a.merged) {
+        say("Loading marker indices");
+        marker_ixs = read_ints_from_binary(a.marker_ixs_path);
+    } else {
+        say("Loading block file");
+        const std::vector<MarkerBlock> blocks_local = shared ? std::vector<MarkerBlock>() : read_blocks(a.block_path);
+        const std::vector<MarkerBlock> &blocks = shared ? shared->blocks : blocks_local;
+        if (a.block_ix < 0 || (size_t)a.block_ix >= blocks.size()) fail("block index out of range");
+        block = blocks[(size_t)a.block_ix];
+    }
+    say("Loading pxp");
+    const Pxp pxp_local = shared ? Pxp() : load_pxp(a.pxp_path, a.hetcor ? a.pxp_se_path : std::string(), a.pearson_sample_size);
+    const Pxp &pxp = shared ? shared->pxp : pxp_local;
+    const size_t num_phen = pxp.num_phen;
+    std::vector<int> time_index_traits(num_phen, 1);
+    if (shared) {
+        time_index_traits = shared->time_index_traits;
+    } else if (a.time_indexed) {
+        say("Loading time_indices");
+        time_index_traits = read_ints_from_lines(a.time_index_path);
+        if (time_index_traits.size() < num_phen) fail("time index file has fewer entries than traits");
+    }
+    const float th = cusk_hetcor_threshold(a.alpha);
+    Reduced gc;
+    std::string stem;
+    if (a.trait_only) {
+        gc.num_var = num_phen;
+        gc.num_phen = num_phen;
+        gc.max_level = a.max_level_one;
+        gc.C = pxp.corr;
+        gc.uniform = !a.hetcor;
+        gc.n_uniform = a.pearson_sample_size;
+        if (a.hetcor) gc.N = pxp.ess;
+        stem = "trait_only";
+    } else {
+        say("Loading mxm");
+        size_t m = 0;
+        const std::vector<float> mxm = load_mxm_square(a.mxm_path, &m);
+        say("Loading mxp summary stats");
+        MxpRows mxp;
+        if (shared && !a.merged) {
+            // rows [first_global, last_global] of the preloaded table
+            const MxpRows &all = shared->mxp_all;
+            const size_t f0 = std::min(block.first_global(), all.num_markers);
+            const size_t f1 = std::min(block.last_global() + 1, all.num_markers);
+            mxp.num_phen = all.num_phen;
+            mxp.num_markers = f1 - f0;
+            mxp.corr.assign(all.corr.begin() + f0 * all.num_phen, all.corr.begin() + f1 * all.num_phen);
+            if (!all.ess.empty()) mxp.ess.assign(all.ess.begin() + f0 * all.num_phen, all.ess.begin() + f1 * all.num_phen);
+        } else {
+            mxp = load_mxp(a.mxp_path, a.hetcor ? a.mxp_se_path : std::string(), !a.merged,
+                           a.merged ? 0 : block.first_global(), a.merged ? 0 : block.last_global(), marker_ixs);
+        }
+        if (pxp.num_phen != mxp.num_phen) fail("Numbers of traits seem to differ between pxp and mxp");
+        if (m != mxp.num_markers) {
+            fail("Numbers of markers seem to differ between mxm and mxp\nmxp: " + std::to_string(mxp.num_markers) + " x " +
+                 std::to_string(mxp.num_phen) + "\nmxm: " + std::to_string(m) + " x " + std::to_string(m));
+        }
+        say("Merging correlations into single matrix");
+        SquareInputs si = make_square_cuskss_inputs(mxm, m, mxp, pxp, a.pearson_sample_size, a.hetcor);
+        gc.num_var = m + num_phen;
+        gc.num_phen = num_phen;
+        gc.max_level = a.max_level_one;
+        gc.C = std::move(si.C);
+        gc.N = std::move(si.N);
+        gc.uniform = si.uniform;
+        gc.n_uniform = si.n_uniform;
+        stem = a.merged ? std::string("cuskss_merged") : block.stem();
+    }
+    gc.new_to_old.resize(gc.num_var);
+    for (size_t i = 0; i < gc.num_var; i++) gc.new_to_old[i] = (int)i;
+    rep->num_var_in = gc.num_var;
+    rep->load_s = now_s() - t0;
+
+    const double t1 = now_s();
+    say("Starting first cusk stage");
+    int rc = cuskss_stage(ctx, gc, true, th, a.depth, a.max_level_one, time_index_traits, &rep->stage[0]);
+    if (rc) return rc;
+    rep->stages = 1;
+    if (a.two_stage && !a.trait_only) {
+        say("Starting second cusk stage");
+        rc = cuskss_stage(ctx, gc, false, th, a.depth, a.max_level_two, time_index_traits, &rep->stage[1]);
+        if (rc) return rc;
+        rep->stages = 2;
+    }
+    rep->device_s = now_s() - t1;
+    if (verbose) std::cout << "Retained " << gc.num_markers() << " markers" << std::endl;
+    const double t2 = now_s();
+    if (a.write_output) gc.to_file(make_path(a.outdir, stem, ""));
+    rep->write_s = now_s() - t2;
+    rep->num_var_out = gc.num_var;
+    rep->retained_markers = gc.num_markers();
+    return CUSK_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// cusk: individual-level data (cli.cpp:432-678)
+// ------------------------------------------------------------------------------------------------
+void load_cusk_shared(const CuskArgs &a, CuskShared *s, bool verbose)
+{
+    for (const char *sfx : {".bed", ".dim", ".means", ".stds", ".bim", ".fam"}) check_path(a.bfiles + sfx);  // io.cpp:408-415
+    check_path(a.phen_path);
+    check_path(a.block_path);
+    check_path(a.outdir);
+    s->phen = load_phen(a.phen_path);
+    s->dims = read_dims(a.bfiles + ".dim");
+    if (s->phen.num_samples != s->dims.num_samples) {
+        std::cerr << "different num samples in phen and dims" << std::endl;
+        fail("different num samples in phen and dims");
+    }
+    BimInfo bim(a.bfiles + ".bim");
+    if (verbose) std::cout << "Found " << s->phen.num_phen << " phenotypes" << std::endl;
+    if (verbose) std::cout << "Loading blocks" << std::endl;
+    s->blocks = read_blocks(a.block_path);
+    if (verbose) std::cout << "Found " << s->blocks.size() << " blocks" << std::endl;
+    s->block_chr_start.resize(s->blocks.size());
+    for (size_t i = 0; i < s->blocks.size(); i++) {
+        const MarkerBlock &b = s->blocks[i];
+        const size_t ci = bim.chr_index(b.chr);
+        if (b.first >= bim.num_on_chr[ci] || b.last >= bim.num_on_chr[ci]) {
+            std::cerr << "block out of bounds with first_ix: " << b.first << " last_ix: " << b.last << std::endl;
+            fail("block out of bounds");
+        }
+        s->block_chr_start[i] = bim.chr_start[ci];
+    }
+    s->Th.resize(15);
+    cusk_threshold_array((int)s->dims.num_samples, a.alpha, s->Th.data());
+    s->means = read_floats_from_line_range(a.bfiles + ".means", 0, (size_t)-1);
+    s->stds = read_floats_from_line_range(a.bfiles + ".stds", 0, (size_t)-1);
+}
+
+int run_cusk_block(cusk_ctx *ctx, const CuskArgs &a, const CuskShared &s, size_t bid, bool verbose, RunReport *rep)
+{
+    RunReport local;
+    if (!rep) rep = &local;
+    *rep = RunReport();
+    if (bid >= s.blocks.size()) fail("block index out of range");
+    const MarkerBlock &block = s.blocks[bid];
+    const size_t m = block.size(), n = s.dims.num_samples, p = s.phen.num_phen, nv = m + p;
+    const size_t col_bytes = s.dims.col_bytes();
+    const size_t g0 = s.block_chr_start[bid] + block.first;
+    if (verbose) {
+        std::cout << std::endl << "Processing block " << bid + 1 << " / " << s.blocks.size() << std::endl;
+        std::cout << "Block size: " << m << std::endl << "Loading bed data" << std::endl;
+    }
+    if (g0 + m > s.means.size() || g0 + m > s.stds.size()) fail("block size and number of means or stds differ");
+    const double t0 = now_s();
+    cudaStream_t st = (cudaStream_t)cusk_ctx_stream(ctx);
+    HOST_CUDA(cudaSetDevice(ctx->device));
+    // ---- load the block (io.cpp:238-250) straight into page-locked memory -----------------------
+    static thread_local Pinned bed_stage;
+    unsigned char *h_bed = (unsigned char *)bed_stage.get(std::max<size_t>(m * col_bytes, 1));
+    {
+        FILE *f = fopen((a.bfiles + ".bed").c_str(), "rb");
+        if (!f) fail("file or directory not found: " + a.bfiles + ".bed");
+        fseek(f, (long)(3 + g0 * col_bytes), SEEK_SET);
+        const size_t got = fread(h_bed, 1, m * col_bytes, f);
+        fclose(f);
+        if (got < m * col_bytes) memset(h_bed + got, 0, m * col_bytes - got);
+    }
+    rep->load_s = now_s() - t0;
+    const double t1 = now_s();
+    arena_reset(ctx->io);
+    unsigned char *d_bed = (unsigned char *)arena_take(ctx->io, m * col_bytes);
+    float *d_phen = (float *)arena_take(ctx->io, std::max<size_t>(p * n, 1) * 4);
+    float *d_mean = (float *)arena_take(ctx->io, m * 4);
+    float *d_std = (float *)arena_take(ctx->io, m * 4);
+    float *d_mxp = (float *)arena_take(ctx->io, std::max<size_t>(m * p, 1) * 4);
+    if (!d_bed || !d_phen || !d_mean || !d_std || !d_mxp) return CUSK_E_CUDA;
+    HOST_CUDA(cudaMemcpyAsync(d_bed, h_bed, m * col_bytes, cudaMemcpyHostToDevice, st));
+    HOST_CUDA(cudaMemcpyAsync(d_phen, s.phen.data.data(), p * n * 4, cudaMemcpyHostToDevice, st));
+    HOST_CUDA(cudaMemcpyAsync(d_mean, s.means.data() + g0, m * 4, cudaMemcpyHostToDevice, st));
+    HOST_CUDA(cudaMemcpyAsync(d_std, s.stds.data() + g0, m * 4, cudaMemcpyHostToDevice, st));
+    // ---- marker x trait screen (cli.cpp:548-576) ---------------------------------------------------
+    if (verbose) std::cout << "Checking for significant marker - phen correlations" << std::endl;
+    arena_reset(ctx);
+    int rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, 0, nullptr, d_mxp, nullptr, nullptr, false,
+                               nullptr, false);
+    if (rc) return rc;
+    std::vector<float> mxp(m * p);
+    HOST_CUDA(cudaMemcpyAsync(mxp.data(), d_mxp, m * p * 4, cudaMemcpyDeviceToHost, st));
+    HOST_CUDA(cudaStreamSynchronize(st));
+    int num_sig = 0;
+    for (float c : mxp) num_sig += (fabs(0.5 * (log(fabs((1 + c))) - log(fabs(1 - c)))) >= s.Th[0]);
+    if (num_sig > 0) {
+        if (verbose) std::cout << "Found " << num_sig << " marker - phen correlations. Proceeding." << std::endl;
+    } else {
+        if (verbose) std::cout << "No significant correlations found. Skipping block." << std::endl;
+        rep->skipped = true;
+        rep->device_s = now_s() - t1;
+        return CUSK_OK;
+    }
+    // ---- all correlations, dense on the device (cli.cpp:581-649) -------------------------------------
+    if (verbose) std::cout << "Computing all correlations" << std::endl;
+    float *d_C = (float *)arena_take(ctx->io, nv * nv * 4);
+    const size_t rw = cusk_row_words((int)nv);
+    uint32_t *d_bits = (uint32_t *)arena_take(ctx->io, nv * rw * 4);
+    if (!d_C || !d_bits) return CUSK_E_CUDA;
+    arena_reset(ctx);
+    rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, 0, d_C, d_mxp, nullptr, nullptr, true, &rep->corr,
+                           true);
+    if (rc) return rc;
+    // ---- first skeleton stage (cli.cpp:662-673) -------------------------------------------------------
+    if (verbose) std::cout << "Running cuPC" << std::endl;
+    int last = 0;
+    rc = skeleton_engine(ctx, d_C, (int)nv, d_bits, s.Th.data(), a.max_level, &last, nullptr, nullptr, &rep->stage[0]);
+    if (rc) return rc;
+    std::vector<uint32_t> bits(nv * rw);
+    HOST_CUDA(cudaMemcpyAsync(bits.data(), d_bits, nv * rw * 4, cudaMemcpyDeviceToHost, st));
+    HOST_CUDA(cudaStreamSynchronize(st));
+    const std::vector<int> sel1 = subset_variables(bits.data(), nv, rw, m, a.depth);
+    const size_t n1 = sel1.size(), m1 = n1 - p;
+    // reduce_gcs #1: only C (gathered on the device) and the index map survive into stage two
+    int *d_sel = (int *)arena_take(ctx->io, n1 * 4);
+    float *d_C1 = (float *)arena_take(ctx->io, n1 * n1 * 4);
+    const size_t rw1 = cusk_row_words((int)n1);
+    uint32_t *d_bits1 = (uint32_t *)arena_take(ctx->io, n1 * rw1 * 4);
+    if (!d_sel || !d_C1 || !d_bits1) return CUSK_E_CUDA;
+    HOST_CUDA(cudaMemcpyAsync(d_sel, sel1.data(), n1 * 4, cudaMemcpyHostToDevice, st));
+    gather_square_kernel<<<dim3((unsigned)((n1 + 255) / 256), (unsigned)n1), 256, 0, st>>>(d_C, (int)nv, d_sel, (int)n1, d_C1);
+    HOST_CUDA(cudaGetLastError());
+    // ---- second stage (reduced_gcs_cusk, cli.cpp:62-87): level 0 re-initialises G -----------------------
+    if (verbose) std::cout << "Starting second cusk stage" << std::endl;
+    std::vector<cusk_sepset> seps;
+    rc = skeleton_engine(ctx, d_C1, (int)n1, d_bits1, s.Th.data(), a.max_level_two, &last, nullptr, &seps, &rep->stage[1]);
+    if (rc) return rc;
+    rep->stages = 2;
+    std::vector<uint32_t> bits1(n1 * rw1);
+    std::vector<float> C1(n1 * n1);
+    HOST_CUDA(cudaMemcpyAsync(bits1.data(), d_bits1, n1 * rw1 * 4, cudaMemcpyDeviceToHost, st));
+    HOST_CUDA(cudaMemcpyAsync(C1.data(), d_C1, n1 * n1 * 4, cudaMemcpyDeviceToHost, st));
+    HOST_CUDA(cudaStreamSynchronize(st));
+    rep->device_s = now_s() - t1;
+    const double t2 = now_s();
+    const std::vector<int> sel2 = subset_variables(bits1.data(), n1, rw1, m1, a.depth);
+    const size_t n2 = sel2.size();
+    // reduce_gcs #2 with index_map = stage one's new_to_old (parent_set.cpp:130-175)
+    Reduced out;
+    out.num_var = n2;
+    out.num_phen = p;
+    out.max_level = CUSK_ML;
+    out.has_sep = true;
+    out.new_to_old.resize(n2);
+    for (size_t i = 0; i < n2; i++) out.new_to_old[i] = sel1[(size_t)sel2[i]];
+    out.G = expand_bits(bits1, n1, rw1, sel2);
+    out.C.resize(n2 * n2);
+    for (size_t i = 0; i < n2; i++)
+        for (size_t j = 0; j < n2; j++) out.C[i * n2 + j] = C1[(size_t)sel2[i] * n1 + sel2[j]];
+    out.S.assign(n2 * n2 * CUSK_ML, -1);
+    // The reference translates separating-set members through VariableSubsetIndices(P, index_map)
+    // (parent_set.h:156-166), whose old_to_new map is keyed by the ORIGINAL index
+    // index_map[sorted P[i]], while it is queried with the stage-two index of the member; a key that
+    // is absent yields 0 (std::unordered_map::operator[]).  Reproduced as is: .sep is a file contract.
+    std::unordered_map<int, int> old_to_new;
+    for (size_t i = 0; i < n2; i++) old_to_new[out.new_to_old[i]] = (int)i;
+    std::vector<int> pos_in_sel2(n1, -1);
+    for (size_t i = 0; i < n2; i++) pos_in_sel2[(size_t)sel2[i]] = (int)i;
+    for (const cusk_sepset &r : seps) {
+        const int i = pos_in_sel2[(size_t)r.x], j = pos_in_sel2[(size_t)r.y];
+        if (i < 0 || j < 0) continue;
+        int *slot = out.S.data() + ((size_t)i * n2 + (size_t)j) * CUSK_ML;
+        int k = 0;
+        for (int q = 0; q < r.level; q++) {
+            const int e = r.s[q];
+            if (e != -1 && pos_in_sel2[(size_t)e] >= 0) {
+                auto it = old_to_new.find(e);
+                slot[k++] = (it == old_to_new.end()) ? 0 : it->second;
+            }
+        }
+    }
+    if (verbose) std::cout << "Retained " << out.num_markers() << " markers" << std::endl;
+    out.to_file(make_path(a.outdir, block.stem(), ""));
+    rep->write_s = now_s() - t2;
+    rep->num_var_in = nv;
+    rep->num_var_out = n2;
+    rep->retained_markers = out.num_markers();
+    return CUSK_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// prep-bed (prep.cpp:157-201): .dim, .means, .stds, .modes
+// ------------------------------------------------------------------------------------------------
+int run_prep(cusk_ctx *ctx, const std::string &bfiles, bool verbose)
+{
+    for (const char *sfx : {".bed", ".bim", ".fam"}) check_path(bfiles + sfx);
+    if (!has_valid_bed_prefix(bfiles + ".bed")) fail("Invalid prefix bytes in bed");
+    const size_t n = count_lines(bfiles + ".fam");
+    BimInfo bim(bfiles + ".bim");
+    const size_t m_total = bim.num_lines;
+    const size_t col_bytes = (n + 3) / 4;
+    if (verbose) std::cout << "Writing dim file." << std::endl;
+    {
+        FILE *f = fopen((bfiles + ".dim").c_str(), "w");
+        if (!f) fail("cannot write " + bfiles + ".dim");
+        fprintf(f, "%zu\t%zu\n", n, m_total);
+        fclose(f);
+    }
+    if (verbose) std::cout << "Computing means, stds, modes." << std::endl;
+    std::vector<float> means, stds;
+    std::vector<int> modes;
+    cudaStream_t st = (cudaStream_t)cusk_ctx_stream(ctx);
+    HOST_CUDA(cudaSetDevice(ctx->device));
+    FILE *f = fopen((bfiles + ".bed").c_str(), "rb");
+    if (!f) fail("file or directory not found: " + bfiles + ".bed");
+    fseek(f, 3, SEEK_SET);
+    // stream the file in chunks of markers; only whole columns count (the reference's read loop
+    // stops at the first short read, prep.cpp:185)
+    const size_t chunk_markers = std::max<size_t>(1, std::min<size_t>(m_total ? m_total : 1, ((size_t)256 << 20) / std::max<size_t>(col_bytes, 1)));
+    Pinned stage;
+    unsigned char *h = (unsigned char *)stage.get(chunk_markers * col_bytes);
+    for (;;) {
+        const size_t got = fread(h, 1, chunk_markers * col_bytes, f);
+        const size_t mk = got / col_bytes;
+        if (mk == 0) break;
+        arena_reset(ctx->io);
+        unsigned char *d_bed = (unsigned char *)arena_take(ctx->io, mk * col_bytes);
+        int *d_counts = (int *)arena_take(ctx->io, mk * 16);
+        float *d_means = (float *)arena_take(ctx->io, mk * 4);
+        float *d_stds = (float *)arena_take(ctx->io, mk * 4);
+        int *d_modes = (int *)arena_take(ctx->io, mk * 4);
+        if (!d_bed || !d_counts || !d_means || !d_stds || !d_modes) {
+            fclose(f);
+            return CUSK_E_CUDA;
+        }
+        const size_t base = means.size();
+        means.resize(base + mk);
+        stds.resize(base + mk);
+        modes.resize(base + mk);
+        cudaMemcpyAsync(d_bed, h, mk * col_bytes, cudaMemcpyHostToDevice, st);
+        launch_bed_counts(st, d_bed, (int)mk, (int)n, col_bytes, d_counts);
+        launch_bed_stats(st, d_bed, (int)mk, (int)n, col_bytes, d_counts, d_means, d_stds, d_modes);
+        cudaMemcpyAsync(means.data() + base, d_means, mk * 4, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(stds.data() + base, d_stds, mk * 4, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(modes.data() + base, d_modes, mk * 4, cudaMemcpyDeviceToHost, st);
+        const cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) {
+            fclose(f);
+            cusk_set_error("prep: %s", cudaGetErrorString(e));
+            return CUSK_E_CUDA;
+        }
+        if (got < chunk_markers * col_bytes) break;
+    }
+    fclose(f);
+    if (verbose) std::cout << "Writing stats to files." << std::endl;
+    write_column(means, bfiles + ".means");
+    write_column(stds, bfiles + ".stds");
+    write_column(modes, bfiles + ".modes");
+    if (verbose) std::cout << "Done." << std::endl;
+    return CUSK_OK;
+}
+
+}  // namespace cuskhost

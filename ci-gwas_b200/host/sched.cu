@@ -1,0 +1,172 @@
+// sched.cu -- multi-GPU block scheduler (north_star item 5).  LD blocks are independent
+// units: one worker thread per GPU pulls blocks from a queue sorted by descending size (longest
+// processing time first), with no collective between GPUs.  The reference has no scheduler; users
+// launch one `ci-gwas.py cusk <block-index>` process per block (README.md:62).
+// Resume: a block whose <stem>.mdim already exists is skipped (the de-facto checkpoint of the
+// reference's workflow; merge-block-outputs tolerates missing blocks, merge_blocks.py:364-386).
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <mutex>
+#include <thread>
+
+#include "../csrc/common.cuh"
+#include "host.hpp"
+
+namespace cuskhost {
+
+std::vector<int> devices_from_env()
+{
+    std::vector<int> out;
+    const char *e = getenv("CUSK_DEVICES");
+    if (e && *e) {
+        const char *p = e;
+        while (*p) {
+            char *end = nullptr;
+            const long v = strtol(p, &end, 10);
+            if (end == p) break;
+            out.push_back((int)v);
+            p = (*end == ',') ? end + 1 : end;
+        }
+    }
+    if (out.empty()) {
+        const int n = cusk_device_count();
+        for (int i = 0; i < n; i++) out.push_back(i);
+    }
+    return out;
+}
+
+// Longest-processing-time-first order: cost model m^2 (level 0 and the correlation Gram are
+// quadratic in the block size; the deeper levels depend on the data).
+std::vector<size_t> lpt_order(const std::vector<MarkerBlock> &blocks)
+{
+    std::vector<size_t> order(blocks.size());
+    for (size_t i = 0; i < order.size(); i++) order[i] = i;
+    std::stable_sort(order.begin(), order.end(),
+                     [&](size_t a, size_t b) { return blocks[a].size() > blocks[b].size(); });
+    return order;
+}
+
+namespace {
+
+struct Tally {
+    std::mutex mu;
+    size_t done = 0, skipped_existing = 0, skipped_nosig = 0, failed = 0;
+    int64_t tests = 0;
+    std::string first_error;
+};
+
+int64_t tests_of(const RunReport &r)
+{
+    int64_t t = 0;
+    for (int s = 0; s < r.stages; s++)
+        for (int l = 0; l <= CUSK_ML; l++) t += r.stage[s].tests_executed[l];
+    return t;
+}
+
+template <class RunOne>
+int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, const std::vector<int> &devices,
+            bool resume, RunOne run_one)
+{
+    if (devices.empty()) {
+        std::cerr << "no CUDA device available" << std::endl;
+        return 1;
+    }
+    const std::vector<size_t> order = lpt_order(blocks);
+    std::atomic<size_t> next{0};
+    Tally tally;
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> workers;
+    for (int dev : devices) {
+        workers.emplace_back([&, dev]() {
+            cusk_ctx *ctx = nullptr;
+            if (cusk_ctx_create(dev, &ctx) != CUSK_OK) {
+                std::lock_guard<std::mutex> lk(tally.mu);
+                tally.failed++;
+                if (tally.first_error.empty()) tally.first_error = cusk_last_error();
+                return;
+            }
+            for (;;) {
+                const size_t k = next.fetch_add(1);
+                if (k >= order.size()) break;
+                const size_t bid = order[k];
+                const std::string stem = make_path(outdir, blocks[bid].stem(), "");
+                if (resume && path_exists(stem + ".mdim")) {
+                    std::lock_guard<std::mutex> lk(tally.mu);
+                    tally.skipped_existing++;
+                    continue;
+                }
+                RunReport rep;
+                int rc;
+                std::string err;
+                try {
+                    rc = run_one(ctx, bid, &rep);
+                    if (rc) err = cusk_last_error();
+                } catch (const HostError &e) {
+                    rc = 1;
+                    err = e.msg;
+                }
+                std::lock_guard<std::mutex> lk(tally.mu);
+                if (rc) {
+                    tally.failed++;
+                    if (tally.first_error.empty()) tally.first_error = "block " + blocks[bid].stem() + ": " + err;
+                } else if (rep.skipped) {
+                    tally.skipped_nosig++;
+                } else {
+                    tally.done++;
+                    tally.tests += tests_of(rep);
+                }
+                printf("{\"block\": \"%s\", \"device\": %d, \"rc\": %d, \"skipped\": %s, \"n_var\": %zu, \"n_out\": %zu, "
+                       "\"load_s\": %.4f, \"device_s\": %.4f, \"write_s\": %.4f, \"tests\": %lld}\n",
+                       blocks[bid].stem().c_str(), dev, rc, rep.skipped ? "true" : "false", rep.num_var_in,
+                       rep.num_var_out, rep.load_s, rep.device_s, rep.write_s, (long long)tests_of(rep));
+            }
+            cusk_ctx_destroy(ctx);
+        });
+    }
+    for (auto &w : workers) w.join();
+    const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    printf("{\"summary\": true, \"blocks\": %zu, \"done\": %zu, \"skipped_existing\": %zu, \"skipped_no_signal\": %zu, "
+           "\"failed\": %zu, \"gpus\": %zu, \"seconds\": %.3f, \"ci_tests\": %lld, \"ci_tests_per_s\": %.4g}\n",
+           blocks.size(), tally.done, tally.skipped_existing, tally.skipped_nosig, tally.failed, devices.size(), secs,
+           (long long)tally.tests, secs > 0 ? (double)tally.tests / secs : 0.0);
+    if (tally.failed) {
+        std::cerr << tally.first_error << std::endl;
+        return 1;
+    }
+    return 0;
+}
+
+}  // namespace
+
+int run_cusk_all(const CuskArgs &a, const std::vector<int> &devices, bool resume)
+{
+    CuskShared shared;
+    load_cusk_shared(a, &shared, true);
+    return run_all(shared.blocks, a.outdir, devices, resume,
+                   [&](cusk_ctx *ctx, size_t bid, RunReport *rep) { return run_cusk_block(ctx, a, shared, bid, false, rep); });
+}
+
+// mxm_pattern: path of the per-block mxm file with "{}" standing for the block stem <chr>_<first>_<last>
+int run_cuskss_all(const CuskssArgs &a, const std::string &mxm_pattern, const std::vector<int> &devices, bool resume)
+{
+    CuskssShared shared;
+    load_cuskss_shared(a, &shared);
+    return run_all(shared.blocks, a.outdir, devices, resume, [&](cusk_ctx *ctx, size_t bid, RunReport *rep) {
+        CuskssArgs b = a;
+        b.block_ix = (int)bid;
+        b.merged = false;
+        b.trait_only = false;
+        std::string path = mxm_pattern;
+        const size_t pos = path.find("{}");
+        if (pos != std::string::npos) path.replace(pos, 2, shared.blocks[bid].stem());
+        b.mxm_path = path;
+        check_path(path);
+        return run_cuskss(ctx, b, false, rep, &shared);
+    });
+}
+
+}  // namespace cuskhost

@@ -147,6 +147,39 @@ int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, const float *
                         size_t n, size_t p, const float *d_mean, const float *d_std, int mode,
                         float *d_Csq, cusk_corr_stats *stats);
 
+/* ---- multi-GPU: one skeleton sharded over several GPUs (cuskss --marker-indices) ------
+ * The level-l work items are dealt round-robin to the ranks; after each level the ranks exchange what
+ * they removed (NCCL all-gather of the adjacency bitmaps + AND for the summary-statistic engine,
+ * all-reduce MIN of the separating-set ranks for the individual-level engine), so every rank returns
+ * the same graph as a single-GPU call.  The reference has no multi-GPU path (nothing to cite). */
+typedef struct cusk_comm cusk_comm;
+int cusk_comm_unique_id(char *out128);                       /* ncclGetUniqueId; share it with all ranks */
+int cusk_comm_create(cusk_ctx *ctx, int rank, int world, const char *id128, cusk_comm **out); /* one process per GPU */
+int cusk_comm_create_all(cusk_ctx **ctxs, int world, cusk_comm **out);   /* one process, NCCL, distinct devices */
+int cusk_comm_create_local(cusk_ctx **ctxs, int world, cusk_comm **out); /* one process, P2P copies; ranks may share a device */
+void cusk_comm_destroy(cusk_comm *c);
+int cusk_ctx_set_comm(cusk_ctx *ctx, cusk_comm *c);          /* attach (NULL detaches): later skeleton calls are sharded */
+int cusk_comm_stats(const cusk_comm *c, double *exchange_ms, int64_t *exchange_bytes); /* of the last call */
+int cusk_nccl_version(void);                                 /* 0 when libnccl cannot be loaded */
+
+/* ---- host layer: the `mps` process contract (apps/mps.cpp:17-121, src/cli.cpp:194,432,696) --------
+ * argv exactly as the reference's binary takes it (`prep`, `cusk`, `cuskss`; plus `cusk-all`,
+ * `cuskss-all`); returns the process exit status.  prep_bed_no_impute (src/prep.cpp:157) is
+ * `mps prep <bfiles>`. */
+int cusk_mps_main(int argc, char **argv);
+int cusk_prep_bed(cusk_ctx *ctx, const char *bfiles);
+/* host-only pieces (no device needed): the cuskss input assembly make_square_cuskss_inputs
+ * (src/cli.cpp:89-173) over the loaders of src/{marker,marker_trait,trait}_summary_stats.cpp
+ * ("NULL" = absent path; *N_out = NULL when the sample size is uniform; release with cusk_free);
+ * subset_variables (src/parent_set.cpp:8-53; out_sel[i] = 1 keeps variable i); load_phen
+ * (src/phen.cpp:27-74; column-major). */
+int cusk_cuskss_square_inputs(const char *mxm, const char *mxp, const char *mxp_se, const char *pxp,
+                              const char *pxp_se, const char *blockfile, int block_index, const char *marker_ixs,
+                              float num_samples, int *num_var, int *num_phen, float **C_out, float **N_out);
+int cusk_subset_variables(const int *G, int num_var, int num_markers, int max_depth, int *out_sel);
+int cusk_load_phen(const char *path, int64_t *num_samples, int64_t *num_phen, float **data_out);
+void cusk_free(void *p);
+
 /* ---- drop-in signatures of the reference -------------------------------------------------- */
 /* include/mps/corr_host.h: cu_marker_phen_corr_pearson / cu_corr_pearson_npn (C++ linkage in the
  * reference; exported here with C linkage and the same argument order) */
