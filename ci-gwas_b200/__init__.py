@@ -9,8 +9,10 @@ from .lib import (  # noqa: F401
     Context,
     Stats,
     build_library,
+    comm_unique_id,
     hetcor_threshold,
     library_path,
     load_library,
+    mps_path,
     threshold_array,
 )

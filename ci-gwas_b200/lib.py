@@ -123,8 +123,26 @@ def load_library():
                                           c_float_p, c_float_p, c_float_p, C.POINTER(CorrStats)]
     lib.cusk_corr_block_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                         C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(CorrStats)]
+    lib.cusk_comm_unique_id.argtypes = [C.c_char_p]
+    lib.cusk_comm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.cusk_comm_destroy.argtypes = [C.c_void_p]
+    lib.cusk_ctx_set_comm.argtypes = [C.c_void_p, C.c_void_p]
+    lib.cusk_comm_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), c_i64_p]
     _LIB = lib
     return lib
+
+
+def mps_path():
+    """the `mps` executable built next to the library (argv contract of the reference's cusk/apps/mps.cpp)"""
+    return os.path.join(_HERE, "mps")
+
+
+def comm_unique_id():
+    """128-byte NCCL unique id; create it on one rank and broadcast it to the others."""
+    buf = C.create_string_buffer(128)
+    if load_library().cusk_comm_unique_id(buf) != 0:
+        raise CuskError(load_library().cusk_last_error().decode())
+    return buf.raw
 
 
 def threshold_array(n, alpha):
@@ -152,6 +170,7 @@ class Context:
         self.device = device
 
     def close(self):
+        self.detach_comm()
         if getattr(self, "h", None):
             self.lib.cusk_ctx_destroy(self.h)
             self.h = None
@@ -165,6 +184,26 @@ class Context:
     def _check(self, rc):
         if rc != 0:
             raise CuskError(f"rc={rc}: {self.lib.cusk_last_error().decode()}")
+
+    # -- edge-sharded mode (one skeleton over several GPUs; include/cusk_b200.h "multi-GPU") --------
+    def attach_comm(self, rank, world, unique_id):
+        """Joins the NCCL communicator of `world` ranks; later skeleton calls on this context take every
+        world-th work item of a level and exchange removals with the other ranks after each level."""
+        h = C.c_void_p()
+        self._check(self.lib.cusk_comm_create(self.h, int(rank), int(world), unique_id, C.byref(h)))
+        self.comm = h
+        self._check(self.lib.cusk_ctx_set_comm(self.h, h))
+
+    def detach_comm(self):
+        if getattr(self, "comm", None):
+            self.lib.cusk_ctx_set_comm(self.h, None)
+            self.lib.cusk_comm_destroy(self.comm)
+            self.comm = None
+
+    def comm_stats(self):
+        ms, by = C.c_double(0), C.c_int64(0)
+        self._check(self.lib.cusk_comm_stats(self.comm, C.byref(ms), C.byref(by)))
+        return dict(exchange_ms=ms.value, exchange_bytes=by.value)
 
     @property
     def stream(self):

@@ -498,12 +498,13 @@ static void run_level(const float *C, int n, int *G, int l, double th_level, boo
                       double th_het, const int *time_index, float *pMax, int *SepSet,
                       const std::vector<std::vector<int>> &adj, long long *tests_canonical,
                       long long *tests_executed, long long *singular, double near_band,
-                      std::vector<NearRec> *near)
+                      std::vector<NearRec> *near, int row_rem = 0, int row_mod = 1)
 {
     long long t_canon = 0, t_exec = 0;
     std::vector<unsigned char> removed((size_t)n * n, 0);  // directed: found from row X
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : t_canon, t_exec)
     for (int X = 0; X < n; X++) {
+        if (row_mod > 1 && (X % row_mod) != row_rem) continue;  // sharded emulation (orc_hetcor_level)
         const std::vector<int> &a = adj[X];
         const int d = (int)a.size();
         if (d <= l) {
@@ -727,6 +728,23 @@ void orc_hetcor_skeleton(const float *C, int n, int *G, const float *N, float th
         }
         *near_n = k;
     }
+}
+
+// One level l >= 1 of the hetcor engine restricted to the rows X with X % row_mod == row_rem, on the
+// adjacency G as it stands at the start of the level (compacted here).  Test scaffolding for the
+// edge-sharded multi-GPU mode: ranks run disjoint row sets, AND their G's, and must reach the
+// single-rank result (PC-stable).  Returns 0 when the level does not run (max degree - 1 < l,
+// src/hetcor-cuPC-S.cu:160-166), else 1.
+int orc_hetcor_level(const float *C, int n, int *G, const float *N, float th, int l, const int *time_index,
+                     int row_rem, int row_mod)
+{
+    std::vector<std::vector<int>> adj;
+    const int nprime = compact(G, n, adj);
+    if (nprime - 1 < l) return 0;
+    long long tc = 0, te = 0, singular = 0;
+    run_level(C, n, G, l, 0.0, true, N, (double)th, time_index, nullptr, nullptr, adj, &tc, &te, &singular, 0.0,
+              nullptr, row_rem, row_mod);
+    return 1;
 }
 
 // Exposed for tests: the two inverse restatements and unranking.

@@ -84,6 +84,13 @@ class Oracle:
                                      C.c_double(near_band), _p(near, c_double_p), cap, C.byref(near_n))
         return dict(G=G, l=l.value, stats=stats, near=near[: near_n.value])
 
+    def hetcor_level(self, Cm, G, N, th, l, time_index, row_rem=0, row_mod=1):
+        """one level l >= 1 on the rows X % row_mod == row_rem (sharded emulation); G is updated in place"""
+        n = Cm.shape[0]
+        ran = self.lib.orc_hetcor_level(_p(Cm, c_float_p), n, _p(G, c_int_p), _p(N, c_float_p), C.c_float(th), int(l),
+                                        _p(time_index, c_int_p), int(row_rem), int(row_mod))
+        return bool(ran)
+
     def bed_col_stats(self, bed, m, n):
         bed = np.ascontiguousarray(bed, np.uint8)
         means = np.zeros(m, np.float32)
