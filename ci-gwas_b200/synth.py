@@ -132,3 +132,66 @@ def random_bed(n_samples, m, stream=3, missing_rate=0.0, sub_block=50, copy_prob
         c4 = np.concatenate([codes, pad]).reshape(nb, 4)
         out[j] = c4[:, 0] | (c4[:, 1] << 2) | (c4[:, 2] << 4) | (c4[:, 3] << 6)
     return out
+
+
+def merged_correlation(loci=400, per_locus=50, p=17, stream=5, num_samples=458000, causal_per_trait=40,
+                       window=12, max_parents=4, wlo=0.6, whi=0.95, dtype=np.float32):
+    """BASELINE.json configs[4] (cuskss-merged): `loci` independent LD loci of `per_locus` selected markers
+    each, followed by p traits.  Same SEM as sem_correlation inside a locus; markers of different loci
+    are independent, so the population matrix is assembled locus by locus (no dense nv x nv product).
+    Sampling noise N(0, 1/num_samples) is added off the diagonal.  Returns C [nv, nv] float32."""
+    rng = rng_for(stream)
+    m = loci * per_locus
+    nv = m + p
+    A_loc = []
+    for _ in range(loci):
+        A = np.zeros((per_locus, per_locus), np.float64)
+        for i in range(per_locus):
+            row = np.zeros(per_locus, np.float64)
+            v = 0.0
+            if i > 0:
+                lo = max(i - window, 0)
+                k = min(int(rng.integers(1, max_parents + 1)), i - lo)
+                par = rng.choice(np.arange(lo, i), size=k, replace=False)
+                w = rng.uniform(wlo, whi, size=k) * rng.choice([-1.0, 1.0], size=k)
+                row = w @ A[par]
+                v = float(row @ row)
+                if v > 0.9:
+                    row *= np.sqrt(0.9 / v)
+                    v = 0.9
+            row[i] = np.sqrt(1.0 - v)
+            A[i] = row
+        A_loc.append(A)
+    # trait rows in the global noise basis (markers' noises, then the traits' own)
+    AT = np.zeros((p, nv), np.float64)
+    for t in range(p):
+        par = rng.choice(np.arange(m), size=min(causal_per_trait, m), replace=False)
+        w = rng.uniform(0.01, 0.05, size=par.size) * rng.choice([-1.0, 1.0], size=par.size)
+        row = np.zeros(nv, np.float64)
+        for i, wi in zip(par, w):
+            L, j = divmod(int(i), per_locus)
+            row[L * per_locus:(L + 1) * per_locus] += wi * A_loc[L][j]
+        for u in range(t):
+            if rng.random() < 0.3:
+                row = row + rng.uniform(-0.3, 0.3) * AT[u]
+        v = float(row @ row)
+        if v > 0.9:
+            row *= np.sqrt(0.9 / v)
+            v = 0.9
+        row[m + t] = np.sqrt(1.0 - v)
+        AT[t] = row
+    Cm = rng.standard_normal((nv, nv), dtype=np.float32)
+    Cm *= np.float32(1.0 / np.sqrt(float(num_samples)))
+    Cm = np.triu(Cm, 1)
+    Cm = Cm + Cm.T
+    for L in range(loci):
+        s = slice(L * per_locus, (L + 1) * per_locus)
+        Cm[s, s] += (A_loc[L] @ A_loc[L].T).astype(np.float32)
+        mt = (A_loc[L] @ AT[:, s].T).astype(np.float32)  # [per_locus, p]
+        Cm[s, m:] += mt
+        Cm[m:, s] += mt.T
+    Cm[m:, m:] += (AT @ AT.T).astype(np.float32)
+    np.clip(Cm, -0.999999, 0.999999, out=Cm)
+    np.fill_diagonal(Cm, 1.0)
+    Cm = np.triu(Cm) + np.triu(Cm, 1).T
+    return np.ascontiguousarray(Cm.astype(dtype))
