@@ -96,6 +96,7 @@ def cpu_port_tests_per_s(Cm, N, steps=1):
     th = orc.hetcor_threshold(ALPHA)
     G1 = np.ones((n, n), np.int32)
     ti = np.zeros(n, np.int32)
+    ti[n - P_TRAITS:] = 1  # cuskss: markers time 0, traits time 1
     times, tests = [], 0
     for _ in range(steps):
         t0 = time.perf_counter()
@@ -182,6 +183,11 @@ def main():
     dN = torch.from_numpy(N).cuda()
     rw = ctx.row_words(n)
     dbits = torch.zeros((n, rw), dtype=torch.int32, device="cuda")
+    # cuskss semantics: markers carry time index 0, traits 1 (cli.cpp:37-42, :219), so traits never
+    # enter the conditioning set of a marker-marker pair
+    ti = np.zeros(n, np.int32)
+    ti[M_MARKERS:] = 1
+    dT = torch.from_numpy(ti).cuda()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     # pinned host buffers for the end-to-end leg (the reference-facing call: host in, host out)
     hC = torch.from_numpy(Cm).pin_memory()
@@ -191,13 +197,15 @@ def main():
     torch.cuda.synchronize()
 
     def step_dev():
-        return ctx.hetcor_skeleton_dev(dC.data_ptr(), n, dbits.data_ptr(), True, dN.data_ptr(), 0.0, th, MAXLEVEL)
+        return ctx.hetcor_skeleton_dev(dC.data_ptr(), n, dbits.data_ptr(), True, dN.data_ptr(), 0.0, th, MAXLEVEL,
+                                       dT.data_ptr())
 
     def step_e2e():
         st = cigwas_b200.Stats()
         l = C.c_int(0)
         rc = lib.cusk_hetcor_skeleton(ctx.h, C.cast(hC.data_ptr(), fp), n, C.cast(hG.data_ptr(), ip), 0,
-                                      C.cast(hN.data_ptr(), fp), C.c_float(th), MAXLEVEL, None, C.byref(l),
+                                      C.cast(hN.data_ptr(), fp), C.c_float(th), MAXLEVEL,
+                                      ti.ctypes.data_as(ip), C.byref(l),
                                       C.byref(st))
         if rc != 0:
             raise RuntimeError(lib.cusk_last_error().decode())
@@ -230,7 +238,8 @@ def main():
         tests_total += sum(st["tests_executed"])
         alg_bytes += algorithmic_bytes(st["tests_executed"])
         ci_ms += sum(st["ci_kernel_ms"])
-        launches += 2 + 4 * MAXLEVEL + 2  # ess scan, level 0, (degree, plan, compact, CI) x 14, final degree + plan
+        # ess scan, level 0, (degree, plan, compact, items, CI) per level that ran, final degree + plan
+        launches += 2 + 5 * (st["levels_run"] - 1) + 2
         last_stats = st
     barrier()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
@@ -279,7 +288,8 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "cuskss single LD block 3000 markers + 17 traits (n_var 3017), max level 14, "
-                                   "alpha 1e-4, 458000 samples (BASELINE.json configs[1]); one block per GPU per step",
+                                   "alpha 1e-4, 458000 samples, time index markers 0 / traits 1 as `mps cuskss` sets it "
+                                   "(BASELINE.json configs[1]); one block per GPU per step",
                        "generator": dict(C2_KW, seed_stream="2+rank"), "l2": "flushed between timed iterations "
                        "(256 MB write)", "tests_per_block": tests_total // args.steps,
                        "tests_canonical_per_level": last_stats["tests_canonical"],
@@ -307,7 +317,6 @@ def main():
             if ref_lib.available():
                 ref = ref_lib.RefLib()
                 G1 = np.ones((n, n), np.int32)
-                ti = np.zeros(n, np.int32)
                 with quiet_stdout():
                     ref.hetcor_skeleton(Cm, G1, N, th, MAXLEVEL, ti)
                     t0 = time.perf_counter()

@@ -53,7 +53,15 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
             // one thread decodes the item (row lookup, C(d,l), rank range) for the whole CTA
             const int item = p.shard_rank + p.shard_world * atomicAdd(p.work_counter, 1);
             s_it.item = item;
-            if (item < nitems) {
+            if (item < nitems && item < p.item_cap) {
+                const int4 a4 = *(const int4 *)&p.items[item];
+                const ulonglong2 r2 = *(const ulonglong2 *)&p.items[item].R0;
+                s_it.X = a4.x;
+                s_it.d = a4.y;
+                s_it.row0 = a4.z;
+                s_it.R0 = r2.x;
+                s_it.R1 = r2.y;
+            } else if (item < nitems) {
                 int lo = 0, hi = n;  // largest X with itemstart[X] <= item
                 while (hi - lo > 1) {
                     const int mid = (lo + hi) >> 1;
@@ -100,8 +108,9 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         const size_t csub_bytes = (size_t)d * dpad * 4;
         int nw;
         bool staged;
-        // staging costs d^2 gathers: only worth it when the item runs a few times as many tests
-        const bool worth_staging = (R1 - R0) * (u64)(d - l) >= 3 * (u64)d * (u64)d;
+        // staging costs d^2 gathers spread over the CTA's 512 threads: for d <= 64 that is a couple of L2
+        // round trips; for larger rows it pays when the item runs a few times as many tests
+        const bool worth_staging = d <= 64 || (R1 - R0) * (u64)(d - l) >= 3 * (u64)d * (u64)d;
         if (worth_staging && csub_bytes + 8 * perwarp <= avail) {
             staged = true;
             const size_t q = (avail - csub_bytes) / perwarp;

@@ -131,9 +131,20 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         // upper-triangle tile list: A block tm = group tm; B block tn = groups 2tn, 2tn+1
         std::vector<int2> tiles;
         const int n_tm = (int)groups, n_tn = (int)((groups + 1) / 2);
-        for (int tn = n_tn - 1; tn >= 0; tn--)  // long rows of the triangle first
-            for (int tm = 0; tm < n_tm; tm++)
-                if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m) tiles.push_back({tm, tn});
+        // Tile order = the order CTAs take them (tile t runs on CTA t % grid, so 148 consecutive tiles
+        // are co-resident).  The triangle is walked in super-blocks of SB_M x SB_N tiles.  Default
+        // SB_M = all, SB_N = 1: a wave shares ONE B block through L2 and streams distinct A blocks from
+        // HBM.  Squarer super-blocks (16 x 9) should cut HBM traffic 4x on paper but measured worse
+        // (ncu: 518 GB read vs 374 GB, L2 hit 39 % vs 50 %, profiles/r1_gram_tile_order.txt): the CTAs
+        // that share a block drift apart by more k-steps than the L2 window holds.
+        static const int SB_M = [] { const char *e = getenv("CUSK_GRAM_SB_M"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 1 << 20; }();
+        static const int SB_N = [] { const char *e = getenv("CUSK_GRAM_SB_N"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 1; }();
+        for (int sn = ((n_tn - 1) / SB_N) * SB_N; sn >= 0; sn -= SB_N)  // long rows of the triangle first
+            for (int sm = 0; sm < n_tm; sm += SB_M)
+                for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
+                    for (int tm = sm; tm < std::min(sm + SB_M, n_tm); tm++)
+                        if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m)
+                            tiles.push_back({tm, tn});
         int2 *d_tiles = (int2 *)arena_take(ctx, sizeof(int2) * std::max<size_t>(tiles.size(), 1));
         if (!d_tiles) return CUSK_E_CUDA;
         CUSK_CUDA(cudaMemcpyAsync(d_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s));

@@ -20,7 +20,18 @@ struct GramParams {
     int mode;            // 0: sin(pi/2 tau_b) (cusk), 1: Pearson with the given means / stds
     const float *mean, *stdv;
     long long *tables;   // optional [m*(m-1)/2][9] exact contingency tables (tests), or nullptr
+    // marker x trait on the same tiles: B block `trait_tn` of the operand matrix holds, per trait t, the
+    // rows 8t..8t+3 = byte limbs of the trait values in offset fixed point (u = round(y 2^S) + 2^31, 0 where
+    // y is NaN) and row 8t+4 = [y not NaN]; -1: no trait block
+    int trait_tn;
+    int p;                      // traits (<= 32)
+    const double *trait_scale;  // [p] 2^-S
+    const double *Ty;           // [p] sum of valid y
+    const int *cnty;            // [p] number of valid y
+    float *mxp;                 // [m*p] out
 };
+
+#define CUSK_TC_MXP_MAX_TRAITS 32
 
 // row of (marker i, part a) in the padded indicator matrix
 __host__ __device__ inline size_t ind_row(int i, int a, int parts, int MI)

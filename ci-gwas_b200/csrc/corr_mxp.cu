@@ -220,3 +220,103 @@ int launch_mxp(cudaStream_t st, const unsigned char *bed, const float *phen, int
     }
     return CUSK_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-core route (north_star item 1: marker x trait as a dense contraction on tcgen05): the trait
+// values become uint8 operand rows next to the genotype indicator rows, so that
+//     sum_{k in class} y_k  =  2^-S ( sum_j 2^(8j) <I_class, limb_j>  -  2^31 <I_class, valid> )
+// with exact int32 dot products.  Fixed point: q = round(y 2^S), |q| < 2^31, S = 29 - floor(log2 max|y|)
+// per trait: the rounding error of a class sum is below 2^-S sqrt(n) ~ 1e-6 absolute on sums of order
+// n E|y| ~ 1e5, i.e. ~1e-11 relative -- five orders inside the 1e-6 bar, and tighter than the float
+// partial sums of mxp_tiled_kernel above.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) trait_scale_kernel(const float *__restrict__ phen, int n, int p,
+                                                          double *__restrict__ Ty, int *__restrict__ cnty,
+                                                          double *__restrict__ scale_inv, int *__restrict__ sexp)
+{
+    const int t = blockIdx.x;
+    double s = 0.0;
+    int c = 0;
+    float mx = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float y = phen[(size_t)t * n + i];
+        if (y == y) {
+            s += (double)y;
+            c++;
+            mx = fmaxf(mx, fabsf(y));
+        }
+    }
+    __shared__ double ss[8];
+    __shared__ int sc[8];
+    __shared__ float sm_[8];
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        c += __shfl_xor_sync(0xffffffffu, c, o);
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        ss[threadIdx.x >> 5] = s;
+        sc[threadIdx.x >> 5] = c;
+        sm_[threadIdx.x >> 5] = mx;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double S = 0;
+        int Cn = 0;
+        float M = 0.f;
+        for (int w = 0; w < 8; w++) {
+            S += ss[w];
+            Cn += sc[w];
+            M = fmaxf(M, sm_[w]);
+        }
+        Ty[t] = S;
+        cnty[t] = Cn;
+        const int e = (M > 0.f && M < 3.0e38f) ? ilogbf(M) : 0;
+        const int S_ = 29 - e;
+        sexp[t] = S_;
+        scale_inv[t] = ldexp(1.0, -S_);
+    }
+}
+
+// thread = 16 samples of one trait -> one 16-byte store into each of the trait's 5 operand rows
+__global__ void __launch_bounds__(256) trait_limbs_kernel(const float *__restrict__ phen, int n, size_t Kp,
+                                                          const int *__restrict__ sexp,
+                                                          unsigned char *__restrict__ rows)
+{
+    const int t = blockIdx.y;
+    const size_t chunk = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (chunk * 16 >= Kp) return;
+    const int S_ = sexp[t];
+    uint32_t o[5][4];
+#pragma unroll
+    for (int j = 0; j < 5; j++)
+#pragma unroll
+        for (int w = 0; w < 4; w++) o[j][w] = 0u;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const size_t s = chunk * 16 + i;
+        if (s >= (size_t)n) continue;
+        const float y = phen[(size_t)t * n + s];
+        if (!(y == y)) continue;
+        const long long q = llrint(ldexp((double)y, S_));
+        const uint32_t u = (uint32_t)(q + 2147483648LL);
+        const int w = i >> 2, sh = 8 * (i & 3);
+        o[0][w] |= (u & 0xffu) << sh;
+        o[1][w] |= ((u >> 8) & 0xffu) << sh;
+        o[2][w] |= ((u >> 16) & 0xffu) << sh;
+        o[3][w] |= ((u >> 24) & 0xffu) << sh;
+        o[4][w] |= 1u << sh;
+    }
+#pragma unroll
+    for (int j = 0; j < 5; j++)
+        *(uint4 *)(rows + ((size_t)t * 8 + j) * Kp + chunk * 16) = make_uint4(o[j][0], o[j][1], o[j][2], o[j][3]);
+}
+
+// rows: first row of the trait block (256 zero-initialised rows of Kp bytes)
+void launch_trait_rows(cudaStream_t st, const float *phen, int n, int p, size_t Kp, unsigned char *rows, double *d_Ty,
+                       int *d_cnty, double *d_scale_inv, int *d_sexp)
+{
+    trait_scale_kernel<<<p, 256, 0, st>>>(phen, n, p, d_Ty, d_cnty, d_scale_inv, d_sexp);
+    dim3 grid((unsigned)((Kp / 16 + 255) / 256), p);
+    trait_limbs_kernel<<<grid, 256, 0, st>>>(phen, n, Kp, d_sexp, rows);
+}

@@ -26,6 +26,8 @@ void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, in
 void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits);
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
+void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
+                  int l, const LevelCtl *ctl, CiItem *items, int item_cap);
 void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits);
 
 extern "C" size_t cusk_row_words(int n) { return (size_t)(n + 31) / 32; }
@@ -112,6 +114,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         }
     }
     size_t nnz0 = 0;
+    // plan_kernel aims at 148 * 16 * world items per level, plus at most one short item per row
+    const int item_cap = n + 148 * 16 * ((sh ? sh->world : 1) + 1);
+    CiItem *d_items = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
+    if (!d_items) return CUSK_E_CUDA;
 
     cudaEvent_t *ev = ctx->ev;
     CUSK_CUDA(cudaEventRecord(ev[0], st));
@@ -172,6 +178,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             if (done) break;
         }
         launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl);
+        launch_items(st, d_deg, d_rowptr, d_itemstart, d_chunk, n, l, ctl, d_items, item_cap);
         CiParams p;
         p.C = a.dC;
         p.N = a.het ? dN : nullptr;
@@ -190,6 +197,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.minkey = d_minkey;
         p.th_het = (double)a.th_het;
         p.smem_bytes = smem_bytes;
+        p.items = d_items;
+        p.item_cap = item_cap;
         p.shard_rank = sh ? sh->rank : 0;
         p.shard_world = sh ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));

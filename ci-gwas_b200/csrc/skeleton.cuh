@@ -22,6 +22,13 @@ struct LevelCtl {
     double T2;       // tanh(threshold)^2 of the level (non-het and uniform-N het)
 };
 
+// One work item of the CI kernel, decoded once per level by items_kernel (the CI kernel's CTAs then
+// fetch an item with one atomic and one 32-byte load instead of a binary search over the rows).
+struct __align__(16) CiItem {
+    int X, d, row0, pad;
+    u64 R0, R1;
+};
+
 struct CiParams {
     const float *C;
     const float *N;          // het, general N; nullptr when uniform
@@ -38,5 +45,7 @@ struct CiParams {
     u64 *minkey;             // non-het
     double th_het;
     int smem_bytes;
+    const CiItem *items;     // decoded items [0, item_cap); items beyond the cap are decoded on the fly
+    int item_cap;
     int shard_rank, shard_world;  // this launch takes items rank, rank + world, ... (1 GPU: 0, 1)
 };

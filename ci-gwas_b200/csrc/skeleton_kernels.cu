@@ -108,7 +108,8 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
                                                     int *__restrict__ rowptr, int *__restrict__ itemstart,
                                                     u64 *__restrict__ chunk, LevelCtl *ctl,
                                                     const LevelCtl *prev, double th_level, double th_het,
-                                                    float n_uniform, int *work_counter, int world)
+                                                    float n_uniform, int *work_counter, int world,
+                                                    int ipsm_shallow, int ipsm_deep)
 {
     __shared__ u64 s_warp[33];
     __shared__ int s_maxdeg;
@@ -171,8 +172,13 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         ctl->T2 = t * t;
         // aim at ~16 items per SM; small levels are cut finer (they are latency-bound: the
         // more warps share a hub row's conditioning sets the shorter the critical path)
-        u64 target = tot_tests / ((u64)148 * 16 * (u64)world);
-        if (target < 512) target = 512;
+        // Items per SM: the first two levels are throughput-bound with very uneven rows and want many
+        // items for balance; from level 3 on an item's cost is dominated by the per-prefix factorisation,
+        // which consecutive conditioning sets share, so few large items win (sweep on the C2 block:
+        // profiles/r1_item_floor_sweep.txt).
+        const u64 per_sm = (u64)(l <= 2 ? ipsm_shallow : ipsm_deep);
+        u64 target = tot_tests / ((u64)148 * per_sm * (u64)world);
+        if (target < 32) target = 32;
         s_target = target;
         *work_counter = 0;
     }
@@ -194,7 +200,8 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
             // an item re-stages the row's d x d submatrix: keep at least ~4 tests per staged entry
             u64 tgt = target;
             // (rows too large to stage gather from L2 per test and have no such cost)
-            const u64 stage_cost = (d <= 200) ? 4 * (u64)d * (u64)d : 0;
+            // (rows with d <= 64 stage in a couple of round trips whatever the item size)
+            const u64 stage_cost = (d > 64 && d <= 200) ? 4 * (u64)d * (u64)d : 0;
             if (tgt < stage_cost) tgt = stage_cost;
             items = (tests + tgt - 1) / tgt;
             if (items > c) items = c;
@@ -214,6 +221,37 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         itemstart[n] = (int)carry;
         ctl->nitems = (int)carry;
     }
+}
+
+// Decodes the level's work items (row, degree, CSR offset, rank range) in parallel: thread = item.
+__global__ void __launch_bounds__(256) items_kernel(const int *__restrict__ deg, const int *__restrict__ rowptr,
+                                                    const int *__restrict__ itemstart, const u64 *__restrict__ chunk,
+                                                    int n, int l, const LevelCtl *ctl, CiItem *__restrict__ items,
+                                                    int item_cap)
+{
+    if (ctl->done) return;
+    const int item = blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= ctl->nitems || item >= item_cap) return;
+    int lo = 0, hi = n;  // largest X with itemstart[X] <= item
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (itemstart[mid] <= item)
+            lo = mid;
+        else
+            hi = mid;
+    }
+    const int dd = deg[lo];
+    const u64 nc = binom64(dd, l);
+    const u64 chx = chunk[lo];
+    const u64 r0 = (u64)(item - itemstart[lo]) * chx;
+    CiItem it;
+    it.X = lo;
+    it.d = dd;
+    it.row0 = rowptr[lo];
+    it.pad = 0;
+    it.R0 = r0;
+    it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
+    items[item] = it;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -421,8 +459,25 @@ void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int
                  LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
                  int *work_counter, int world)
 {
+    // tuning knobs: work items per SM at levels 1-2 and at levels >= 3
+    static const int ipsm_shallow = [] {
+        const char *e = getenv("CUSK_ITEMS_PER_SM_SHALLOW");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 ? v : 16;
+    }();
+    static const int ipsm_deep = [] {
+        const char *e = getenv("CUSK_ITEMS_PER_SM_DEEP");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 ? v : 2;
+    }();
     plan_kernel<<<1, 1024, 0, st>>>(deg, n, l, rowptr, itemstart, chunk, ctl, prev, th_level, th_het,
-                                    n_uniform, work_counter, world);
+                                    n_uniform, work_counter, world, ipsm_shallow, ipsm_deep);
+}
+
+void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
+                  int l, const LevelCtl *ctl, CiItem *items, int item_cap)
+{
+    items_kernel<<<(item_cap + 255) / 256, 256, 0, st>>>(deg, rowptr, itemstart, chunk, n, l, ctl, items, item_cap);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,

@@ -134,7 +134,7 @@ def random_bed(n_samples, m, stream=3, missing_rate=0.0, sub_block=50, copy_prob
     return out
 
 
-def merged_correlation(loci=400, per_locus=50, p=17, stream=5, num_samples=458000, causal_per_trait=40,
+def merged_correlation(loci=400, per_locus=50, p=17, stream=5, num_samples=458000, causal_per_trait=12,
                        window=12, max_parents=4, wlo=0.6, whi=0.95, dtype=np.float32):
     """BASELINE.json configs[4] (cuskss-merged): `loci` independent LD loci of `per_locus` selected markers
     each, followed by p traits.  Same SEM as sem_correlation inside a locus; markers of different loci
