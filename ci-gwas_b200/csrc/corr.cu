@@ -15,6 +15,8 @@ void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size
                    size_t Kp, unsigned char *ind);
 int launch_mxp(cudaStream_t st, const unsigned char *bed, const float *phen, int m, int n, int p, size_t col_bytes,
                const float *mean, const float *stdv, float *out, bool any_missing, double *d_Ty, int *d_cnty);
+void launch_trait_rows(cudaStream_t st, const float *phen, int n, int p, size_t Kp, unsigned char *rows, double *d_Ty,
+                       int *d_cnty, double *d_scale_inv, int *d_sexp);
 void launch_pxp(cudaStream_t st, const float *phen, int n, int p, float *out_upper, float *Csq, int ldc, int m_off);
 void launch_pack_upper(cudaStream_t st, const float *Csq, int m, int ldc, float *upper);
 void launch_set_diag(cudaStream_t st, float *Csq, int nvar, int ldc);
@@ -93,19 +95,31 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         CUSK_CUDA(cudaStreamSynchronize(s));
         for (size_t i = 0; i < m; i++) any_missing |= h_counts[4 * i + 3] != 0;
     }
-    // ---- marker x trait and trait x trait (CUDA cores) -------------------------------------------------
+    // ---- marker x trait -------------------------------------------------------------------------------
+    // Default: on the tensor cores, as extra tiles of the Gram kernel below (trait values as uint8 limb
+    // rows).  CUDA-core kernel (corr_mxp.cu) for more than 32 traits or with CUSK_MXP_CUDA_CORES=1.
+    static const bool force_cuda_cores = getenv("CUSK_MXP_CUDA_CORES") != nullptr;
+    const bool tc_mxp = p > 0 && m > 0 && p <= CUSK_TC_MXP_MAX_TRAITS && !force_cuda_cores;
+    const bool tc_traits = tc_mxp && !mxp_ready;  // trait tiles to compute in this call
+    double *d_Ty = nullptr, *d_scale = nullptr;
+    int *d_cnty = nullptr, *d_sexp = nullptr;
     if (p > 0 && m > 0) {
-        double *d_Ty = (double *)arena_take(ctx, sizeof(double) * p);
-        int *d_cnty = (int *)arena_take(ctx, sizeof(int) * p);
-        if (!d_Ty || !d_cnty) return CUSK_E_CUDA;
-        t_mxp.start();
-        if (!mxp_ready) {
-            int rc = launch_mxp(s, d_bed, d_phen, (int)m, (int)n, (int)p, col_bytes, d_mean, d_std, d_mxp, any_missing,
-                                d_Ty, d_cnty);
-            if (rc) return rc;
+        d_Ty = (double *)arena_take(ctx, sizeof(double) * p);
+        d_cnty = (int *)arena_take(ctx, sizeof(int) * p);
+        d_scale = (double *)arena_take(ctx, sizeof(double) * p);
+        d_sexp = (int *)arena_take(ctx, sizeof(int) * p);
+        if (!d_Ty || !d_cnty || !d_scale || !d_sexp) return CUSK_E_CUDA;
+        if (!tc_mxp) {
+            t_mxp.start();
+            if (!mxp_ready) {
+                int rc = launch_mxp(s, d_bed, d_phen, (int)m, (int)n, (int)p, col_bytes, d_mean, d_std, d_mxp,
+                                    any_missing, d_Ty, d_cnty);
+                if (rc) return rc;
+            }
+            if (d_Csq)
+                scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
+            t_mxp.stop();
         }
-        if (d_Csq) scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
-        t_mxp.stop();
     }
     if (p > 1 && (d_pxp_out || d_Csq)) {
         t_pxp.start();
@@ -115,22 +129,34 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
     CUSK_CUDA(cudaGetLastError());
     if (st) st->bed_bytes = (int64_t)(m * col_bytes);
     // ---- marker x marker: indicator Gram on the tensor cores ----------------------------------------
-    if (want_mxm && m > 1) {
+    const bool mxm_tiles = want_mxm && m > 1;
+    if (mxm_tiles || tc_traits) {
         const int parts = any_missing ? 3 : 2;
         const int MI = 128 / parts;
         const size_t groups = (m + MI - 1) / MI;
         const size_t rows = ((groups * 128 + 255) / 256) * 256;
         const size_t Kp = ((n + 127) / 128) * 128;
-        unsigned char *d_ind = (unsigned char *)arena_take(ctx, rows * Kp);
+        // operand matrix: the genotype indicator rows, then (tensor-core mxp) one 256-row block of trait rows
+        const size_t rows_total = rows + (tc_traits ? 256 : 0);
+        const int trait_tn = tc_traits ? (int)(rows / 256) : -1;
+        unsigned char *d_ind = (unsigned char *)arena_take(ctx, rows_total * Kp);
         if (!d_ind) return CUSK_E_CUDA;
         t_decode.start();
         // padding rows of every group and the tail of K must be zero
-        CUSK_CUDA(cudaMemsetAsync(d_ind, 0, rows * Kp, s));
+        CUSK_CUDA(cudaMemsetAsync(d_ind, 0, rows_total * Kp, s));
         launch_decode(s, d_bed, (int)m, (int)n, col_bytes, parts, MI, Kp, d_ind);
         t_decode.stop();
+        if (tc_traits) {
+            t_mxp.start();
+            launch_trait_rows(s, d_phen, (int)n, (int)p, Kp, d_ind + rows * Kp, d_Ty, d_cnty, d_scale, d_sexp);
+            t_mxp.stop();
+        }
         // upper-triangle tile list: A block tm = group tm; B block tn = groups 2tn, 2tn+1
         std::vector<int2> tiles;
         const int n_tm = (int)groups, n_tn = (int)((groups + 1) / 2);
+        if (tc_traits)
+            for (int tm = 0; tm < n_tm; tm++)
+                if ((size_t)tm * MI < m) tiles.push_back({tm, trait_tn});
         // Tile order = the order CTAs take them (tile t runs on CTA t % grid, so 148 consecutive tiles
         // are co-resident).  The triangle is walked in super-blocks of SB_M x SB_N tiles.  Default
         // SB_M = all, SB_N = 1: a wave shares ONE B block through L2 and streams distinct A blocks from
@@ -139,7 +165,7 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         // that share a block drift apart by more k-steps than the L2 window holds.
         static const int SB_M = [] { const char *e = getenv("CUSK_GRAM_SB_M"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 1 << 20; }();
         static const int SB_N = [] { const char *e = getenv("CUSK_GRAM_SB_N"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 1; }();
-        for (int sn = ((n_tn - 1) / SB_N) * SB_N; sn >= 0; sn -= SB_N)  // long rows of the triangle first
+        for (int sn = ((n_tn - 1) / SB_N) * SB_N; mxm_tiles && sn >= 0; sn -= SB_N)  // long rows of the triangle first
             for (int sm = 0; sm < n_tm; sm += SB_M)
                 for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
                     for (int tm = sm; tm < std::min(sm + SB_M, n_tm); tm++)
@@ -151,7 +177,7 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         float *d_out = d_Csq;
         int ldc = nvar;
         CUtensorMap map_a, map_b;
-        int rc = gram_make_maps(d_ind, rows, Kp, &map_a, &map_b);
+        int rc = gram_make_maps(d_ind, rows_total, Kp, &map_a, &map_b);
         if (rc) return rc;
         GramParams gp = {};
         gp.parts = parts;
@@ -168,10 +194,18 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         gp.mean = d_mean;
         gp.stdv = d_std;
         gp.tables = d_tables;
+        gp.trait_tn = trait_tn;
+        gp.p = (int)p;
+        gp.trait_scale = d_scale;
+        gp.Ty = d_Ty;
+        gp.cnty = d_cnty;
+        gp.mxp = d_mxp;
         t_gram.start();
         rc = launch_gram(s, map_a, map_b, gp, std::min<int>(ctx->sm_count, (int)tiles.size()));
         if (rc) return rc;
         t_gram.stop();
+        if (tc_mxp && d_Csq)
+            scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
         CUSK_CUDA(cudaGetLastError());
         CUSK_CUDA(cudaStreamSynchronize(s));  // the host tile list must outlive the copy
         if (st) {

@@ -232,6 +232,49 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + (uint32_t)(as * TILE_N) + ((uint32_t)(q * 32) << 16);
+            if (tile.y == p.trait_tn) {
+                // ---- marker x trait tile: columns 8t..8t+4 = <row, limb_0..3>, <row, valid> of trait t ----
+                // (replaces bed_marker_phen_corr_pearson_scan, src/corr_kernels.cu:157-238:
+                //  r = (sum v g y - mean_g sum v y) / (sum v * std_g))
+                double *sS = (double *)epi;           // [128 rows][2 traits] class sums of y
+                int *sC = (int *)(sS + 2 * TILE_M);   // [128 rows][2 traits] class counts
+                for (int c = 0; 2 * c < p.p; c++) {
+                    int v[16];
+                    tmem_ld16(tmem_d + (uint32_t)(c * 16), v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int tt = 0; tt < 2; tt++) {
+                        const int t = 2 * c + tt;
+                        const long long sq = (long long)v[8 * tt] + ((long long)v[8 * tt + 1] << 8) +
+                                             ((long long)v[8 * tt + 2] << 16) + ((long long)v[8 * tt + 3] << 24) -
+                                             ((long long)v[8 * tt + 4] << 31);
+                        sS[row * 2 + tt] = (t < p.p) ? (double)sq * p.trait_scale[t] : 0.0;
+                        sC[row * 2 + tt] = v[8 * tt + 4];
+                    }
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    {
+                        const int il = et >> 1, tt = et & 1;
+                        const int t = 2 * c + tt, i = tile.x * MI + il;
+                        if (il < MI && i < p.m && t < p.p) {
+                            double s1, s2, sy, sv;
+                            if (parts == 2) {  // no missing call in the block: rows [g==1], [g==2]
+                                s1 = sS[(2 * il) * 2 + tt];
+                                s2 = sS[(2 * il + 1) * 2 + tt];
+                                sy = p.Ty[t];
+                                sv = (double)p.cnty[t];
+                            } else {           // rows [valid], [g==1], [g==2]
+                                sy = sS[(3 * il) * 2 + tt];
+                                sv = (double)sC[(3 * il) * 2 + tt];
+                                s1 = sS[(3 * il + 1) * 2 + tt];
+                                s2 = sS[(3 * il + 2) * 2 + tt];
+                            }
+                            const double r = (s1 + 2.0 * s2 - (double)p.mean[i] * sy) / (sv * (double)p.stdv[i]);
+                            p.mxp[(size_t)i * p.p + t] = (float)r;
+                        }
+                    }
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+            } else
             for (int g = 0; g < 2; g++) {                       // the two 128-row groups of the B block
                 const int jbase_group = (2 * tile.y + g) * MI;  // first marker of the group
                 if (jbase_group >= p.m) continue;
