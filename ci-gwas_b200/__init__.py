@@ -10,6 +10,7 @@ from .lib import (  # noqa: F401
     Stats,
     build_library,
     comm_unique_id,
+    local_group,
     hetcor_threshold,
     library_path,
     load_library,

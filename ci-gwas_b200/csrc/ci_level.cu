@@ -360,6 +360,7 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
                             if (HET) {
                                 atomicAnd(&p.bits[(size_t)X * p.rw + (Y >> 5)], ~(1u << (Y & 31)));
                                 atomicAnd(&p.bits[(size_t)Y * p.rw + (X >> 5)], ~(1u << (X & 31)));
+                                if (p.removed) p.removed[row0 + yc] = 1;
                             } else {
                                 const u64 R = Rbase + (u64)(z4 + q - zfirst);
                                 atomicMin(&p.minkey[row0 + yc], R);

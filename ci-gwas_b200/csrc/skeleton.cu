@@ -29,6 +29,8 @@ int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
 void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
                   int l, const LevelCtl *ctl, CiItem *items, int item_cap);
 void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits);
+void launch_apply_removed(cudaStream_t st, const unsigned char *flags, int world, size_t stride, int n, int rw,
+                          const int *rowptr, const int *deg, const int *adj, uint32_t *bits);
 
 extern "C" size_t cusk_row_words(int n) { return (size_t)(n + 31) / 32; }
 
@@ -103,17 +105,14 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
 
     // edge-sharded mode: every rank holds the whole problem and takes every world-th work item
     ShardLink *sh = (ctx->shard && ctx->shard->world > 1) ? ctx->shard : nullptr;
-    uint32_t *d_gather = nullptr;
-    const size_t bit_words = (size_t)n * rw;
+    // het engine: what a rank removed in a level travels as one byte per slot of the level's CSR
+    // (nnz_l bytes per rank instead of the n * rw word bitmap), all-gathered and applied by every rank
+    unsigned char *d_removed = nullptr, *d_gather = nullptr;
+    size_t flag_stride = 0, nnz_l = 0;
     if (sh) {
         sh->exchange_ms = 0.0;
         sh->exchange_bytes = 0;
-        if (a.het) {
-            d_gather = (uint32_t *)arena_take(ctx, bit_words * 4 * (size_t)sh->world);
-            if (!d_gather) return CUSK_E_CUDA;
-        }
     }
-    size_t nnz0 = 0;
     // plan_kernel aims at 148 * 16 * world items per level, plus at most one short item per row
     const int item_cap = n + 148 * 16 * ((sh ? sh->world : 1) + 1);
     CiItem *d_items = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
@@ -157,7 +156,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
             CUSK_CUDA(cudaStreamSynchronize(st));
             const size_t nnz = (size_t)h.nnz;
-            nnz0 = nnz;
+
             d_adj = (int *)arena_take(ctx, sizeof(int) * std::max<size_t>(nnz, 1));
             if (!d_adj) return CUSK_E_CUDA;
             if (!a.het) {
@@ -169,13 +168,21 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
                     if (!d_seps) return CUSK_E_CUDA;
                 }
             }
+            if (sh && a.het) {
+                flag_stride = (nnz + 15) & ~(size_t)15;
+                d_removed = (unsigned char *)arena_take(ctx, std::max<size_t>(flag_stride, 16));
+                d_gather = (unsigned char *)arena_take(ctx, std::max<size_t>(flag_stride, 16) * (size_t)sh->world);
+                if (!d_removed || !d_gather) return CUSK_E_CUDA;
+            }
         }
         if (sh) {
-            // the ranks must agree on when to stop exchanging: read the level's verdict
-            int done = 0;
-            CUSK_CUDA(cudaMemcpyAsync(&done, &ctl->done, sizeof(int), cudaMemcpyDeviceToHost, st));
+            // the ranks must agree on when to stop exchanging: read the level's verdict (and its CSR size)
+            LevelCtl h;
+            CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
             CUSK_CUDA(cudaStreamSynchronize(st));
-            if (done) break;
+            if (h.done) break;
+            nnz_l = (size_t)h.nnz;
+            if (d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, (nnz_l + 15) & ~(size_t)15, st));
         }
         launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl);
         launch_items(st, d_deg, d_rowptr, d_itemstart, d_chunk, n, l, ctl, d_items, item_cap);
@@ -199,6 +206,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.smem_bytes = smem_bytes;
         p.items = d_items;
         p.item_cap = item_cap;
+        p.removed = d_removed;
         p.shard_rank = sh ? sh->rank : 0;
         p.shard_world = sh ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
@@ -212,12 +220,14 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             const auto t0 = std::chrono::steady_clock::now();
             int xrc;
             if (a.het) {
-                xrc = sh->allgather(sh->user, a.dbits, d_gather, bit_words * 4, st);
-                if (!xrc) launch_and_reduce(st, d_gather, sh->world, bit_words, a.dbits);
-                sh->exchange_bytes += bit_words * 4 * (size_t)sh->world;
+                const size_t cnt = (nnz_l + 15) & ~(size_t)15;
+                xrc = sh->allgather(sh->user, d_removed, d_gather, cnt, st);
+                if (!xrc)
+                    launch_apply_removed(st, d_gather, sh->world, cnt, n, rw, d_rowptr, d_deg, d_adj, a.dbits);
+                sh->exchange_bytes += cnt * (size_t)sh->world;
             } else {
-                xrc = sh->allreduce_min_u64(sh->user, d_minkey, nnz0, st);
-                sh->exchange_bytes += nnz0 * 8;
+                xrc = sh->allreduce_min_u64(sh->user, d_minkey, nnz_l, st);
+                sh->exchange_bytes += nnz_l * 8;
             }
             if (xrc) {
                 cusk_set_error("skeleton: exchange step of level %d failed (rc %d)", l, xrc);

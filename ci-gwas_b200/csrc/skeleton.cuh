@@ -47,5 +47,6 @@ struct CiParams {
     int smem_bytes;
     const CiItem *items;     // decoded items [0, item_cap); items beyond the cap are decoded on the fly
     int item_cap;
+    unsigned char *removed;       // edge-sharded het engine: removed[slot of (X,Y) in the level's CSR] = 1
     int shard_rank, shard_world;  // this launch takes items rank, rank + world, ... (1 GPU: 0, 1)
 };

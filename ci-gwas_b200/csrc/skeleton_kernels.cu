@@ -56,6 +56,85 @@ __global__ void __launch_bounds__(256) level0_kernel(const float *__restrict__ C
 }
 
 // ---------------------------------------------------------------------------------------------
+// Level 0, tiled over the upper triangle (no candidate matrix).  One warp owns a 32 x 32 tile
+// (rows R0.., columns C0.., R0 <= C0): lane c reads C[R0+i][C0+c] for i = 0..31 (coalesced 128 B
+// rows), the ballot of row i is the adjacency word (R0+i, C0/32) and lane c collects its own
+// decisions into the mirrored word (C0+c, R0/32), so every pair is read and tested once and the
+// lower triangle is never touched: 2 n^2 bytes of C [+ 2 n^2 of N] read, n^2/8 written.
+// Het engine: the decision is taken in FP32 when z and the threshold differ by more than 1e-3
+// relative (FP32 evaluation error is < 1e-6), otherwise - and for any non-finite operand - by the
+// FP64 expression of level0_kernel, so the result is that of the FP64 expression everywhere.
+// ---------------------------------------------------------------------------------------------
+template <bool HET>
+__global__ void __launch_bounds__(256) level0_tile_kernel(const float *__restrict__ C,
+                                                          const float *__restrict__ N, float n_uniform, int n,
+                                                          int rw, double th, uint32_t *__restrict__ bits,
+                                                          float *__restrict__ pMax)
+{
+    __shared__ float s_z[HET ? 1 : 8][HET ? 1 : 32][HET ? 1 : 33];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int tr = blockIdx.y;
+    const int tc = blockIdx.x * 8 + wid;
+    if (tc < tr || tc >= rw) return;
+    const int R0 = tr * 32, C0 = tc * 32;
+    const int c = C0 + lane;
+    const bool diag = (tr == tc);
+    const float thf = (float)th;
+    const float t_uni = HET ? thf * rsqrtf(n_uniform - 3.0f) : 0.f;
+    const double th_uni = HET ? th / sqrt((double)n_uniform - 3.0) : th;
+    uint32_t my_row_word = 0;  // word (R0 + lane, tc)
+    uint32_t my_col_word = 0;  // word (C0 + lane, tr)
+#pragma unroll 8
+    for (int i = 0; i < 32; i++) {
+        const int r = R0 + i;
+        bool keep = false;
+        float zf_out = 0.f;
+        if (r < n && c < n && r < c) {
+            const size_t ix = (size_t)r * n + c;
+            const float rho = __ldg(&C[ix]);
+            if (HET) {
+                const float nn = N ? __ldg(&N[ix]) : n_uniform;
+                const float zf = fabsf(0.5f * logf(fabsf((1.0f + rho) / (1.0f - rho))));
+                const float tf = N ? thf * rsqrtf(nn - 3.0f) : t_uni;
+                if (fabsf(zf - tf) > 1e-3f * tf + 1e-6f) {
+                    keep = !(zf < tf);
+                } else {
+                    const double z = fisher_z((double)rho);
+                    const double loc_th = N ? th / sqrt((double)nn - 3.0) : th_uni;
+                    keep = !(z < loc_th);
+                }
+            } else {
+                const double z = fisher_z((double)rho);
+                keep = !(z < th);
+                zf_out = keep ? 0.f : (float)z;
+            }
+        }
+        if (!HET && pMax) {
+            if (r < n && c < n && (r < c || (diag && r == c))) pMax[(size_t)r * n + c] = zf_out;
+            s_z[wid][i][lane] = zf_out;
+        }
+        const uint32_t w = __ballot_sync(0xffffffffu, keep);
+        if (lane == i) my_row_word = w;
+        my_col_word |= (keep ? 1u : 0u) << i;
+    }
+    if (diag) {
+        // both triangles of the diagonal tile come from its upper entries
+        if (R0 + lane < n) bits[(size_t)(R0 + lane) * rw + tc] = my_row_word | my_col_word;
+    } else {
+        if (R0 + lane < n) bits[(size_t)(R0 + lane) * rw + tc] = my_row_word;
+        if (c < n) bits[(size_t)c * rw + tr] = my_col_word;
+    }
+    if (!HET && pMax) {
+        __syncwarp();
+        // mirrored pMax entries, written row-wise: row C0 + j, columns R0 + lane
+        for (int j = 0; j < 32; j++) {
+            const int rr = C0 + j, cc = R0 + lane;
+            if (rr < n && cc < n && cc < rr) pMax[(size_t)rr * n + cc] = s_z[wid][lane][j];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Degrees: one warp per row, popcount over the bitmap row.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) degree_kernel(const uint32_t *__restrict__ bits, int n, int rw,
@@ -443,6 +522,14 @@ __global__ void __launch_bounds__(256) ess_minmax_kernel(const float *__restrict
 void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, float n_uniform, const int *G_in,
                    int n, int rw, double th, uint32_t *bits, float *pMax)
 {
+    if (!G_in) {
+        dim3 tg((rw + 7) / 8, rw);
+        if (het)
+            level0_tile_kernel<true><<<tg, 256, 0, st>>>(C, N, n_uniform, n, rw, th, bits, pMax);
+        else
+            level0_tile_kernel<false><<<tg, 256, 0, st>>>(C, N, n_uniform, n, rw, th, bits, pMax);
+        return;
+    }
     dim3 grid((rw + 7) / 8, n);
     if (het)
         level0_kernel<true><<<grid, 256, 0, st>>>(C, N, n_uniform, G_in, n, rw, th, bits, pMax);
@@ -527,6 +614,33 @@ __global__ void __launch_bounds__(256) and_reduce_kernel(const uint32_t *__restr
         bits[i] = v;
     }
 }
+// edge-sharded het engine: flags[r][slot] = 1 where rank r removed the edge of CSR slot `slot` of this level;
+// one warp per row clears both adjacency bits of every flagged slot (idempotent on the removing rank).
+__global__ void __launch_bounds__(256) apply_removed_kernel(const unsigned char *__restrict__ flags, int world,
+                                                            size_t stride, int n, int rw,
+                                                            const int *__restrict__ rowptr, const int *__restrict__ deg,
+                                                            const int *__restrict__ adj, uint32_t *__restrict__ bits)
+{
+    const int lane = threadIdx.x & 31;
+    const int X = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (X >= n) return;
+    const int r0 = rowptr[X], d = deg[X];
+    for (int a = lane; a < d; a += 32) {
+        unsigned f = 0;
+        for (int r = 0; r < world; r++) f |= flags[(size_t)r * stride + r0 + a];
+        if (f) {
+            const int Y = adj[r0 + a];
+            atomicAnd(&bits[(size_t)X * rw + (Y >> 5)], ~(1u << (Y & 31)));
+            atomicAnd(&bits[(size_t)Y * rw + (X >> 5)], ~(1u << (X & 31)));
+        }
+    }
+}
+void launch_apply_removed(cudaStream_t st, const unsigned char *flags, int world, size_t stride, int n, int rw,
+                          const int *rowptr, const int *deg, const int *adj, uint32_t *bits)
+{
+    apply_removed_kernel<<<(n + 7) / 8, 256, 0, st>>>(flags, world, stride, n, rw, rowptr, deg, adj, bits);
+}
+
 void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits)
 {
     const int grid = (int)std::min<size_t>((words + 255) / 256, 148 * 8);

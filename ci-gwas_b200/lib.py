@@ -137,6 +137,21 @@ def mps_path():
     return os.path.join(_HERE, "mps")
 
 
+def local_group(ctxs):
+    """One process, one thread per context: in-process exchange by peer copies (the contexts may share a
+    device).  Every context of the group must then make the same skeleton call from its own thread."""
+    lib = ctxs[0].lib
+    world = len(ctxs)
+    hs = (C.c_void_p * world)(*[c.h for c in ctxs])
+    out = (C.c_void_p * world)()
+    lib.cusk_comm_create_local.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p)]
+    rc = lib.cusk_comm_create_local(hs, world, out)
+    if rc != 0:
+        raise CuskError(f"rc={rc}: {lib.cusk_last_error().decode()}")
+    for c, h in zip(ctxs, out):
+        c.adopt_comm(C.c_void_p(h))
+
+
 def comm_unique_id():
     """128-byte NCCL unique id; create it on one rank and broadcast it to the others."""
     buf = C.create_string_buffer(128)
@@ -193,6 +208,11 @@ class Context:
         self._check(self.lib.cusk_comm_create(self.h, int(rank), int(world), unique_id, C.byref(h)))
         self.comm = h
         self._check(self.lib.cusk_ctx_set_comm(self.h, h))
+
+    def adopt_comm(self, handle):
+        """Attaches a communicator made elsewhere (local_group below)."""
+        self.comm = handle
+        self._check(self.lib.cusk_ctx_set_comm(self.h, handle))
 
     def detach_comm(self):
         if getattr(self, "comm", None):

@@ -149,7 +149,7 @@ int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, const float *
 
 /* ---- multi-GPU: one skeleton sharded over several GPUs (cuskss --marker-indices) ------
  * The level-l work items are dealt round-robin to the ranks; after each level the ranks exchange what
- * they removed (NCCL all-gather of the adjacency bitmaps + AND for the summary-statistic engine,
+ * they removed (NCCL all-gather of one removed-flag byte per CSR slot for the summary-statistic engine,
  * all-reduce MIN of the separating-set ranks for the individual-level engine), so every rank returns
  * the same graph as a single-GPU call.  The reference has no multi-GPU path (nothing to cite). */
 typedef struct cusk_comm cusk_comm;

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """BASELINE.json configs[4]: cuskss-merged on ~20k selected markers + 17 traits (heterologous sample sizes),
-the level-l tests of the ONE skeleton sharded over the GPUs of a box, NCCL all-gather of the adjacency
-bitmaps between levels.
+the level-l tests of the ONE skeleton sharded over the GPUs of a box, NCCL all-gather of the removed-edge flags
+(one byte per CSR slot) between levels.
 
     python scripts/bench_merged.py                      # 1 GPU
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
@@ -118,7 +118,7 @@ def main():
         print(json.dumps({
             "metric": "ci_tests_per_s", "workload": f"cuskss-merged {m} markers + {p} traits (n_var {n}), "
             f"{'uniform N' if args.uniform else 'heterologous N (0.5% NA)'}, max level {args.maxlevel}, alpha 1e-4; level-l "
-            "work items dealt round-robin over the GPUs, ncclAllGather of the adjacency bitmaps per level",
+            "work items dealt round-robin over the GPUs, ncclAllGather of one removed-flag byte per CSR slot per level",
             "n_gpus": world, "scaling": "strong", "steps": args.steps, "ms_per_skeleton": ms / args.steps,
             "value": tests / (ms * 1e-3), "unit": "tests/s", "tests_per_skeleton": tests // args.steps,
             "levels_run": st["levels_run"], "last_level": st["last_level"], "max_degree": st["max_degree"],

@@ -156,6 +156,16 @@ def test_cuskss_merged_edge_sharded_matches_single(tmp_path, oracle):
         assert (a[k] == b[k]).all()
 
 
+def test_cuskss_merged_edge_sharded_nccl(tmp_path, oracle):
+    """the same over NCCL (ncclCommInitAll in one process, one rank per GPU); needs >= 2 GPUs on the box"""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    _cuskss_case(tmp_path, oracle, 170, 5, 307, het=True, L1=5, L2=0, depth=3, merged=True,
+                 env={"CUSK_SHARD_GPUS": "2"})
+
+
 # ---- cusk (individual-level data) ------------------------------------------------------------------------------
 def _write_bfiles(d, beds, n, chrs):
     """beds: list of uint8 [m_i, ceil(n/4)] per chromosome"""

@@ -192,3 +192,76 @@ def test_device_resident_api(ctx, oracle):
     assert (G == ro["G"]).all()
     assert l == ro["l"]
     assert st["tests_executed"][1] > 0
+
+
+def _run_group(world, devices, fn):
+    """One context + thread per rank of an in-process group; fn(ctx) is the (identical) call each makes."""
+    import threading
+
+    import cigwas_b200
+
+    ctxs = [cigwas_b200.Context(devices[r % len(devices)]) for r in range(world)]
+    cigwas_b200.local_group(ctxs)
+    out, err = [None] * world, [None] * world
+
+    def work(r):
+        try:
+            out[r] = fn(ctxs[r])
+        except Exception as e:  # noqa: BLE001
+            err[r] = e
+
+    ts = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=120)
+    for c in ctxs:
+        c.detach_comm()
+        c.close()
+    assert not any(err), err
+    return out
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_edge_sharded_individual_level_identical(ctx, world):
+    """the individual-level engine sharded over `world` ranks (work items dealt round-robin, MIN
+    all-reduce of the separating-set ranks per level): graph, separating sets and pMax of EVERY rank are
+    those of the single-GPU call, bit for bit.  Ranks share GPU 0 (or use two GPUs when the box has them)."""
+    import torch
+
+    from cigwas_b200 import synth
+    import cigwas_b200
+
+    Cm = synth.sem_correlation(240, 6, stream=91, num_samples=10000, causal_per_trait=10)
+    Th = cigwas_b200.threshold_array(10000, ALPHA)
+    one = ctx.skeleton(Cm, Th, 14)
+    devices = list(range(min(world, torch.cuda.device_count())))
+    res = _run_group(world, devices, lambda c: c.skeleton(Cm, Th, 14))
+    for r in res:
+        assert r["l"] == one["l"]
+        assert (r["G"] == one["G"]).all()
+        assert (r["SepSet"] == one["SepSet"]).all()
+        assert np.array_equal(r["pMax"], one["pMax"])
+        # canonical counts come from the (replicated) level plan: the same on every rank
+        assert r["stats"]["tests_canonical"] == one["stats"]["tests_canonical"]
+
+
+def test_edge_sharded_hetcor_identical(ctx):
+    import torch
+
+    from cigwas_b200 import synth
+    import cigwas_b200
+
+    m, p = 300, 6
+    n = m + p
+    Cm = synth.sem_correlation(m, p, stream=93, num_samples=20000, causal_per_trait=10)
+    N = synth.het_sample_sizes(n, m, 20000, stream=94, lo=4000, na_rate=0.01)
+    th = cigwas_b200.hetcor_threshold(ALPHA)
+    ti = np.zeros(n, np.int32)
+    ti[m:] = 1
+    G0 = np.ones((n, n), np.int32)
+    one = ctx.hetcor_skeleton(Cm, G0, N, th, 14, ti)
+    devices = list(range(min(3, torch.cuda.device_count())))
+    res = _run_group(3, devices, lambda c: c.hetcor_skeleton(Cm, G0, N, th, 14, ti))
+    for r in res:
+        assert r["l"] == one["l"] and (r["G"] == one["G"]).all()
