@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         u64 R0, R1;
     } s_it;
     LevelCtl *ctl = p.ctl;
-    if (ctl->done) return;
+    if (ctl->done || ctl->small) return;  // small: ci_small_kernel (ci_small.cu) runs this level
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int l = p.l, k = l - 1, n = p.n;
     const int nitems = ctl->nitems;

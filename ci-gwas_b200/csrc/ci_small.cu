@@ -1,0 +1,293 @@
+// ci_small.cu -- level-l CI tests for levels whose rows are all short (max degree <= CS_DMAX): one
+// THREAD per conditioning set (replaces cal_Indepl1..14, src/cuPC-S.cu:486-3020, and the _ess
+// variants, src/hetcor-cuPC-S.cu:379-3052, which are also thread-per-set; sm_100a).
+//
+// ci_level.cu shares one incremental factorisation between the sets of a warp and spreads the
+// neighbours over the lanes; with d ~ 16 that leaves half the lanes idle and every step waits on
+// the previous one, so a level with a few hundred thousand tests takes ~0.2 ms whatever its size.
+// Here the parallelism is ACROSS sets instead:
+//   * a warp pulls a work item (row X, rank range) from the level's queue, stages the row's
+//     neighbourhood submatrix C[adj(X), adj(X)] (<= 32 x 32 floats) in its own shared-memory slice,
+//   * every lane takes a contiguous sub-range of the ranks, unranks its first set with a Pascal
+//     table in shared memory and steps to the successor set afterwards,
+//   * per set S the lane runs an LDL^T (unit lower L, signed pivots D) of C[S,S] in registers - the
+//     kernel is compiled once per level l <= CI_SMALL_LMAX, every loop unrolled - carrying X
+//     along (tx = L^-1 C[S,X]); per neighbour Y it forward-substitutes ty = L^-1 C[S,Y] and gets
+//       h01 = Cxy - sum_j tx_j ty_j / D_j, h00 = 1 - sum_j tx_j^2 / D_j, h11 = 1 - sum_j ty_j^2 / D_j,
+//     the same quantities, pivot rule (|D| < CI_PIVOT_TOL drops the direction) and decision
+//     rho^2 < tanh(th)^2 [or > coth(th)^2] as ci_level.cu, in FP64.
+//   * levels above CI_SMALL_LMAX (state no longer fits the register file) stay with ci_level.cu.
+// PC-stable semantics are those of ci_level.cu: sets come from the adjacency compacted at level
+// start, removals clear bits (het engine) or lower the slot's minimum rank (individual-level engine).
+//
+// Algorithmic bytes per test: 4 (l + 2).
+#include "skeleton.cuh"
+
+#define CS_DMAX CI_SMALL_DMAX  // rows up to this degree (plan_kernel picks the kernel per level)
+#define CS_NWARPS 8
+#define CS_NTHREADS (CS_NWARPS * 32)
+#define CS_STRIDE (CS_DMAX + 1)
+#define FULLMASK 0xffffffffu
+
+struct CsWarp {
+    float csub[CS_DMAX * CS_STRIDE];
+    float cx[CS_DMAX];
+    int adj[CS_DMAX];
+    int time[CS_DMAX];
+    unsigned long long minkey[CS_DMAX];
+    unsigned skipmask;  // het engine: bit y set = edge (X, adj[y]) already removed
+    unsigned pad[3];
+};
+
+template <int LT>
+struct CsIdx {
+    static constexpr int LM = LT;
+    // W[j][a], j < a < LM, packed row by row
+    __device__ __forceinline__ static constexpr int w(int j, int a) { return j * LM - (j * (j + 1)) / 2 + (a - j - 1); }
+};
+
+template <bool HET, int LT>
+__global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kernel(const CiParams p)
+{
+    constexpr int LM = CsIdx<LT>::LM;
+    __shared__ CsWarp s_w[CS_NWARPS];
+    __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
+    LevelCtl *ctl = p.ctl;
+    if (ctl->done || !ctl->small) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int l = LT;
+    const int n = p.n;
+    const int nitems = ctl->nitems;
+    const double T2u = ctl->T2;
+    const bool het_general = HET && p.N != nullptr;
+    const bool use_time = HET && p.time_index != nullptr;
+    const double npairs = 0.5 * (double)((l + 2) * (l + 1));
+    for (int e = tid; e < (CS_DMAX + 1) * (CUSK_ML + 1); e += CS_NTHREADS)
+        s_binom[e] = (unsigned)binom64(e / (CUSK_ML + 1), e % (CUSK_ML + 1));
+    __syncthreads();
+    CsWarp &S = s_w[warp];
+    u64 my_tests = 0;
+    unsigned my_sing = 0;
+
+    for (;;) {
+        int item = 0;
+        if (lane == 0) item = p.shard_rank + p.shard_world * atomicAdd(p.work_counter, 1);
+        item = __shfl_sync(FULLMASK, item, 0);
+        if (item >= nitems) break;
+        if (item >= p.item_cap) {  // cannot happen: plan_kernel bounds the item count of a small level
+            if (lane == 0) ctl->infeasible = 3;
+            break;
+        }
+        const int4 a4 = *(const int4 *)&p.items[item];
+        const ulonglong2 r2 = *(const ulonglong2 *)&p.items[item].R0;
+        const int X = a4.x, d = a4.y, row0 = a4.z;
+        const unsigned R0 = (unsigned)r2.x, R1 = (unsigned)r2.y;
+        const int tX = use_time ? p.time_index[X] : 0;
+
+        // ---- stage the row (this warp's slice) ------------------------------------------------
+        __syncwarp();
+        if (lane < d) {
+            const int v = p.adj[row0 + lane];
+            S.adj[lane] = v;
+            S.cx[lane] = p.C[(size_t)X * n + v];
+            if (use_time) S.time[lane] = p.time_index[v];
+            if (!HET) S.minkey[lane] = __ldcg(&p.minkey[row0 + lane]);
+        }
+        if (HET) {
+            bool gone = false;
+            if (lane < d) {
+                const int v = p.adj[row0 + lane];
+                const uint32_t wbits = __ldcg(&p.bits[(size_t)X * p.rw + (v >> 5)]);
+                gone = !((wbits >> (v & 31)) & 1u);
+            }
+            const unsigned m = __ballot_sync(FULLMASK, gone);
+            if (lane == 0) S.skipmask = m;
+        }
+        __syncwarp();
+        for (int i = 0; i < d; i++) {
+            if (lane < d) S.csub[i * CS_STRIDE + lane] = (i == lane) ? 1.0f : __ldg(&p.C[(size_t)S.adj[i] * n + S.adj[lane]]);
+        }
+        __syncwarp();
+
+        // ---- this lane's ranks: [ra, rb) ---------------------------------------------------------
+        const unsigned cnt = R1 - R0;
+        const unsigned per = (cnt + 31u) / 32u;
+        const unsigned ra = R0 + (unsigned)lane * per;
+        const unsigned rb = (ra + per < R1) ? ra + per : R1;
+        if (ra < rb) {
+            int pos[LM];
+            {
+                unsigned rank = ra;
+                int x = 0;
+#pragma unroll
+                for (int i = 0; i < LM; i++) {
+                    for (;; x++) {
+                        const unsigned c = s_binom[(d - 1 - x) * (CUSK_ML + 1) + (l - 1 - i)];
+                        if (rank < c) break;
+                        rank -= c;
+                    }
+                    pos[i] = x;
+                    x++;
+                }
+            }
+            for (unsigned R = ra; R < rb; R++) {
+                // ---- LDL^T of C[S,S] (unit lower L, signed pivots D), X carried along ---------------
+                //   G_ji = A_ji - sum_{k<i} G_jk L_ik,  L_ji = G_ji / D_i,  D_j = 1 - sum_{i<j} G_ji L_ji
+                //   t = L^-1 c  =>  c' A^-1 c'' = sum_j t'_j t''_j / D_j
+                double Lm[LM * (LM - 1) / 2 + 1], invD[LM], tx[LM], txd[LM];
+                int tS = -2147483647 - 1;
+                unsigned inS = 0;
+                bool any_drop = false;
+                double h00 = 1.0;
+#pragma unroll
+                for (int j = 0; j < LM; j++) {
+                    double G[LM];
+                    double D = 1.0;
+                    double t = (double)S.cx[pos[j]];
+#pragma unroll
+                    for (int i = 0; i < j; i++) {
+                        double g = (double)S.csub[pos[j] * CS_STRIDE + pos[i]];
+#pragma unroll
+                        for (int k = 0; k < i; k++) g -= G[k] * Lm[CsIdx<LT>::w(k, i)];
+                        G[i] = g;
+                        const double lji = g * invD[i];
+                        Lm[CsIdx<LT>::w(i, j)] = lji;
+                        D -= g * lji;
+                        t -= lji * tx[i];
+                    }
+                    const bool drop = fabs(D) < CI_PIVOT_TOL;
+                    invD[j] = drop ? 0.0 : 1.0 / D;
+                    if (drop && j < LM - 1) any_drop = true;
+                    tx[j] = t;
+                    txd[j] = t * invD[j];
+                    h00 -= t * txd[j];
+                    inS |= 1u << pos[j];
+                    if (use_time) tS = max(tS, S.time[pos[j]]);
+                }
+                if (any_drop) my_sing++;
+                const double c2 = fabs(h00);
+                double SP = 0.0;
+                if (het_general) {
+                    // pairs inside S and S x X (src/hetcor-cuPC-S.cu:3068-3089: N[later * n + earlier],
+                    // tuple ordered X, Y, S_1..S_l)
+#pragma unroll
+                    for (int j = 0; j < LM; j++) {
+                        const size_t rowj = (size_t)S.adj[pos[j]] * n;
+                        SP += (double)__float2int_rz(p.N[rowj + X]);
+#pragma unroll
+                        for (int i = 0; i < j; i++) SP += (double)__float2int_rz(p.N[rowj + S.adj[pos[i]]]);
+                    }
+                }
+                // ---- this set's neighbours Y: every member of adj(X) outside S ----------------------
+                unsigned todo = ~inS & ((d >= 32) ? 0xffffffffu : ((1u << d) - 1u));
+                if (HET) todo &= ~*(volatile unsigned *)&S.skipmask;
+                while (todo) {
+                    const int y = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    if (HET) {
+                        if (use_time && tS > max(tX, S.time[y])) continue;
+                    } else {
+                        if (S.minkey[y] < (unsigned long long)R) continue;
+                    }
+                    my_tests++;
+                    double ty[LM];
+                    double h01 = (double)S.cx[y], h11 = 1.0;
+#pragma unroll
+                    for (int j = 0; j < LM; j++) {
+                        double u = (double)S.csub[y * CS_STRIDE + pos[j]];
+#pragma unroll
+                        for (int i = 0; i < j; i++) u -= Lm[CsIdx<LT>::w(i, j)] * ty[i];
+                        ty[j] = u;
+                        h01 -= u * txd[j];
+                        h11 -= u * u * invD[j];
+                    }
+                    const double lhs = h01 * h01;
+                    const double den = c2 * fabs(h11);
+                    double T2 = T2u;
+                    if (het_general) {
+                        const int Y = S.adj[y];
+                        double sum = SP + (double)__float2int_rz(p.N[(size_t)Y * n + X]);
+#pragma unroll
+                        for (int j = 0; j < LM; j++) sum += (double)__float2int_rz(p.N[(size_t)S.adj[pos[j]] * n + Y]);
+                        const double m = sum / npairs;
+                        const double th = p.th_het / sqrt(m - (double)l - 3.0);
+                        const double t = tanh(th);
+                        T2 = t * t;
+                    }
+                    // |rho| < tanh(th)  or, on the |rho| > 1 branch, |rho| > coth(th)
+                    const bool rem = (lhs < T2 * den) || (den > 0.0 && lhs * T2 > den);
+                    if (rem) {
+                        const int Y = S.adj[y];
+                        if (HET) {
+                            atomicAnd(&p.bits[(size_t)X * p.rw + (Y >> 5)], ~(1u << (Y & 31)));
+                            atomicAnd(&p.bits[(size_t)Y * p.rw + (X >> 5)], ~(1u << (X & 31)));
+                            if (p.removed) p.removed[row0 + y] = 1;
+                            atomicOr(&S.skipmask, 1u << y);
+                        } else {
+                            atomicMin(&p.minkey[row0 + y], (u64)R);
+                            atomicMin(&S.minkey[y], (unsigned long long)R);
+                        }
+                    }
+                }
+                // ---- successor set -----------------------------------------------------------------
+                int ii = -1;
+#pragma unroll
+                for (int j = 0; j < LM; j++)
+                    if (pos[j] < d - l + j) ii = j;
+#pragma unroll
+                for (int j = 0; j < LM; j++) {
+                    if (j == ii)
+                        pos[j]++;
+                    else if (j > ii && ii >= 0 && j > 0)
+                        pos[j] = pos[j - 1] + 1;
+                }
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        my_tests += __shfl_xor_sync(FULLMASK, my_tests, o);
+        my_sing += __shfl_xor_sync(FULLMASK, my_sing, o);
+    }
+    if (lane == 0) {
+        if (my_tests) atomicAdd((unsigned long long *)&ctl->executed, (unsigned long long)my_tests);
+        if (my_sing) atomicAdd((unsigned long long *)&ctl->singular, (unsigned long long)my_sing);
+    }
+}
+
+template <bool HET, int LT>
+static int cs_launch(cudaStream_t st, const CiParams &p)
+{
+    static int ctas_per_sm = 0;  // per instantiation
+    if (!ctas_per_sm) {
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ci_small_kernel<HET, LT>, CS_NTHREADS, 0) != cudaSuccess ||
+            nb < 1)
+            nb = 1;
+        ctas_per_sm = nb;
+    }
+    ci_small_kernel<HET, LT><<<148 * ctas_per_sm, CS_NTHREADS, 0, st>>>(p);
+    return CUSK_OK;
+}
+
+template <bool HET>
+static int cs_dispatch(cudaStream_t st, const CiParams &p)
+{
+    switch (p.l) {
+        case 1: return cs_launch<HET, 1>(st, p);
+        case 2: return cs_launch<HET, 2>(st, p);
+        case 3: return cs_launch<HET, 3>(st, p);
+        case 4: return cs_launch<HET, 4>(st, p);
+        case 5: return cs_launch<HET, 5>(st, p);
+        case 6: return cs_launch<HET, 6>(st, p);
+        case 7: return cs_launch<HET, 7>(st, p);
+        case 8: return cs_launch<HET, 8>(st, p);
+        case 9: return cs_launch<HET, 9>(st, p);
+        case 10: return cs_launch<HET, 10>(st, p);
+        default: return CUSK_OK;  // l > CI_SMALL_LMAX: plan_kernel never marks the level small
+    }
+}
+
+int launch_ci_small(cudaStream_t st, bool het, const CiParams &p)
+{
+    return het ? cs_dispatch<true>(st, p) : cs_dispatch<false>(st, p);
+}

@@ -28,6 +28,7 @@ void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx,
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
 void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
                   int l, const LevelCtl *ctl, CiItem *items, int item_cap);
+int launch_ci_small(cudaStream_t st, bool het, const CiParams &p);
 void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits);
 void launch_apply_removed(cudaStream_t st, const unsigned char *flags, int world, size_t stride, int n, int rw,
                           const int *rowptr, const int *deg, const int *adj, uint32_t *bits);
@@ -113,8 +114,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         sh->exchange_ms = 0.0;
         sh->exchange_bytes = 0;
     }
-    // plan_kernel aims at 148 * 16 * world items per level, plus at most one short item per row
-    const int item_cap = n + 148 * 16 * ((sh ? sh->world : 1) + 1);
+    // plan_kernel aims at up to 148 * CI_SMALL_IPSM_MAX * world items per level, plus at most one short item per row
+    const int item_cap = n + 148 * CI_SMALL_IPSM_MAX * ((sh ? sh->world : 1) + 1);
     CiItem *d_items = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
     if (!d_items) return CUSK_E_CUDA;
 
@@ -211,6 +212,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.shard_world = sh ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = launch_ci_level(st, a.het, p, grid);
+        if (rc) return rc;
+        rc = launch_ci_small(st, a.het, p);  // runs instead when the level's rows are all short (ctl->small)
         if (rc) return rc;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
         if (sh) {

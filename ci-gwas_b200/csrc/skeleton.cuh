@@ -6,6 +6,9 @@
 #define CI_NTHREADS (CI_NWARPS * 32)
 #define CI_ZB 4                 // leaf (z) register blocking
 #define CI_PIVOT_TOL 1e-10      // |pivot| below this: the direction is dropped (pseudo-inverse)
+#define CI_SMALL_DMAX 32        // ci_small.cu: thread-per-set kernel for levels whose max degree is at most this
+#define CI_SMALL_LMAX 10        // ... and whose level is at most this (per-set state in registers)
+#define CI_SMALL_IPSM_MAX 64    // upper bound of its items per SM (sizes the decoded item table)
 #define CI_MAX_COMB ((u64)1 << 48)  // per-row conditioning-set count above which a level is infeasible
 
 // One per level, written by plan_kernel, read by every other kernel of the level and copied
@@ -20,6 +23,8 @@ struct LevelCtl {
     u64 nnz;         // directed edges at level start
     u64 singular;    // dropped pivots
     double T2;       // tanh(threshold)^2 of the level (non-het and uniform-N het)
+    int small;       // 1: every row is short (max degree <= CI_SMALL_DMAX): ci_small_kernel runs the level
+    int pad;
 };
 
 // One work item of the CI kernel, decoded once per level by items_kernel (the CI kernel's CTAs then

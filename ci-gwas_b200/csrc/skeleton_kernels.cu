@@ -188,12 +188,13 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
                                                     u64 *__restrict__ chunk, LevelCtl *ctl,
                                                     const LevelCtl *prev, double th_level, double th_het,
                                                     float n_uniform, int *work_counter, int world,
-                                                    int ipsm_shallow, int ipsm_deep)
+                                                    int ipsm_shallow, int ipsm_deep, int ipsm_small)
 {
     __shared__ u64 s_warp[33];
     __shared__ int s_maxdeg;
     __shared__ u64 s_target;
     __shared__ int s_infeasible;
+    __shared__ int s_small;
     const int tid = threadIdx.x;
     if (prev && prev->done) {
         if (tid == 0) {
@@ -255,7 +256,13 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         // items for balance; from level 3 on an item's cost is dominated by the per-prefix factorisation,
         // which consecutive conditioning sets share, so few large items win (sweep on the C2 block:
         // profiles/r1_item_floor_sweep.txt).
-        const u64 per_sm = (u64)(l <= 2 ? ipsm_shallow : ipsm_deep);
+        // A level whose rows are all short goes to the thread-per-set kernel (ci_small.cu): a warp per
+        // item, a lane per rank, so it wants many items of >= 32 ranks.
+        const int small = (ipsm_small > 0 && s_maxdeg <= CI_SMALL_DMAX && l <= CI_SMALL_LMAX) ? 1 : 0;
+        ctl->small = small;
+        ctl->pad = 0;
+        s_small = small;
+        const u64 per_sm = small ? (u64)ipsm_small : (u64)(l <= 2 ? ipsm_shallow : ipsm_deep);
         u64 target = tot_tests / ((u64)148 * per_sm * (u64)world);
         if (target < 32) target = 32;
         s_target = target;
@@ -268,6 +275,7 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
     }
     // pass 2: work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks.
     const u64 target = s_target;
+    const bool small = s_small != 0;
     carry = 0;
     for (int base = 0; base < n; base += blockDim.x) {
         const int r = base + tid;
@@ -285,7 +293,8 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
             items = (tests + tgt - 1) / tgt;
             if (items > c) items = c;
             if (items < 1) items = 1;
-            const u64 ch = (c + items - 1) / items;
+            u64 ch = (c + items - 1) / items;
+            if (small && ch < 32) ch = (c < 32) ? c : 32;  // a lane per rank
             items = (c + ch - 1) / ch;
             chunk[r] = ch;
         } else if (r < n) {
@@ -557,8 +566,16 @@ void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int
         const int v = e ? atoi(e) : 0;
         return v > 0 ? v : 2;
     }();
+    // items per SM of the thread-per-set kernel (ci_small.cu); CUSK_SMALL_KERNEL=0 switches it off
+    static const int ipsm_small = [] {
+        const char *off = getenv("CUSK_SMALL_KERNEL");
+        if (off && atoi(off) == 0) return 0;
+        const char *e = getenv("CUSK_ITEMS_PER_SM_SMALL");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 32;
+    }();
     plan_kernel<<<1, 1024, 0, st>>>(deg, n, l, rowptr, itemstart, chunk, ctl, prev, th_level, th_het,
-                                    n_uniform, work_counter, world, ipsm_shallow, ipsm_deep);
+                                    n_uniform, work_counter, world, ipsm_shallow, ipsm_deep, ipsm_small);
 }
 
 void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
