@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         u64 R0, R1;
     } s_it;
     LevelCtl *ctl = p.ctl;
-    if (ctl->done || ctl->small) return;  // small: ci_small_kernel (ci_small.cu) runs this level
+    if (ctl->done) return;  // (short rows are not in this kernel's item table: ci_small.cu)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int l = p.l, k = l - 1, n = p.n;
     const int nitems = ctl->nitems;
@@ -61,24 +61,9 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
                 s_it.row0 = a4.z;
                 s_it.R0 = r2.x;
                 s_it.R1 = r2.y;
-            } else if (item < nitems) {
-                int lo = 0, hi = n;  // largest X with itemstart[X] <= item
-                while (hi - lo > 1) {
-                    const int mid = (lo + hi) >> 1;
-                    if (p.itemstart[mid] <= item)
-                        lo = mid;
-                    else
-                        hi = mid;
-                }
-                const int dd = p.deg[lo];
-                const u64 nc = binom64(dd, l);
-                const u64 chx = p.chunk[lo];
-                const u64 r0 = (u64)(item - p.itemstart[lo]) * chx;
-                s_it.X = lo;
-                s_it.d = dd;
-                s_it.row0 = p.rowptr[lo];
-                s_it.R0 = r0;
-                s_it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
+            } else if (item < nitems) {  // cannot happen: plan_kernel bounds the item count
+                ctl->infeasible = 3;
+                s_it.item = nitems;
             }
         }
         __syncthreads();
@@ -143,10 +128,25 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         }
         __syncthreads();
         if (staged) {
-            for (int i = warp; i < d; i += CI_NWARPS) {
-                const float *crow = p.C + (size_t)s_adj[i] * n;
-                for (int j = lane; j < dpad; j += 32)
-                    Csub[(size_t)i * dpad + j] = (j < d) ? ((i == j) ? 1.0f : crow[s_adj[j]]) : 0.0f;
+            // d x dpad gathers from L2: eight independent loads in flight per thread (the row is idle until
+            // they land, so the memory-level parallelism here is what a short item costs)
+            const int total = d * dpad;
+            for (int base = tid; base < total; base += CI_NTHREADS * 8) {
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const int idx = base + u * CI_NTHREADS;
+                    v[u] = 0.0f;
+                    if (idx < total) {
+                        const int i = idx / dpad, j = idx - i * dpad;
+                        if (j < d) v[u] = (i == j) ? 1.0f : __ldg(&p.C[(size_t)s_adj[i] * n + s_adj[j]]);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const int idx = base + u * CI_NTHREADS;
+                    if (idx < total) Csub[idx] = v[u];
+                }
             }
             __syncthreads();
         }

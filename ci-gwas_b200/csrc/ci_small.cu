@@ -1,11 +1,11 @@
-// ci_small.cu -- level-l CI tests for levels whose rows are all short (max degree <= CS_DMAX): one
+// ci_small.cu -- level-l CI tests of the short rows (degree <= CS_DMAX) at levels l <= CI_SMALL_LMAX: one
 // THREAD per conditioning set (replaces cal_Indepl1..14, src/cuPC-S.cu:486-3020, and the _ess
 // variants, src/hetcor-cuPC-S.cu:379-3052, which are also thread-per-set; sm_100a).
 //
-// ci_level.cu shares one incremental factorisation between the sets of a warp and spreads the
-// neighbours over the lanes; with d ~ 16 that leaves half the lanes idle and every step waits on
-// the previous one, so a level with a few hundred thousand tests takes ~0.2 ms whatever its size.
-// Here the parallelism is ACROSS sets instead:
+// ci_level.cu gives a whole CTA to one row, shares one incremental factorisation between the sets of
+// a warp and spreads the neighbours over the lanes: right for hub rows with hundreds of neighbours,
+// but with d ~ 16-30 most lanes idle and every step waits on the previous one.  plan_kernel therefore
+// routes every row by its degree; for the short ones the parallelism is ACROSS sets instead:
 //   * a warp pulls a work item (row X, rank range) from the level's queue, stages the row's
 //     neighbourhood submatrix C[adj(X), adj(X)] (<= 32 x 32 floats) in its own shared-memory slice,
 //   * every lane takes a contiguous sub-range of the ranks, unranks its first set with a Pascal
@@ -53,11 +53,11 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
     __shared__ CsWarp s_w[CS_NWARPS];
     __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
     LevelCtl *ctl = p.ctl;
-    if (ctl->done || !ctl->small) return;
+    if (ctl->done) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int l = LT;
     const int n = p.n;
-    const int nitems = ctl->nitems;
+    const int nitems = ctl->nitems_small;
     const double T2u = ctl->T2;
     const bool het_general = HET && p.N != nullptr;
     const bool use_time = HET && p.time_index != nullptr;
@@ -71,15 +71,15 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
 
     for (;;) {
         int item = 0;
-        if (lane == 0) item = p.shard_rank + p.shard_world * atomicAdd(p.work_counter, 1);
+        if (lane == 0) item = p.shard_rank + p.shard_world * atomicAdd(p.work_counter_small, 1);
         item = __shfl_sync(FULLMASK, item, 0);
         if (item >= nitems) break;
         if (item >= p.item_cap) {  // cannot happen: plan_kernel bounds the item count of a small level
             if (lane == 0) ctl->infeasible = 3;
             break;
         }
-        const int4 a4 = *(const int4 *)&p.items[item];
-        const ulonglong2 r2 = *(const ulonglong2 *)&p.items[item].R0;
+        const int4 a4 = *(const int4 *)&p.items_small[item];
+        const ulonglong2 r2 = *(const ulonglong2 *)&p.items_small[item].R0;
         const int X = a4.x, d = a4.y, row0 = a4.z;
         const unsigned R0 = (unsigned)r2.x, R1 = (unsigned)r2.y;
         const int tX = use_time ? p.time_index[X] : 0;
@@ -104,8 +104,20 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
             if (lane == 0) S.skipmask = m;
         }
         __syncwarp();
-        for (int i = 0; i < d; i++) {
-            if (lane < d) S.csub[i * CS_STRIDE + lane] = (i == lane) ? 1.0f : __ldg(&p.C[(size_t)S.adj[i] * n + S.adj[lane]]);
+        {
+            const int myv = (lane < d) ? S.adj[lane] : 0;
+            for (int i0 = 0; i0 < d; i0 += 8) {  // eight independent gathers in flight per lane
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const int i = i0 + u;
+                    v[u] = 1.0f;
+                    if (i < d && lane < d && i != lane) v[u] = __ldg(&p.C[(size_t)S.adj[i] * n + myv]);
+                }
+#pragma unroll
+                for (int u = 0; u < 8; u++)
+                    if (i0 + u < d && lane < d) S.csub[(i0 + u) * CS_STRIDE + lane] = v[u];
+            }
         }
         __syncwarp();
 

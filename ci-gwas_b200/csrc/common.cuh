@@ -112,6 +112,10 @@ __host__ __device__ inline void unrank_comb_fast(u64 rank, int N, int k, int *po
     u64 c = binom64(m, r);
     int x = 0;
     for (int i = 0; i < k; i++) {
+        if (r == 0) {  // last slot: C(m, 0) = 1 per candidate, so the remaining rank is the offset
+            pos[i] = x + (int)rank;
+            break;
+        }
         while (rank >= c) {  // skip x: C(m-1, r) = C(m, r) (m - r) / m
             rank -= c;
             c = (m > 0) ? c * (u64)(m - r) / (u64)m : 0;

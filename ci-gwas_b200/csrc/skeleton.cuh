@@ -6,8 +6,8 @@
 #define CI_NTHREADS (CI_NWARPS * 32)
 #define CI_ZB 4                 // leaf (z) register blocking
 #define CI_PIVOT_TOL 1e-10      // |pivot| below this: the direction is dropped (pseudo-inverse)
-#define CI_SMALL_DMAX 32        // ci_small.cu: thread-per-set kernel for levels whose max degree is at most this
-#define CI_SMALL_LMAX 10        // ... and whose level is at most this (per-set state in registers)
+#define CI_SMALL_DMAX 32        // ci_small.cu: thread-per-set kernel for the rows whose degree is at most this
+#define CI_SMALL_LMAX 10        // ... at levels up to this one (per-set state in registers)
 #define CI_SMALL_IPSM_MAX 64    // upper bound of its items per SM (sizes the decoded item table)
 #define CI_MAX_COMB ((u64)1 << 48)  // per-row conditioning-set count above which a level is infeasible
 
@@ -23,7 +23,7 @@ struct LevelCtl {
     u64 nnz;         // directed edges at level start
     u64 singular;    // dropped pivots
     double T2;       // tanh(threshold)^2 of the level (non-het and uniform-N het)
-    int small;       // 1: every row is short (max degree <= CI_SMALL_DMAX): ci_small_kernel runs the level
+    int nitems_small;  // work items of the thread-per-set kernel (rows with degree <= CI_SMALL_DMAX)
     int pad;
 };
 
@@ -43,15 +43,15 @@ struct CiParams {
     const int *deg;
     const int *rowptr;
     const int *adj;
-    const int *itemstart;
-    const u64 *chunk;
     LevelCtl *ctl;
     int *work_counter;
+    int *work_counter_small;  // queue of ci_small_kernel
     u64 *minkey;             // non-het
     double th_het;
     int smem_bytes;
-    const CiItem *items;     // decoded items [0, item_cap); items beyond the cap are decoded on the fly
-    int item_cap;
+    const CiItem *items;        // decoded items of ci_level_kernel [0, ctl->nitems)
+    const CiItem *items_small;  // decoded items of ci_small_kernel [0, ctl->nitems_small)
+    int item_cap;               // capacity of either table (plan_kernel keeps the counts below it)
     unsigned char *removed;       // edge-sharded het engine: removed[slot of (X,Y) in the level's CSR] = 1
     int shard_rank, shard_world;  // this launch takes items rank, rank + world, ... (1 GPU: 0, 1)
 };

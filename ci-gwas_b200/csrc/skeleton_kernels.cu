@@ -187,19 +187,19 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
                                                     int *__restrict__ rowptr, int *__restrict__ itemstart,
                                                     u64 *__restrict__ chunk, LevelCtl *ctl,
                                                     const LevelCtl *prev, double th_level, double th_het,
-                                                    float n_uniform, int *work_counter, int world,
-                                                    int ipsm_shallow, int ipsm_deep, int ipsm_small)
+                                                    float n_uniform, int *work_counter, int *work_counter_small,
+                                                    int world, int ipsm_shallow, int ipsm_deep, int ipsm_small)
 {
     __shared__ u64 s_warp[33];
     __shared__ int s_maxdeg;
-    __shared__ u64 s_target;
+    __shared__ u64 s_target, s_target_small;
     __shared__ int s_infeasible;
-    __shared__ int s_small;
     const int tid = threadIdx.x;
     if (prev && prev->done) {
         if (tid == 0) {
             ctl->done = 1;
             ctl->nitems = 0;
+            ctl->nitems_small = 0;
         }
         return;
     }
@@ -208,8 +208,10 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         s_infeasible = 0;
     }
     __syncthreads();
+    // rows of at most this degree go to the thread-per-set kernel (ci_small.cu), the others to ci_level.cu
+    const int dsmall = (ipsm_small > 0 && l <= CI_SMALL_LMAX) ? CI_SMALL_DMAX : 0;
     // pass 1: CSR offsets, max degree, canonical test count
-    u64 carry = 0, tests_sum = 0, canon_sum = 0;
+    u64 carry = 0, tests_sum = 0, tests_small = 0, canon_sum = 0;
     int mx = 0;
     for (int base = 0; base < n; base += blockDim.x) {
         const int r = base + tid;
@@ -223,6 +225,8 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
             const u64 c = binom64(d, l);
             if (c >= CI_MAX_COMB)
                 atomicExch(&s_infeasible, 1);
+            else if (d <= dsmall)
+                tests_small += c * (u64)(d - l);
             else
                 tests_sum += c * (u64)(d - l);
             canon_sum += (c > ((u64)1 << 40) ? ((u64)1 << 40) : c) * (u64)(d - l);
@@ -230,8 +234,9 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
     }
     if (tid == 0) rowptr[n] = (int)carry;
     atomicMax(&s_maxdeg, mx);
-    u64 tot_tests, tot_canon;
+    u64 tot_tests, tot_small, tot_canon;
     block_scan_excl_u64(tests_sum, s_warp, &tot_tests);
+    block_scan_excl_u64(tests_small, s_warp, &tot_small);
     block_scan_excl_u64(canon_sum, s_warp, &tot_canon);
     __syncthreads();
     const bool runs = (s_maxdeg - 1 >= l) && !s_infeasible;
@@ -243,6 +248,7 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         ctl->singular = 0;
         ctl->infeasible = s_infeasible;
         ctl->done = runs ? 0 : 1;
+        ctl->pad = 0;
         double th = th_level;
         if (th_level < 0) {
             const double m = (double)__float2int_rz(n_uniform);
@@ -250,44 +256,46 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         }
         const double t = tanh(th);
         ctl->T2 = t * t;
-        // aim at ~16 items per SM; small levels are cut finer (they are latency-bound: the
-        // more warps share a hub row's conditioning sets the shorter the critical path)
-        // Items per SM: the first two levels are throughput-bound with very uneven rows and want many
-        // items for balance; from level 3 on an item's cost is dominated by the per-prefix factorisation,
-        // which consecutive conditioning sets share, so few large items win (sweep on the C2 block:
-        // profiles/r1_item_floor_sweep.txt).
-        // A level whose rows are all short goes to the thread-per-set kernel (ci_small.cu): a warp per
-        // item, a lane per rank, so it wants many items of >= 32 ranks.
-        const int small = (ipsm_small > 0 && s_maxdeg <= CI_SMALL_DMAX && l <= CI_SMALL_LMAX) ? 1 : 0;
-        ctl->small = small;
-        ctl->pad = 0;
-        s_small = small;
-        const u64 per_sm = small ? (u64)ipsm_small : (u64)(l <= 2 ? ipsm_shallow : ipsm_deep);
+        // Items per SM of ci_level_kernel: the first two levels are throughput-bound with very uneven rows
+        // and want many items for balance; from level 3 on an item's cost is dominated by the per-prefix
+        // factorisation, which consecutive conditioning sets share, so few large items win (sweep on the
+        // C2 block: profiles/r1_item_floor_sweep.txt).
+        const u64 per_sm = (u64)(l <= 2 ? ipsm_shallow : ipsm_deep);
         u64 target = tot_tests / ((u64)148 * per_sm * (u64)world);
         if (target < 32) target = 32;
         s_target = target;
+        // ci_small_kernel: a warp per item, a lane per rank, so many items of >= 32 ranks
+        u64 ts = tot_small / ((u64)148 * (u64)(ipsm_small > 0 ? ipsm_small : 1) * (u64)world);
+        if (ts < 32) ts = 32;
+        s_target_small = ts;
         *work_counter = 0;
+        *work_counter_small = 0;
     }
     __syncthreads();
     if (!runs) {
-        if (tid == 0) ctl->nitems = 0;
+        if (tid == 0) {
+            ctl->nitems = 0;
+            ctl->nitems_small = 0;
+        }
         return;
     }
-    // pass 2: work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks.
-    const u64 target = s_target;
-    const bool small = s_small != 0;
-    carry = 0;
+    // pass 2: work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks; the two
+    // kernels have separate item tables, itemstart[r] is the row's offset in its own (stored as ~offset
+    // for a short row).
+    const u64 target = s_target, target_small = s_target_small;
+    carry = 0;  // low 32 bits: items of ci_level_kernel, high 32 bits: items of ci_small_kernel
     for (int base = 0; base < n; base += blockDim.x) {
         const int r = base + tid;
         const int d = (r < n) ? deg[r] : 0;
         u64 items = 0;
+        const bool small = d <= dsmall;
         if (r < n && d > l) {
             const u64 c = binom64(d, l);
             const u64 tests = c * (u64)(d - l);
-            // an item re-stages the row's d x d submatrix: keep at least ~4 tests per staged entry
-            u64 tgt = target;
-            // (rows too large to stage gather from L2 per test and have no such cost)
-            // (rows with d <= 64 stage in a couple of round trips whatever the item size)
+            u64 tgt = small ? target_small : target;
+            // an item of ci_level_kernel re-stages the row's d x d submatrix: keep at least ~4 tests per
+            // staged entry (rows too large to stage gather from L2 per test and have no such cost; rows
+            // with d <= 64 stage in a couple of round trips whatever the item size)
             const u64 stage_cost = (d > 64 && d <= 200) ? 4 * (u64)d * (u64)d : 0;
             if (tgt < stage_cost) tgt = stage_cost;
             items = (tests + tgt - 1) / tgt;
@@ -301,45 +309,51 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
             chunk[r] = 0;
         }
         u64 tot;
-        const u64 ex = block_scan_excl_u64(items, s_warp, &tot);
-        if (r < n) itemstart[r] = (int)(carry + ex);
+        const u64 ex = block_scan_excl_u64(small ? (items << 32) : items, s_warp, &tot);
+        if (r < n) {
+            const u64 at = carry + ex;
+            itemstart[r] = small ? ~(int)(at >> 32) : (int)(at & 0xffffffffu);
+        }
         carry += tot;
     }
     if (tid == 0) {
-        itemstart[n] = (int)carry;
-        ctl->nitems = (int)carry;
+        ctl->nitems = (int)(carry & 0xffffffffu);
+        ctl->nitems_small = (int)(carry >> 32);
     }
 }
 
-// Decodes the level's work items (row, degree, CSR offset, rank range) in parallel: thread = item.
+// Decodes the level's work items (row, degree, CSR offset, rank range) into the two item tables: a warp
+// per row, the lanes stride over the row's items.
 __global__ void __launch_bounds__(256) items_kernel(const int *__restrict__ deg, const int *__restrict__ rowptr,
                                                     const int *__restrict__ itemstart, const u64 *__restrict__ chunk,
                                                     int n, int l, const LevelCtl *ctl, CiItem *__restrict__ items,
-                                                    int item_cap)
+                                                    CiItem *__restrict__ items_small, int item_cap)
 {
     if (ctl->done) return;
-    const int item = blockIdx.x * blockDim.x + threadIdx.x;
-    if (item >= ctl->nitems || item >= item_cap) return;
-    int lo = 0, hi = n;  // largest X with itemstart[X] <= item
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (itemstart[mid] <= item)
-            lo = mid;
-        else
-            hi = mid;
-    }
-    const int dd = deg[lo];
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= n) return;
+    const u64 chx = chunk[r];
+    if (chx == 0) return;
+    const int dd = deg[r];
     const u64 nc = binom64(dd, l);
-    const u64 chx = chunk[lo];
-    const u64 r0 = (u64)(item - itemstart[lo]) * chx;
-    CiItem it;
-    it.X = lo;
-    it.d = dd;
-    it.row0 = rowptr[lo];
-    it.pad = 0;
-    it.R0 = r0;
-    it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
-    items[item] = it;
+    const u64 cnt = (nc + chx - 1) / chx;
+    const int is = itemstart[r];
+    CiItem *table = (is < 0) ? items_small : items;
+    const u64 off = (u64)((is < 0) ? ~is : is);
+    const int row0 = rowptr[r];
+    for (u64 k = lane; k < cnt; k += 32) {
+        if (off + k >= (u64)item_cap) break;
+        const u64 r0 = k * chx;
+        CiItem it;
+        it.X = r;
+        it.d = dd;
+        it.row0 = row0;
+        it.pad = 0;
+        it.R0 = r0;
+        it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
+        table[off + k] = it;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -553,13 +567,13 @@ void launch_degree(cudaStream_t st, const uint32_t *bits, int n, int rw, int *de
 
 void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int *itemstart, u64 *chunk,
                  LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
-                 int *work_counter, int world)
+                 int *work_counter, int *work_counter_small, int world)
 {
     // tuning knobs: work items per SM at levels 1-2 and at levels >= 3
     static const int ipsm_shallow = [] {
         const char *e = getenv("CUSK_ITEMS_PER_SM_SHALLOW");
         const int v = e ? atoi(e) : 0;
-        return v > 0 ? v : 16;
+        return v > 0 ? v : 8;
     }();
     static const int ipsm_deep = [] {
         const char *e = getenv("CUSK_ITEMS_PER_SM_DEEP");
@@ -575,13 +589,14 @@ void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int
         return v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 32;
     }();
     plan_kernel<<<1, 1024, 0, st>>>(deg, n, l, rowptr, itemstart, chunk, ctl, prev, th_level, th_het,
-                                    n_uniform, work_counter, world, ipsm_shallow, ipsm_deep, ipsm_small);
+                                    n_uniform, work_counter, work_counter_small, world, ipsm_shallow, ipsm_deep,
+                                    ipsm_small);
 }
 
 void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
-                  int l, const LevelCtl *ctl, CiItem *items, int item_cap)
+                  int l, const LevelCtl *ctl, CiItem *items, CiItem *items_small, int item_cap)
 {
-    items_kernel<<<(item_cap + 255) / 256, 256, 0, st>>>(deg, rowptr, itemstart, chunk, n, l, ctl, items, item_cap);
+    items_kernel<<<(n + 7) / 8, 256, 0, st>>>(deg, rowptr, itemstart, chunk, n, l, ctl, items, items_small, item_cap);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
