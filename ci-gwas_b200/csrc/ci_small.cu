@@ -11,12 +11,11 @@
 //   * every lane takes a contiguous sub-range of the ranks, unranks its first set with a Pascal
 //     table in shared memory and steps to the successor set afterwards,
 //   * per set S the lane runs an LDL^T (unit lower L, signed pivots D) of C[S,S] in registers - the
-//     kernel is compiled once per level l <= CI_SMALL_LMAX, every loop unrolled - carrying X
+//     kernel is compiled once per level, every loop unrolled (l > 10: L in shared memory) - carrying X
 //     along (tx = L^-1 C[S,X]); per neighbour Y it forward-substitutes ty = L^-1 C[S,Y] and gets
 //       h01 = Cxy - sum_j tx_j ty_j / D_j, h00 = 1 - sum_j tx_j^2 / D_j, h11 = 1 - sum_j ty_j^2 / D_j,
 //     the same quantities, pivot rule (|D| < CI_PIVOT_TOL drops the direction) and decision
 //     rho^2 < tanh(th)^2 [or > coth(th)^2] as ci_level.cu, in FP64.
-//   * levels above CI_SMALL_LMAX (state no longer fits the register file) stay with ci_level.cu.
 // PC-stable semantics are those of ci_level.cu: sets come from the adjacency compacted at level
 // start, removals clear bits (het engine) or lower the slot's minimum rank (individual-level engine).
 //
@@ -24,8 +23,9 @@
 #include "skeleton.cuh"
 
 #define CS_DMAX CI_SMALL_DMAX  // rows up to this degree (plan_kernel picks the kernel per level)
-#define CS_NWARPS 8
-#define CS_NTHREADS (CS_NWARPS * 32)
+#define CS_LREG 10      // up to this level the factor L lives in registers; above, in shared memory
+#define CS_NWARPS(LT) ((LT) <= CS_LREG ? 8 : 4)
+#define CS_NTHREADS(LT) (CS_NWARPS(LT) * 32)
 #define CS_STRIDE (CS_DMAX + 1)
 #define FULLMASK 0xffffffffu
 
@@ -39,6 +39,26 @@ struct CsWarp {
     unsigned pad[3];
 };
 
+// factor storage: registers (static indices after unrolling) or shared memory, element e of thread tid at
+// s[e * NT + tid] (conflict-free: the lanes of a warp run in lockstep over e)
+template <bool REG, int NT>
+struct CsL {
+    __device__ __forceinline__ static double get(const double *r, const double *s, int e, int tid)
+    {
+        if constexpr (REG)
+            return r[e];
+        else
+            return s[e * NT + tid];
+    }
+    __device__ __forceinline__ static void set(double *r, double *s, int e, int tid, double v)
+    {
+        if constexpr (REG)
+            r[e] = v;
+        else
+            s[e * NT + tid] = v;
+    }
+};
+
 template <int LT>
 struct CsIdx {
     static constexpr int LM = LT;
@@ -47,10 +67,14 @@ struct CsIdx {
 };
 
 template <bool HET, int LT>
-__global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kernel(const CiParams p)
+__global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2 : 1) ci_small_kernel(const CiParams p)
 {
     constexpr int LM = CsIdx<LT>::LM;
-    __shared__ CsWarp s_w[CS_NWARPS];
+    constexpr int NT = CS_NTHREADS(LT);
+    constexpr bool LREG = (LT <= CS_LREG);
+    using LS = CsL<LREG, NT>;
+    extern __shared__ double s_L[];  // LT > CS_LREG: LT (LT - 1) / 2 doubles per thread
+    __shared__ CsWarp s_w[CS_NWARPS(LT)];
     __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
     LevelCtl *ctl = p.ctl;
     if (ctl->done) return;
@@ -62,7 +86,7 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
     const bool het_general = HET && p.N != nullptr;
     const bool use_time = HET && p.time_index != nullptr;
     const double npairs = 0.5 * (double)((l + 2) * (l + 1));
-    for (int e = tid; e < (CS_DMAX + 1) * (CUSK_ML + 1); e += CS_NTHREADS)
+    for (int e = tid; e < (CS_DMAX + 1) * (CUSK_ML + 1); e += NT)
         s_binom[e] = (unsigned)binom64(e / (CUSK_ML + 1), e % (CUSK_ML + 1));
     __syncthreads();
     CsWarp &S = s_w[warp];
@@ -146,7 +170,7 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
                 // ---- LDL^T of C[S,S] (unit lower L, signed pivots D), X carried along ---------------
                 //   G_ji = A_ji - sum_{k<i} G_jk L_ik,  L_ji = G_ji / D_i,  D_j = 1 - sum_{i<j} G_ji L_ji
                 //   t = L^-1 c  =>  c' A^-1 c'' = sum_j t'_j t''_j / D_j
-                double Lm[LM * (LM - 1) / 2 + 1], invD[LM], tx[LM], txd[LM];
+                double Lm[LREG ? LM * (LM - 1) / 2 + 1 : 1], invD[LM], tx[LM], txd[LM];
                 int tS = -2147483647 - 1;
                 unsigned inS = 0;
                 bool any_drop = false;
@@ -160,10 +184,10 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
                     for (int i = 0; i < j; i++) {
                         double g = (double)S.csub[pos[j] * CS_STRIDE + pos[i]];
 #pragma unroll
-                        for (int k = 0; k < i; k++) g -= G[k] * Lm[CsIdx<LT>::w(k, i)];
+                        for (int k = 0; k < i; k++) g -= G[k] * LS::get(Lm, s_L, CsIdx<LT>::w(k, i), tid);
                         G[i] = g;
                         const double lji = g * invD[i];
-                        Lm[CsIdx<LT>::w(i, j)] = lji;
+                        LS::set(Lm, s_L, CsIdx<LT>::w(i, j), tid, lji);
                         D -= g * lji;
                         t -= lji * tx[i];
                     }
@@ -208,7 +232,7 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
                     for (int j = 0; j < LM; j++) {
                         double u = (double)S.csub[y * CS_STRIDE + pos[j]];
 #pragma unroll
-                        for (int i = 0; i < j; i++) u -= Lm[CsIdx<LT>::w(i, j)] * ty[i];
+                        for (int i = 0; i < j; i++) u -= LS::get(Lm, s_L, CsIdx<LT>::w(i, j), tid) * ty[i];
                         ty[j] = u;
                         h01 -= u * txd[j];
                         h11 -= u * u * invD[j];
@@ -269,15 +293,22 @@ __global__ void __launch_bounds__(CS_NTHREADS, (LT <= 6) ? 2 : 1) ci_small_kerne
 template <bool HET, int LT>
 static int cs_launch(cudaStream_t st, const CiParams &p)
 {
+    constexpr int NT = CS_NTHREADS(LT);
+    constexpr int dyn = (LT <= CS_LREG) ? 0 : LT * (LT - 1) / 2 * 8 * NT;
     static int ctas_per_sm = 0;  // per instantiation
     if (!ctas_per_sm) {
+        if (dyn > 0 && cudaFuncSetAttribute(ci_small_kernel<HET, LT>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn) !=
+                           cudaSuccess) {
+            cusk_set_error("cudaFuncSetAttribute(ci_small_kernel<%d>, %d B): %s", LT, dyn,
+                           cudaGetErrorString(cudaGetLastError()));
+            return CUSK_E_CUDA;
+        }
         int nb = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ci_small_kernel<HET, LT>, CS_NTHREADS, 0) != cudaSuccess ||
-            nb < 1)
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ci_small_kernel<HET, LT>, NT, dyn) != cudaSuccess || nb < 1)
             nb = 1;
         ctas_per_sm = nb;
     }
-    ci_small_kernel<HET, LT><<<148 * ctas_per_sm, CS_NTHREADS, 0, st>>>(p);
+    ci_small_kernel<HET, LT><<<148 * ctas_per_sm, NT, dyn, st>>>(p);
     return CUSK_OK;
 }
 
@@ -295,7 +326,11 @@ static int cs_dispatch(cudaStream_t st, const CiParams &p)
         case 8: return cs_launch<HET, 8>(st, p);
         case 9: return cs_launch<HET, 9>(st, p);
         case 10: return cs_launch<HET, 10>(st, p);
-        default: return CUSK_OK;  // l > CI_SMALL_LMAX: plan_kernel never marks the level small
+        case 11: return cs_launch<HET, 11>(st, p);
+        case 12: return cs_launch<HET, 12>(st, p);
+        case 13: return cs_launch<HET, 13>(st, p);
+        case 14: return cs_launch<HET, 14>(st, p);
+        default: return CUSK_OK;
     }
 }
 

@@ -7,7 +7,7 @@
 #define CI_ZB 4                 // leaf (z) register blocking
 #define CI_PIVOT_TOL 1e-10      // |pivot| below this: the direction is dropped (pseudo-inverse)
 #define CI_SMALL_DMAX 32        // ci_small.cu: thread-per-set kernel for the rows whose degree is at most this
-#define CI_SMALL_LMAX 10        // ... at levels up to this one (per-set state in registers)
+#define CI_SMALL_LMAX 14        // ... at levels up to this one
 #define CI_SMALL_IPSM_MAX 64    // upper bound of its items per SM (sizes the decoded item table)
 #define CI_MAX_COMB ((u64)1 << 48)  // per-row conditioning-set count above which a level is infeasible
 
