@@ -239,7 +239,7 @@ def main():
         alg_bytes += algorithmic_bytes(st["tests_executed"])
         ci_ms += sum(st["ci_kernel_ms"])
         # ess scan, level 0, (degree, plan, compact, items, CI) per level that ran, final degree + plan
-        launches += 2 + 5 * (st["levels_run"] - 1) + 2
+        launches += 2 + 4 * (st["levels_run"] - 1) + 1
         last_stats = st
     barrier()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)

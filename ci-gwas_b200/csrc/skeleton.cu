@@ -12,12 +12,12 @@
 // launch wrappers (skeleton_kernels.cu, ci_level.cu)
 void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, float n_uniform, const int *G_in,
                    int n, int rw, double th, uint32_t *bits, float *pMax);
-void launch_degree(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, const LevelCtl *prev);
-void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int *itemstart, u64 *chunk,
-                 LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
-                 int *work_counter, int *work_counter_small, int world);
+void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
+                        int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
+                        double th_het, float n_uniform, int *work_counter, int *work_counter_small, int world);
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
-                    u64 *minkey, const LevelCtl *ctl);
+                    u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
+                    CiItem *items, CiItem *items_small, int item_cap);
 void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
                     const int *rowptr, const int *adj, const u64 *minkey, float *pMax, cusk_sepset *seps,
                     unsigned long long *sep_count, u64 sep_cap, const LevelCtl *ctl);
@@ -26,8 +26,6 @@ void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, in
 void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits);
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
-void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
-                  int l, const LevelCtl *ctl, CiItem *items, CiItem *items_small, int item_cap);
 int launch_ci_small(cudaStream_t st, bool het, const CiParams &p);
 void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits);
 void launch_apply_removed(cudaStream_t st, const unsigned char *flags, int world, size_t stride, int n, int rw,
@@ -150,9 +148,9 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         CUSK_CUDA(cudaEventRecord(ev[l], st));
         LevelCtl *ctl = d_ctl + l;
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
-        launch_degree(st, a.dbits, n, rw, d_deg, prev);
-        launch_plan(st, d_deg, n, l, d_rowptr, d_itemstart, d_chunk, ctl, prev, a.het ? -1.0 : (double)a.Th[l],
-                    (double)a.th_het, n_uniform, d_work + l, d_work_small + l, sh ? sh->world : 1);
+        launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
+                           a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l, d_work_small + l,
+                           sh ? sh->world : 1);
         if (l == 1) {
             // the only mid-call synchronisation: directed edge count after level 0
             LevelCtl h;
@@ -187,8 +185,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             nnz_l = (size_t)h.nnz;
             if (d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, (nnz_l + 15) & ~(size_t)15, st));
         }
-        launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl);
-        launch_items(st, d_deg, d_rowptr, d_itemstart, d_chunk, n, l, ctl, d_items, d_items_small, item_cap);
+        launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
+                       d_items_small, item_cap);
         CiParams p;
         p.C = a.dC;
         p.N = a.het ? dN : nullptr;
@@ -247,9 +245,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         CUSK_CUDA(cudaGetLastError());
     }
     // final degrees (edge count) and pMax post-processing
-    launch_degree(st, a.dbits, n, rw, d_deg, nullptr);
-    launch_plan(st, d_deg, n, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1, nullptr, 1.0, 1.0,
-                n_uniform, d_work + CUSK_ML + 1, d_work_small + CUSK_ML + 1, 1);
+    launch_degree_plan(st, a.dbits, n, rw, d_deg, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1,
+                       nullptr, 1.0, 1.0, n_uniform, d_work + CUSK_ML + 1, d_work_small + CUSK_ML + 1, 1);
     if (!a.het && a.d_pMax) launch_pmax_final(st, a.dbits, n, rw, a.d_pMax);
     CUSK_CUDA(cudaEventRecord(ev[maxl + 1], st));
     CUSK_CUDA(cudaGetLastError());

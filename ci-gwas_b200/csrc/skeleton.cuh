@@ -25,6 +25,10 @@ struct LevelCtl {
     double T2;       // tanh(threshold)^2 of the level (non-het and uniform-N het)
     int nitems_small;  // work items of the thread-per-set kernel (rows with degree <= CI_SMALL_DMAX)
     int pad;
+    // accumulators of degree_plan_kernel's row phase (zero at the start of a call)
+    u64 acc_tests, acc_small, acc_canon;
+    int acc_maxdeg, acc_infeasible;
+    unsigned ticket, pad2;
 };
 
 // One work item of the CI kernel, decoded once per level by items_kernel (the CI kernel's CTAs then

@@ -135,22 +135,6 @@ __global__ void __launch_bounds__(256) level0_tile_kernel(const float *__restric
 }
 
 // ---------------------------------------------------------------------------------------------
-// Degrees: one warp per row, popcount over the bitmap row.
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) degree_kernel(const uint32_t *__restrict__ bits, int n, int rw,
-                                                     int *__restrict__ deg, const LevelCtl *prev)
-{
-    if (prev && prev->done) return;
-    const int lane = threadIdx.x & 31;
-    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (r >= n) return;
-    int c = 0;
-    for (int w = lane; w < rw; w += 32) c += __popc(bits[(size_t)r * rw + w]);
-    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-    if (lane == 0) deg[r] = c;
-}
-
-// ---------------------------------------------------------------------------------------------
 // Level plan: a single CTA scans the degrees into CSR offsets, decides whether the level runs
 // (src/cuPC-S.cu:154-159: a level l runs iff max_degree - 1 >= l), sizes the work items of the
 // CI kernel and computes the level's decision constant.
@@ -183,20 +167,25 @@ __device__ __forceinline__ u64 block_scan_excl_u64(u64 v, u64 *s_warp, u64 *tota
     return s_warp[wid] + inc - v;
 }
 
-__global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg, int n, int l,
-                                                    int *__restrict__ rowptr, int *__restrict__ itemstart,
-                                                    u64 *__restrict__ chunk, LevelCtl *ctl,
-                                                    const LevelCtl *prev, double th_level, double th_het,
-                                                    float n_uniform, int *work_counter, int *work_counter_small,
-                                                    int world, int ipsm_shallow, int ipsm_deep, int ipsm_small)
+// Degrees and level plan in one launch.  Row phase (every CTA, a warp per row): popcount of the bitmap
+// row, C(d, l) and the row's share of the level totals.  The CTA that finishes last then plans the level:
+// CSR offsets, whether the level runs (src/cuPC-S.cu:154-159: iff max_degree - 1 >= l), the work items of
+// the two CI kernels and the level's decision constant.
+__global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__restrict__ bits, int n, int rw,
+                                                           int *__restrict__ deg, int l, int *__restrict__ rowptr,
+                                                           int *__restrict__ itemstart, u64 *__restrict__ chunk,
+                                                           LevelCtl *ctl, const LevelCtl *prev, double th_level,
+                                                           double th_het, float n_uniform, int *work_counter,
+                                                           int *work_counter_small, int world, int ipsm_shallow,
+                                                           int ipsm_deep, int ipsm_small)
 {
     __shared__ u64 s_warp[33];
-    __shared__ int s_maxdeg;
+    __shared__ u64 s_acc[3];
+    __shared__ int s_maxdeg, s_infeasible, s_last;
     __shared__ u64 s_target, s_target_small;
-    __shared__ int s_infeasible;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (prev && prev->done) {
-        if (tid == 0) {
+        if (blockIdx.x == 0 && tid == 0) {
             ctl->done = 1;
             ctl->nitems = 0;
             ctl->nitems_small = 0;
@@ -204,49 +193,76 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         return;
     }
     if (tid == 0) {
+        s_acc[0] = s_acc[1] = s_acc[2] = 0;
         s_maxdeg = 0;
         s_infeasible = 0;
     }
     __syncthreads();
     // rows of at most this degree go to the thread-per-set kernel (ci_small.cu), the others to ci_level.cu
     const int dsmall = (ipsm_small > 0 && l <= CI_SMALL_LMAX) ? CI_SMALL_DMAX : 0;
-    // pass 1: CSR offsets, max degree, canonical test count
-    u64 carry = 0, tests_sum = 0, tests_small = 0, canon_sum = 0;
-    int mx = 0;
+    // ---- row phase -----------------------------------------------------------------------------------
+    {
+        const int r = blockIdx.x * 32 + wid;
+        if (r < n) {
+            int c = 0;
+            for (int w = lane; w < rw; w += 32) c += __popc(bits[(size_t)r * rw + w]);
+            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+            if (lane == 0) {
+                const int d = c;
+                deg[r] = d;
+                u64 cb = 0;
+                if (d > l) {
+                    cb = binom64(d, l);
+                    const u64 canon = (cb > ((u64)1 << 40) ? ((u64)1 << 40) : cb) * (u64)(d - l);
+                    atomicAdd((unsigned long long *)&s_acc[2], (unsigned long long)canon);
+                    if (cb >= CI_MAX_COMB)
+                        atomicExch(&s_infeasible, 1);
+                    else
+                        atomicAdd((unsigned long long *)&s_acc[d <= dsmall ? 1 : 0], (unsigned long long)(cb * (u64)(d - l)));
+                }
+                chunk[r] = cb;  // C(d, l) for the plan phase, which replaces it by the row's chunk size
+                atomicMax(&s_maxdeg, d);
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (s_acc[0]) atomicAdd((unsigned long long *)&ctl->acc_tests, (unsigned long long)s_acc[0]);
+        if (s_acc[1]) atomicAdd((unsigned long long *)&ctl->acc_small, (unsigned long long)s_acc[1]);
+        if (s_acc[2]) atomicAdd((unsigned long long *)&ctl->acc_canon, (unsigned long long)s_acc[2]);
+        atomicMax(&ctl->acc_maxdeg, s_maxdeg);
+        if (s_infeasible) atomicExch(&ctl->acc_infeasible, 1);
+        __threadfence();
+        s_last = (atomicAdd(&ctl->ticket, 1u) == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // ---- plan phase (one CTA) ----------------------------------------------------------------------------
+    const int maxdeg = *(volatile int *)&ctl->acc_maxdeg;
+    const int infeasible = *(volatile int *)&ctl->acc_infeasible;
+    const u64 tot_tests = *(volatile u64 *)&ctl->acc_tests;
+    const u64 tot_small = *(volatile u64 *)&ctl->acc_small;
+    const u64 tot_canon = *(volatile u64 *)&ctl->acc_canon;
+    // CSR offsets
+    u64 carry = 0;
     for (int base = 0; base < n; base += blockDim.x) {
         const int r = base + tid;
-        const int d = (r < n) ? deg[r] : 0;
-        mx = max(mx, d);
+        const int d = (r < n) ? __ldcg(&deg[r]) : 0;
         u64 tot;
         const u64 ex = block_scan_excl_u64((u64)d, s_warp, &tot);
         if (r < n) rowptr[r] = (int)(carry + ex);
         carry += tot;
-        if (r < n && d > l) {
-            const u64 c = binom64(d, l);
-            if (c >= CI_MAX_COMB)
-                atomicExch(&s_infeasible, 1);
-            else if (d <= dsmall)
-                tests_small += c * (u64)(d - l);
-            else
-                tests_sum += c * (u64)(d - l);
-            canon_sum += (c > ((u64)1 << 40) ? ((u64)1 << 40) : c) * (u64)(d - l);
-        }
     }
     if (tid == 0) rowptr[n] = (int)carry;
-    atomicMax(&s_maxdeg, mx);
-    u64 tot_tests, tot_small, tot_canon;
-    block_scan_excl_u64(tests_sum, s_warp, &tot_tests);
-    block_scan_excl_u64(tests_small, s_warp, &tot_small);
-    block_scan_excl_u64(canon_sum, s_warp, &tot_canon);
-    __syncthreads();
-    const bool runs = (s_maxdeg - 1 >= l) && !s_infeasible;
+    const bool runs = (maxdeg - 1 >= l) && !infeasible;
     if (tid == 0) {
-        ctl->maxdeg = s_maxdeg;
+        ctl->maxdeg = maxdeg;
         ctl->nnz = carry;
-        ctl->canon = (s_maxdeg - 1 >= l) ? tot_canon : 0;
+        ctl->canon = (maxdeg - 1 >= l) ? tot_canon : 0;
         ctl->executed = 0;
         ctl->singular = 0;
-        ctl->infeasible = s_infeasible;
+        ctl->infeasible = infeasible;
         ctl->done = runs ? 0 : 1;
         ctl->pad = 0;
         double th = th_level;
@@ -279,18 +295,18 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
         }
         return;
     }
-    // pass 2: work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks; the two
-    // kernels have separate item tables, itemstart[r] is the row's offset in its own (stored as ~offset
-    // for a short row).
+    // Work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks; the two kernels
+    // have separate item tables, itemstart[r] is the row's offset in its own (stored as ~offset for a
+    // short row).
     const u64 target = s_target, target_small = s_target_small;
     carry = 0;  // low 32 bits: items of ci_level_kernel, high 32 bits: items of ci_small_kernel
     for (int base = 0; base < n; base += blockDim.x) {
         const int r = base + tid;
-        const int d = (r < n) ? deg[r] : 0;
+        const int d = (r < n) ? __ldcg(&deg[r]) : 0;
         u64 items = 0;
         const bool small = d <= dsmall;
         if (r < n && d > l) {
-            const u64 c = binom64(d, l);
+            const u64 c = __ldcg(&chunk[r]);
             const u64 tests = c * (u64)(d - l);
             u64 tgt = small ? target_small : target;
             // an item of ci_level_kernel re-stages the row's d x d submatrix: keep at least ~4 tests per
@@ -322,53 +338,47 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int *__restrict__ deg,
     }
 }
 
-// Decodes the level's work items (row, degree, CSR offset, rank range) into the two item tables: a warp
-// per row, the lanes stride over the row's items.
-__global__ void __launch_bounds__(256) items_kernel(const int *__restrict__ deg, const int *__restrict__ rowptr,
-                                                    const int *__restrict__ itemstart, const u64 *__restrict__ chunk,
-                                                    int n, int l, const LevelCtl *ctl, CiItem *__restrict__ items,
-                                                    CiItem *__restrict__ items_small, int item_cap)
-{
-    if (ctl->done) return;
-    const int lane = threadIdx.x & 31;
-    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (r >= n) return;
-    const u64 chx = chunk[r];
-    if (chx == 0) return;
-    const int dd = deg[r];
-    const u64 nc = binom64(dd, l);
-    const u64 cnt = (nc + chx - 1) / chx;
-    const int is = itemstart[r];
-    CiItem *table = (is < 0) ? items_small : items;
-    const u64 off = (u64)((is < 0) ? ~is : is);
-    const int row0 = rowptr[r];
-    for (u64 k = lane; k < cnt; k += 32) {
-        if (off + k >= (u64)item_cap) break;
-        const u64 r0 = k * chx;
-        CiItem it;
-        it.X = r;
-        it.d = dd;
-        it.row0 = row0;
-        it.pad = 0;
-        it.R0 = r0;
-        it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
-        table[off + k] = it;
-    }
-}
-
 // ---------------------------------------------------------------------------------------------
-// Compaction (replaces scan_compact, src/cuPC-S.cu:6355-6432): one warp per row; each lane
+// Compaction (replaces scan_compact, src/cuPC-S.cu:6355-6432) and work-item decoding: one warp per row; each lane
 // popcounts one bitmap word, a warp prefix sum gives its output offset, set bits are expanded
 // to ascending neighbour ids.  Bytes: n^2/8 read + 4 nnz written (+ 8 nnz for minkey).
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) compact_kernel(const uint32_t *__restrict__ bits, int n, int rw,
                                                       const int *__restrict__ rowptr, int *__restrict__ adj,
-                                                      u64 *__restrict__ minkey, const LevelCtl *ctl)
+                                                      u64 *__restrict__ minkey, const LevelCtl *ctl,
+                                                      const int *__restrict__ deg, const int *__restrict__ itemstart,
+                                                      const u64 *__restrict__ chunk, int l, CiItem *__restrict__ items,
+                                                      CiItem *__restrict__ items_small, int item_cap)
 {
     if (ctl->done) return;
     const int lane = threadIdx.x & 31;
     const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (r >= n) return;
+    // the row's work items (row, degree, CSR offset, rank range) into the table of its CI kernel
+    {
+        const u64 chx = chunk[r];
+        if (chx != 0) {
+            const int dd = deg[r];
+            const u64 nc = binom64(dd, l);
+            const u64 cnt = (nc + chx - 1) / chx;
+            const int is = itemstart[r];
+            CiItem *table = (is < 0) ? items_small : items;
+            const u64 off = (u64)((is < 0) ? ~is : is);
+            const int row0 = rowptr[r];
+            for (u64 k = lane; k < cnt; k += 32) {
+                if (off + k >= (u64)item_cap) break;
+                const u64 r0 = k * chx;
+                CiItem it;
+                it.X = r;
+                it.d = dd;
+                it.row0 = row0;
+                it.pad = 0;
+                it.R0 = r0;
+                it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
+                table[off + k] = it;
+            }
+        }
+    }
     int out = rowptr[r];
     for (int w0 = 0; w0 < rw; w0 += 32) {
         const int w = w0 + lane;
@@ -560,16 +570,11 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
         level0_kernel<false><<<grid, 256, 0, st>>>(C, N, n_uniform, G_in, n, rw, th, bits, pMax);
 }
 
-void launch_degree(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, const LevelCtl *prev)
+void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
+                        int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
+                        double th_het, float n_uniform, int *work_counter, int *work_counter_small, int world)
 {
-    degree_kernel<<<(n + 7) / 8, 256, 0, st>>>(bits, n, rw, deg, prev);
-}
-
-void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int *itemstart, u64 *chunk,
-                 LevelCtl *ctl, const LevelCtl *prev, double th_level, double th_het, float n_uniform,
-                 int *work_counter, int *work_counter_small, int world)
-{
-    // tuning knobs: work items per SM at levels 1-2 and at levels >= 3
+    // tuning knobs: work items per SM of ci_level_kernel at levels 1-2 and at levels >= 3
     static const int ipsm_shallow = [] {
         const char *e = getenv("CUSK_ITEMS_PER_SM_SHALLOW");
         const int v = e ? atoi(e) : 0;
@@ -588,21 +593,18 @@ void launch_plan(cudaStream_t st, const int *deg, int n, int l, int *rowptr, int
         const int v = e ? atoi(e) : 0;
         return v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 32;
     }();
-    plan_kernel<<<1, 1024, 0, st>>>(deg, n, l, rowptr, itemstart, chunk, ctl, prev, th_level, th_het,
-                                    n_uniform, work_counter, work_counter_small, world, ipsm_shallow, ipsm_deep,
-                                    ipsm_small);
-}
-
-void launch_items(cudaStream_t st, const int *deg, const int *rowptr, const int *itemstart, const u64 *chunk, int n,
-                  int l, const LevelCtl *ctl, CiItem *items, CiItem *items_small, int item_cap)
-{
-    items_kernel<<<(n + 7) / 8, 256, 0, st>>>(deg, rowptr, itemstart, chunk, n, l, ctl, items, items_small, item_cap);
+    degree_plan_kernel<<<(n + 31) / 32, 1024, 0, st>>>(bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl, prev,
+                                                       th_level, th_het, n_uniform, work_counter,
+                                                       work_counter_small, world, ipsm_shallow, ipsm_deep,
+                                                       ipsm_small);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
-                    u64 *minkey, const LevelCtl *ctl)
+                    u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
+                    CiItem *items, CiItem *items_small, int item_cap)
 {
-    compact_kernel<<<(n + 7) / 8, 256, 0, st>>>(bits, n, rw, rowptr, adj, minkey, ctl);
+    compact_kernel<<<(n + 7) / 8, 256, 0, st>>>(bits, n, rw, rowptr, adj, minkey, ctl, deg, itemstart, chunk, l, items,
+                                                items_small, item_cap);
 }
 
 void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
