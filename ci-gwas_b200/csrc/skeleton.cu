@@ -14,10 +14,11 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
                    int n, int rw, double th, uint32_t *bits, float *pMax);
 void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
                         int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
-                        double th_het, float n_uniform, int *work_counter, int *work_counter_small, int world);
+                        double th_het, float n_uniform, int *work_counter, int *work_counter_small,
+                        int *work_counter_mid, int world);
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
                     u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
-                    CiItem *items, CiItem *items_small, int item_cap);
+                    CiItem *items, CiItem *items_small, CiItem *items_mid, int item_cap);
 void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
                     const int *rowptr, const int *adj, const u64 *minkey, float *pMax, cusk_sepset *seps,
                     unsigned long long *sep_count, u64 sep_cap, const LevelCtl *ctl);
@@ -27,6 +28,7 @@ void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bi
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
 int launch_ci_small(cudaStream_t st, bool het, const CiParams &p);
+int launch_ci_mid(cudaStream_t st, bool het, const CiParams &p);
 void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits);
 void launch_apply_removed(cudaStream_t st, const unsigned char *flags, int world, size_t stride, int n, int rw,
                           const int *rowptr, const int *deg, const int *adj, uint32_t *bits);
@@ -77,14 +79,15 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     int *d_itemstart = (int *)arena_take(ctx, sizeof(int) * ((size_t)n + 1));
     u64 *d_chunk = (u64 *)arena_take(ctx, sizeof(u64) * (size_t)n);
     LevelCtl *d_ctl = (LevelCtl *)arena_take(ctx, sizeof(LevelCtl) * (CUSK_ML + 2));
-    int *d_work = (int *)arena_take(ctx, sizeof(int) * 2 * (CUSK_ML + 2));  // queues of the two CI kernels
+    int *d_work = (int *)arena_take(ctx, sizeof(int) * 3 * (CUSK_ML + 2));  // queues of the three CI kernels
     int *d_work_small = d_work ? d_work + (CUSK_ML + 2) : nullptr;
+    int *d_work_mid = d_work ? d_work + 2 * (CUSK_ML + 2) : nullptr;
     unsigned long long *d_sepcount = (unsigned long long *)arena_take(ctx, sizeof(unsigned long long));
     int *d_minmax = (int *)arena_take(ctx, 2 * sizeof(int));
     if (!d_deg || !d_rowptr || !d_itemstart || !d_chunk || !d_ctl || !d_work || !d_sepcount || !d_minmax)
         return CUSK_E_CUDA;
     CUSK_CUDA(cudaMemsetAsync(d_ctl, 0, sizeof(LevelCtl) * (CUSK_ML + 2), st));
-    CUSK_CUDA(cudaMemsetAsync(d_work, 0, sizeof(int) * 2 * (CUSK_ML + 2), st));
+    CUSK_CUDA(cudaMemsetAsync(d_work, 0, sizeof(int) * 3 * (CUSK_ML + 2), st));
     CUSK_CUDA(cudaMemsetAsync(d_sepcount, 0, sizeof(unsigned long long), st));
 
     // het engine: uniform effective sample sizes take the constant-threshold fast path
@@ -117,7 +120,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     const int item_cap = n + 148 * CI_SMALL_IPSM_MAX * ((sh ? sh->world : 1) + 1);
     CiItem *d_items = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
     CiItem *d_items_small = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
-    if (!d_items || !d_items_small) return CUSK_E_CUDA;
+    CiItem *d_items_mid = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
+    if (!d_items || !d_items_small || !d_items_mid) return CUSK_E_CUDA;
 
     cudaEvent_t *ev = ctx->ev;
     CUSK_CUDA(cudaEventRecord(ev[0], st));
@@ -150,7 +154,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
         launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
                            a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l, d_work_small + l,
-                           sh ? sh->world : 1);
+                           d_work_mid + l, sh ? sh->world : 1);
         if (l == 1) {
             // the only mid-call synchronisation: directed edge count after level 0
             LevelCtl h;
@@ -186,7 +190,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             if (d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, (nnz_l + 15) & ~(size_t)15, st));
         }
         launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
-                       d_items_small, item_cap);
+                       d_items_small, d_items_mid, item_cap);
         CiParams p;
         p.C = a.dC;
         p.N = a.het ? dN : nullptr;
@@ -201,11 +205,13 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.ctl = ctl;
         p.work_counter = d_work + l;
         p.work_counter_small = d_work_small + l;
+        p.work_counter_mid = d_work_mid + l;
         p.minkey = d_minkey;
         p.th_het = (double)a.th_het;
         p.smem_bytes = smem_bytes;
         p.items = d_items;
         p.items_small = d_items_small;
+        p.items_mid = d_items_mid;
         p.item_cap = item_cap;
         p.removed = d_removed;
         p.shard_rank = sh ? sh->rank : 0;
@@ -215,6 +221,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         if (rc) return rc;
         rc = launch_ci_small(st, a.het, p);  // the level's short rows (thread per conditioning set)
         if (rc) return rc;
+        if (l <= CI_MID_LMAX) {
+            rc = launch_ci_mid(st, a.het, p);  // levels 1-2: the medium rows
+            if (rc) return rc;
+        }
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
         if (sh) {
             // exchange step of the level: removed edges (het: AND of the bitmaps; individual-level:
@@ -246,7 +256,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     }
     // final degrees (edge count) and pMax post-processing
     launch_degree_plan(st, a.dbits, n, rw, d_deg, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1,
-                       nullptr, 1.0, 1.0, n_uniform, d_work + CUSK_ML + 1, d_work_small + CUSK_ML + 1, 1);
+                       nullptr, 1.0, 1.0, n_uniform, d_work + CUSK_ML + 1, d_work_small + CUSK_ML + 1,
+                       d_work_mid + CUSK_ML + 1, 1);
     if (!a.het && a.d_pMax) launch_pmax_final(st, a.dbits, n, rw, a.d_pMax);
     CUSK_CUDA(cudaEventRecord(ev[maxl + 1], st));
     CUSK_CUDA(cudaGetLastError());

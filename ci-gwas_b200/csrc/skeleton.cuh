@@ -8,6 +8,8 @@
 #define CI_PIVOT_TOL 1e-10      // |pivot| below this: the direction is dropped (pseudo-inverse)
 #define CI_SMALL_DMAX 32        // ci_small.cu: thread-per-set kernel for the rows whose degree is at most this
 #define CI_SMALL_LMAX 14        // ... at levels up to this one
+#define CI_MID_DMAX 160         // ci_mid.cu: levels 1-2, rows with CI_SMALL_DMAX < degree <= this (CTA per item)
+#define CI_MID_LMAX 2
 #define CI_SMALL_IPSM_MAX 64    // upper bound of its items per SM (sizes the decoded item table)
 #define CI_MAX_COMB ((u64)1 << 48)  // per-row conditioning-set count above which a level is infeasible
 
@@ -24,11 +26,12 @@ struct LevelCtl {
     u64 singular;    // dropped pivots
     double T2;       // tanh(threshold)^2 of the level (non-het and uniform-N het)
     int nitems_small;  // work items of the thread-per-set kernel (rows with degree <= CI_SMALL_DMAX)
-    int pad;
+    int nitems_mid;    // work items of ci_mid_kernel (levels 1-2, medium rows)
     // accumulators of degree_plan_kernel's row phase (zero at the start of a call)
     u64 acc_tests, acc_small, acc_canon;
     int acc_maxdeg, acc_infeasible;
     unsigned ticket, pad2;
+    u64 acc_mid;
 };
 
 // One work item of the CI kernel, decoded once per level by items_kernel (the CI kernel's CTAs then
@@ -50,11 +53,13 @@ struct CiParams {
     LevelCtl *ctl;
     int *work_counter;
     int *work_counter_small;  // queue of ci_small_kernel
+    int *work_counter_mid;    // queue of ci_mid_kernel
     u64 *minkey;             // non-het
     double th_het;
     int smem_bytes;
     const CiItem *items;        // decoded items of ci_level_kernel [0, ctl->nitems)
     const CiItem *items_small;  // decoded items of ci_small_kernel [0, ctl->nitems_small)
+    const CiItem *items_mid;    // decoded items of ci_mid_kernel [0, ctl->nitems_mid)
     int item_cap;               // capacity of either table (plan_kernel keeps the counts below it)
     unsigned char *removed;       // edge-sharded het engine: removed[slot of (X,Y) in the level's CSR] = 1
     int shard_rank, shard_world;  // this launch takes items rank, rank + world, ... (1 GPU: 0, 1)

@@ -176,30 +176,33 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                                                            int *__restrict__ itemstart, u64 *__restrict__ chunk,
                                                            LevelCtl *ctl, const LevelCtl *prev, double th_level,
                                                            double th_het, float n_uniform, int *work_counter,
-                                                           int *work_counter_small, int world, int ipsm_shallow,
-                                                           int ipsm_deep, int ipsm_small)
+                                                           int *work_counter_small, int *work_counter_mid, int world,
+                                                           int ipsm_shallow, int ipsm_deep, int ipsm_small, int ipsm_mid)
 {
     __shared__ u64 s_warp[33];
-    __shared__ u64 s_acc[3];
+    __shared__ u64 s_acc[4];
     __shared__ int s_maxdeg, s_infeasible, s_last;
-    __shared__ u64 s_target, s_target_small;
+    __shared__ u64 s_target, s_target_small, s_target_mid;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (prev && prev->done) {
         if (blockIdx.x == 0 && tid == 0) {
             ctl->done = 1;
             ctl->nitems = 0;
             ctl->nitems_small = 0;
+            ctl->nitems_mid = 0;
         }
         return;
     }
     if (tid == 0) {
-        s_acc[0] = s_acc[1] = s_acc[2] = 0;
+        s_acc[0] = s_acc[1] = s_acc[2] = s_acc[3] = 0;
         s_maxdeg = 0;
         s_infeasible = 0;
     }
     __syncthreads();
     // rows of at most this degree go to the thread-per-set kernel (ci_small.cu), the others to ci_level.cu
     const int dsmall = (ipsm_small > 0 && l <= CI_SMALL_LMAX) ? CI_SMALL_DMAX : 0;
+    // ... and at levels 1-2 the rows up to this degree to ci_mid.cu
+    const int dmid = (ipsm_mid > 0 && l <= CI_MID_LMAX) ? CI_MID_DMAX : 0;
     // ---- row phase -----------------------------------------------------------------------------------
     {
         const int r = blockIdx.x * 32 + wid;
@@ -218,7 +221,8 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                     if (cb >= CI_MAX_COMB)
                         atomicExch(&s_infeasible, 1);
                     else
-                        atomicAdd((unsigned long long *)&s_acc[d <= dsmall ? 1 : 0], (unsigned long long)(cb * (u64)(d - l)));
+                        atomicAdd((unsigned long long *)&s_acc[d <= dsmall ? 1 : (d <= dmid ? 3 : 0)],
+                                  (unsigned long long)(cb * (u64)(d - l)));
                 }
                 chunk[r] = cb;  // C(d, l) for the plan phase, which replaces it by the row's chunk size
                 atomicMax(&s_maxdeg, d);
@@ -230,6 +234,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         if (s_acc[0]) atomicAdd((unsigned long long *)&ctl->acc_tests, (unsigned long long)s_acc[0]);
         if (s_acc[1]) atomicAdd((unsigned long long *)&ctl->acc_small, (unsigned long long)s_acc[1]);
         if (s_acc[2]) atomicAdd((unsigned long long *)&ctl->acc_canon, (unsigned long long)s_acc[2]);
+        if (s_acc[3]) atomicAdd((unsigned long long *)&ctl->acc_mid, (unsigned long long)s_acc[3]);
         atomicMax(&ctl->acc_maxdeg, s_maxdeg);
         if (s_infeasible) atomicExch(&ctl->acc_infeasible, 1);
         __threadfence();
@@ -244,6 +249,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
     const u64 tot_tests = *(volatile u64 *)&ctl->acc_tests;
     const u64 tot_small = *(volatile u64 *)&ctl->acc_small;
     const u64 tot_canon = *(volatile u64 *)&ctl->acc_canon;
+    const u64 tot_mid = *(volatile u64 *)&ctl->acc_mid;
     // CSR offsets
     u64 carry = 0;
     for (int base = 0; base < n; base += blockDim.x) {
@@ -264,7 +270,6 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         ctl->singular = 0;
         ctl->infeasible = infeasible;
         ctl->done = runs ? 0 : 1;
-        ctl->pad = 0;
         double th = th_level;
         if (th_level < 0) {
             const double m = (double)__float2int_rz(n_uniform);
@@ -284,57 +289,71 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         u64 ts = tot_small / ((u64)148 * (u64)(ipsm_small > 0 ? ipsm_small : 1) * (u64)world);
         if (ts < 32) ts = 32;
         s_target_small = ts;
+        // ci_mid_kernel: a CTA per item
+        u64 tm = tot_mid / ((u64)148 * (u64)(ipsm_mid > 0 ? ipsm_mid : 1) * (u64)world);
+        if (tm < 32) tm = 32;
+        s_target_mid = tm;
         *work_counter = 0;
         *work_counter_small = 0;
+        *work_counter_mid = 0;
     }
     __syncthreads();
     if (!runs) {
         if (tid == 0) {
             ctl->nitems = 0;
             ctl->nitems_small = 0;
+            ctl->nitems_mid = 0;
         }
         return;
     }
     // Work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks; the two kernels
     // have separate item tables, itemstart[r] is the row's offset in its own (stored as ~offset for a
     // short row).
-    const u64 target = s_target, target_small = s_target_small;
-    carry = 0;  // low 32 bits: items of ci_level_kernel, high 32 bits: items of ci_small_kernel
+    // The three kernels have separate item tables; itemstart[r] = class * 2^24 + offset in the class's table
+    // (class 0: ci_level_kernel, 1: ci_small_kernel, 2: ci_mid_kernel).
+    const u64 target = s_target, target_small = s_target_small, target_mid = s_target_mid;
+    carry = 0;  // three 21-bit fields: items of ci_level_kernel, ci_small_kernel, ci_mid_kernel
     for (int base = 0; base < n; base += blockDim.x) {
         const int r = base + tid;
         const int d = (r < n) ? __ldcg(&deg[r]) : 0;
         u64 items = 0;
-        const bool small = d <= dsmall;
+        const int cls = (d <= dsmall) ? 1 : ((d <= dmid) ? 2 : 0);
         if (r < n && d > l) {
             const u64 c = __ldcg(&chunk[r]);
             const u64 tests = c * (u64)(d - l);
-            u64 tgt = small ? target_small : target;
+            u64 tgt = (cls == 1) ? target_small : ((cls == 2) ? target_mid : target);
             // an item of ci_level_kernel re-stages the row's d x d submatrix: keep at least ~4 tests per
             // staged entry (rows too large to stage gather from L2 per test and have no such cost; rows
             // with d <= 64 stage in a couple of round trips whatever the item size)
-            const u64 stage_cost = (d > 64 && d <= 200) ? 4 * (u64)d * (u64)d : 0;
+            const u64 stage_cost = (cls == 0 && d > 64 && d <= 200) ? 4 * (u64)d * (u64)d : 0;
             if (tgt < stage_cost) tgt = stage_cost;
             items = (tests + tgt - 1) / tgt;
             if (items > c) items = c;
             if (items < 1) items = 1;
             u64 ch = (c + items - 1) / items;
-            if (small && ch < 32) ch = (c < 32) ? c : 32;  // a lane per rank
+            if (cls == 1 && ch < 32) ch = (c < 32) ? c : 32;  // a lane per rank
+            if (cls == 2) {
+                // a thread per (rank, 32-neighbour chunk): at least a CTA's worth of them per item
+                const u64 minr = (u64)((256 + ((d + 31) >> 5) - 1) / ((d + 31) >> 5));
+                if (ch < minr) ch = (c < minr) ? c : minr;
+            }
             items = (c + ch - 1) / ch;
             chunk[r] = ch;
         } else if (r < n) {
             chunk[r] = 0;
         }
         u64 tot;
-        const u64 ex = block_scan_excl_u64(small ? (items << 32) : items, s_warp, &tot);
+        const u64 ex = block_scan_excl_u64(items << (21 * cls), s_warp, &tot);
         if (r < n) {
             const u64 at = carry + ex;
-            itemstart[r] = small ? ~(int)(at >> 32) : (int)(at & 0xffffffffu);
+            itemstart[r] = (cls << 24) | (int)((at >> (21 * cls)) & 0x1fffffu);
         }
         carry += tot;
     }
     if (tid == 0) {
-        ctl->nitems = (int)(carry & 0xffffffffu);
-        ctl->nitems_small = (int)(carry >> 32);
+        ctl->nitems = (int)(carry & 0x1fffffu);
+        ctl->nitems_small = (int)((carry >> 21) & 0x1fffffu);
+        ctl->nitems_mid = (int)((carry >> 42) & 0x1fffffu);
     }
 }
 
@@ -348,7 +367,8 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint32_t *__restrict
                                                       u64 *__restrict__ minkey, const LevelCtl *ctl,
                                                       const int *__restrict__ deg, const int *__restrict__ itemstart,
                                                       const u64 *__restrict__ chunk, int l, CiItem *__restrict__ items,
-                                                      CiItem *__restrict__ items_small, int item_cap)
+                                                      CiItem *__restrict__ items_small, CiItem *__restrict__ items_mid,
+                                                      int item_cap)
 {
     if (ctl->done) return;
     const int lane = threadIdx.x & 31;
@@ -362,8 +382,9 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint32_t *__restrict
             const u64 nc = binom64(dd, l);
             const u64 cnt = (nc + chx - 1) / chx;
             const int is = itemstart[r];
-            CiItem *table = (is < 0) ? items_small : items;
-            const u64 off = (u64)((is < 0) ? ~is : is);
+            const int cls = is >> 24;
+            CiItem *table = (cls == 1) ? items_small : ((cls == 2) ? items_mid : items);
+            const u64 off = (u64)(is & 0xffffff);
             const int row0 = rowptr[r];
             for (u64 k = lane; k < cnt; k += 32) {
                 if (off + k >= (u64)item_cap) break;
@@ -572,7 +593,8 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
 
 void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
                         int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
-                        double th_het, float n_uniform, int *work_counter, int *work_counter_small, int world)
+                        double th_het, float n_uniform, int *work_counter, int *work_counter_small,
+                        int *work_counter_mid, int world)
 {
     // tuning knobs: work items per SM of ci_level_kernel at levels 1-2 and at levels >= 3
     static const int ipsm_shallow = [] {
@@ -593,18 +615,26 @@ void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, in
         const int v = e ? atoi(e) : 0;
         return v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 32;
     }();
+    // items per SM of the level-1/2 kernel for medium rows (ci_mid.cu); CUSK_MID_KERNEL=0 switches it off
+    static const int ipsm_mid = [] {
+        const char *off = getenv("CUSK_MID_KERNEL");
+        if (off && atoi(off) == 0) return 0;
+        const char *e = getenv("CUSK_ITEMS_PER_SM_MID");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 4;
+    }();
     degree_plan_kernel<<<(n + 31) / 32, 1024, 0, st>>>(bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl, prev,
                                                        th_level, th_het, n_uniform, work_counter,
-                                                       work_counter_small, world, ipsm_shallow, ipsm_deep,
-                                                       ipsm_small);
+                                                       work_counter_small, work_counter_mid, world, ipsm_shallow,
+                                                       ipsm_deep, ipsm_small, ipsm_mid);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
                     u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
-                    CiItem *items, CiItem *items_small, int item_cap)
+                    CiItem *items, CiItem *items_small, CiItem *items_mid, int item_cap)
 {
     compact_kernel<<<(n + 7) / 8, 256, 0, st>>>(bits, n, rw, rowptr, adj, minkey, ctl, deg, itemstart, chunk, l, items,
-                                                items_small, item_cap);
+                                                items_small, items_mid, item_cap);
 }
 
 void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
