@@ -1,4 +1,4 @@
-// ci_mid.cu -- levels 1 and 2 for the rows of medium degree (CI_SMALL_DMAX < d <= CI_MID_DMAX): one CTA
+// ci_mid.cu -- levels 1 and 2 for the rows of medium degree (CI_SMALL_DMAX < d <= 1024 / 160): one CTA
 // per work item, one thread per (conditioning set, 32-neighbour chunk) (replaces cal_Indepl1/2,
 // src/cuPC-S.cu:486-760, and cal_Indepl1_ess/2_ess, src/hetcor-cuPC-S.cu:379-640; sm_100a).
 //
@@ -32,13 +32,14 @@ __global__ void __launch_bounds__(CM_NTHREADS) ci_mid_kernel(const CiParams p)
     const bool het_general = HET && p.N != nullptr;
     const bool use_time = HET && p.time_index != nullptr;
     const double npairs = 0.5 * (double)((l + 2) * (l + 1));
-    // shared memory: adj, cx, time, skip (int each, CI_MID_DMAX), minkey (u64), then csub (level 2)
+    // shared memory: adj, cx, time, skip (int each, DM), minkey (u64), then csub (level 2)
+    constexpr int DM = (LT == 1) ? CI_MID_DMAX1 : CI_MID_DMAX;
     int *s_adj = (int *)smem;
-    float *s_cx = (float *)(s_adj + CI_MID_DMAX);
-    int *s_time = (int *)(s_cx + CI_MID_DMAX);
-    int *s_skip = s_time + CI_MID_DMAX;
-    unsigned long long *s_minkey = (unsigned long long *)(s_skip + CI_MID_DMAX);
-    float *csub = (float *)(s_minkey + CI_MID_DMAX);
+    float *s_cx = (float *)(s_adj + DM);
+    int *s_time = (int *)(s_cx + DM);
+    int *s_skip = s_time + DM;
+    unsigned long long *s_minkey = (unsigned long long *)(s_skip + DM);
+    float *csub = (float *)(s_minkey + DM);
     u64 my_tests = 0;
 
     for (;;) {
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(CM_NTHREADS) ci_mid_kernel(const CiParams p)
 template <bool HET, int LT>
 static int cm_launch(cudaStream_t st, const CiParams &p)
 {
-    constexpr int base = CI_MID_DMAX * (4 + 4 + 4 + 4 + 8);
+    constexpr int base = ((LT == 1) ? CI_MID_DMAX1 : CI_MID_DMAX) * (4 + 4 + 4 + 4 + 8);
     constexpr int dyn = base + (LT == 2 ? CI_MID_DMAX * (CI_MID_DMAX | 1) * 4 : 0);
     static int ctas_per_sm = 0;  // per instantiation
     if (!ctas_per_sm) {

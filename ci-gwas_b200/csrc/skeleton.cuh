@@ -8,7 +8,8 @@
 #define CI_PIVOT_TOL 1e-10      // |pivot| below this: the direction is dropped (pseudo-inverse)
 #define CI_SMALL_DMAX 32        // ci_small.cu: thread-per-set kernel for the rows whose degree is at most this
 #define CI_SMALL_LMAX 14        // ... at levels up to this one
-#define CI_MID_DMAX 160         // ci_mid.cu: levels 1-2, rows with CI_SMALL_DMAX < degree <= this (CTA per item)
+#define CI_MID_DMAX 160         // ci_mid.cu: level 2, rows with CI_SMALL_DMAX < degree <= this (CTA per item)
+#define CI_MID_DMAX1 1024       // ... level 1 (nothing staged, so only the row's index arrays bound it)
 #define CI_MID_LMAX 2
 #define CI_SMALL_IPSM_MAX 64    // upper bound of its items per SM (sizes the decoded item table)
 #define CI_MAX_COMB ((u64)1 << 48)  // per-row conditioning-set count above which a level is infeasible

@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
     // rows of at most this degree go to the thread-per-set kernel (ci_small.cu), the others to ci_level.cu
     const int dsmall = (ipsm_small > 0 && l <= CI_SMALL_LMAX) ? CI_SMALL_DMAX : 0;
     // ... and at levels 1-2 the rows up to this degree to ci_mid.cu
-    const int dmid = (ipsm_mid > 0 && l <= CI_MID_LMAX) ? CI_MID_DMAX : 0;
+    const int dmid = (ipsm_mid > 0 && l <= CI_MID_LMAX) ? (l == 1 ? CI_MID_DMAX1 : CI_MID_DMAX) : 0;
     // ---- row phase -----------------------------------------------------------------------------------
     {
         const int r = blockIdx.x * 32 + wid;
@@ -547,19 +547,19 @@ __global__ void __launch_bounds__(256) ess_minmax_kernel(const float *__restrict
     // min / max of the float bit patterns (ordered like the values for f >= 0); a NaN or a
     // negative entry poisons the result so that the general path is taken.  Uniform <=> mn == mx.
     int lo = 2147483647, hi = -2147483647 - 1;
-    const size_t total = (size_t)n * n;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (size_t)gridDim.x * blockDim.x) {
-        const size_t r = i / n, c = i - r * n;
-        if (r == c) continue;
-        const float f = N[i];
-        if (!(f >= 0.f)) {
-            lo = -2147483647 - 1;
-            hi = 2147483647;
-        } else {
-            const int v = __float_as_int(f);
-            lo = min(lo, v);
-            hi = max(hi, v);
+    for (int r = blockIdx.x; r < n; r += gridDim.x) {
+        const float *row = N + (size_t)r * n;
+        for (int c = threadIdx.x; c < n; c += blockDim.x) {
+            if (c == r) continue;
+            const float f = __ldg(row + c);
+            if (!(f >= 0.f)) {
+                lo = -2147483647 - 1;
+                hi = 2147483647;
+            } else {
+                const int v = __float_as_int(f);
+                lo = min(lo, v);
+                hi = max(hi, v);
+            }
         }
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -665,7 +665,7 @@ void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bi
 
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count)
 {
-    ess_minmax_kernel<<<sm_count * 8, 256, 0, st>>>(N, n, mn, mx);
+    ess_minmax_kernel<<<std::min(n, sm_count * 8), 256, 0, st>>>(N, n, mn, mx);
 }
 
 // edge-sharded mode: bits = AND over the ranks' bitmaps (each rank only ever clears bits)
