@@ -51,6 +51,10 @@ struct ShardLink {
     int (*allgather)(void *user, const void *d_send, void *d_recv, size_t bytes, cudaStream_t st) = nullptr;
     // element-wise minimum over ranks, in place (ncclAllReduce, ncclUint64, ncclMin)
     int (*allreduce_min_u64)(void *user, void *d_buf, size_t count, cudaStream_t st) = nullptr;
+    // ranks that are threads of ONE process: host barrier taken once per call, after the call's last device
+    // allocation and before its first exchange (cudaMalloc synchronises peer devices, so it must not run
+    // while another rank's collective kernel is already waiting for this rank); nullptr for one process per GPU
+    void (*host_barrier)(void *user) = nullptr;
     void *user = nullptr;
     double exchange_ms = 0.0;   // host-measured time spent in the exchanges of the last call
     size_t exchange_bytes = 0;  // bytes received by this rank in the exchanges of the last call

@@ -179,6 +179,12 @@ static int nccl_allreduce_min_u64(void *user, void *d_buf, size_t count, cudaStr
     return 0;
 }
 
+static void group_barrier(void *user)
+{
+    cusk_comm *c = (cusk_comm *)user;
+    if (c->group) c->group->barrier();
+}
+
 static void fill_link(cusk_comm *c, int rank, int world)
 {
     c->link.rank = rank;
@@ -242,10 +248,16 @@ extern "C" int cusk_comm_create_all(cusk_ctx **ctxs, int world, cusk_comm **out)
         cusk_set_error("ncclCommInitAll: %s", g_nccl.GetErrorString(r));
         return CUSK_E_CUDA;
     }
+    LocalGroup *g = new LocalGroup();  // only its host barrier is used (the exchanges go through NCCL)
+    g->world = world;
+    g->refs = world;
     for (int i = 0; i < world; i++) {
         out[i] = new cusk_comm();
         out[i]->comm = comms[i];
+        out[i]->group = g;
+        out[i]->device = devs[i];
         fill_link(out[i], i, world);
+        out[i]->link.host_barrier = group_barrier;
     }
     return CUSK_OK;
 }
@@ -277,6 +289,7 @@ extern "C" int cusk_comm_create_local(cusk_ctx **ctxs, int world, cusk_comm **ou
         out[i]->device = g->device[i];
         out[i]->link.rank = i;
         out[i]->link.world = world;
+        out[i]->link.host_barrier = group_barrier;
         out[i]->link.allgather = local_allgather;
         out[i]->link.allreduce_min_u64 = local_allreduce_min_u64;
         out[i]->link.user = out[i];

@@ -180,6 +180,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
                 if (!d_removed || !d_gather) return CUSK_E_CUDA;
             }
         }
+        if (sh && l == 1 && sh->host_barrier) sh->host_barrier(sh->user);  // every rank has done its allocations
         if (sh) {
             // the ranks must agree on when to stop exchanging: read the level's verdict (and its CSR size)
             LevelCtl h;

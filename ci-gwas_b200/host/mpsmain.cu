@@ -255,6 +255,9 @@ int dispatch(int argc, char **argv)
 
 int mps_main(int argc, char **argv)
 {
+    // ranks as threads of this process (CUSK_SHARD_GPUS): load every kernel up front, so that no module load
+    // (a context-wide operation) can fall between two ranks' collectives
+    if (getenv("CUSK_SHARD_GPUS")) setenv("CUDA_MODULE_LOADING", "EAGER", 0);
     try {
         return dispatch(argc, argv);
     } catch (const HostError &e) {

@@ -17,8 +17,17 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 MPS = os.path.join(ROOT, "ci-gwas_b200", "mps")
 
 
+def _device_count():
+    import torch
+
+    return torch.cuda.device_count()
+
+
 def run_mps(args, env=None, check=True):
     e = dict(os.environ)
+    # at most two GPUs per mps process: what these tests were verified on (a process that touches all eight
+    # GPUs of a box spends most of its run time initialising them)
+    e.setdefault("CUSK_DEVICES", "0,1" if _device_count() >= 2 else "0")
     e.update(env or {})
     r = subprocess.run([MPS] + [str(a) for a in args], capture_output=True, text=True, env=e)
     if check:
@@ -147,11 +156,11 @@ def test_cuskss_het_merged_two_stage(tmp_path, oracle):
 
 
 def test_cuskss_merged_edge_sharded_matches_single(tmp_path, oracle):
-    """the level-l tests of one skeleton dealt to 3 ranks (in-process exchange, ranks share the GPU)
+    """the level-l tests of one skeleton dealt to 3 ranks (in-process exchange, ranks share GPU 0)
     -> the same files as the single-GPU run and as the oracle"""
     a = _cuskss_case(tmp_path / "one", oracle, 170, 5, 307, het=True, L1=5, L2=0, depth=3, merged=True)
     b = _cuskss_case(tmp_path / "three", oracle, 170, 5, 307, het=True, L1=5, L2=0, depth=3, merged=True,
-                     env={"CUSK_SHARD_GPUS": "3", "CUSK_LOCAL_EXCHANGE": "1"})
+                     env={"CUSK_SHARD_GPUS": "3", "CUSK_LOCAL_EXCHANGE": "1", "CUSK_DEVICES": "0"})
     for k in ("ixs", "adj", "corr"):
         assert (a[k] == b[k]).all()
 
