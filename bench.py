@@ -238,8 +238,9 @@ def main():
         tests_total += sum(st["tests_executed"])
         alg_bytes += algorithmic_bytes(st["tests_executed"])
         ci_ms += sum(st["ci_kernel_ms"])
-        # ess scan, level 0, (degree, plan, compact, items, CI) per level that ran, final degree + plan
-        launches += 2 + 4 * (st["levels_run"] - 1) + 1
+        # ess scan, level 0, (degree+plan, compact+items, ci_level, ci_small [, ci_mid at levels 1-2]) per level
+        # that ran, final degree+plan
+        launches += 2 + 4 * (st["levels_run"] - 1) + min(2, st["levels_run"] - 1) + 1
         last_stats = st
     barrier()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
@@ -299,11 +300,14 @@ def main():
                     "h2d_bytes_per_step": 3 * nn * 4, "d2h_bytes_per_step": nn * 4,
                     "ms_per_step": e2e_ms_max / args.steps, "api": "cusk_hetcor_skeleton (host C, G, N in; host G out)"},
             "gpu_launches": launches_all,
-            "roofline": {"bound": "hbm", "kernel": "ci_level_kernel<HET>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "level-l CI kernels of the step (ci_mid_kernel<HET,1|2>, "
+                         "ci_small_kernel<HET,l>, ci_level_kernel<HET>)", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
-                         "note": "algorithmic bytes = sum_l tests_l * 4 (l+2); the kernel keeps the row's "
-                                 "submatrix in shared memory and is FP64-issue/latency bound, not HBM bound"},
+                         "note": "algorithmic bytes = sum_l tests_l * 4 (l+2), time = sum of the CI kernels' "
+                                 "durations (CUDA events on the engine's stream); the kernels work out of shared "
+                                 "memory / L2 and are FP64-issue and latency bound, not HBM bound; traffic = DRAM "
+                                 "bytes of the same launches (ncu, profiles/ci_level_traffic.json)"},
             "clocks": sampler.summary(),
         }
         if not args.no_cpu_baseline:
