@@ -112,6 +112,12 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     // (nnz_l bytes per rank instead of the n * rw word bitmap), all-gathered and applied by every rank
     unsigned char *d_removed = nullptr, *d_gather = nullptr;
     size_t flag_stride = 0, nnz_l = 0;
+    bool shard_level = false;
+    static const u64 shard_min_tests = [] {
+        const char *e = getenv("CUSK_SHARD_MIN_TESTS");
+        const long long v = e ? atoll(e) : -1;
+        return (u64)(v >= 0 ? v : 4000000);
+    }();
     if (sh) {
         sh->exchange_ms = 0.0;
         sh->exchange_bytes = 0;
@@ -188,7 +194,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             CUSK_CUDA(cudaStreamSynchronize(st));
             if (h.done) break;
             nnz_l = (size_t)h.nnz;
-            if (d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, (nnz_l + 15) & ~(size_t)15, st));
+            // a level with few tests is cheaper run whole by every rank (same result everywhere, no exchange)
+            // than dealt out and exchanged: an exchange costs a stream synchronisation plus the collective's latency
+            shard_level = (h.acc_tests + h.acc_small + h.acc_mid) >= shard_min_tests;
+            if (shard_level && d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, (nnz_l + 15) & ~(size_t)15, st));
         }
         launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
                        d_items_small, d_items_mid, item_cap);
@@ -214,9 +223,9 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.items_small = d_items_small;
         p.items_mid = d_items_mid;
         p.item_cap = item_cap;
-        p.removed = d_removed;
-        p.shard_rank = sh ? sh->rank : 0;
-        p.shard_world = sh ? sh->world : 1;
+        p.removed = shard_level ? d_removed : nullptr;
+        p.shard_rank = shard_level ? sh->rank : 0;
+        p.shard_world = shard_level ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = launch_ci_level(st, a.het, p, grid);
         if (rc) return rc;
@@ -227,7 +236,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             if (rc) return rc;
         }
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
-        if (sh) {
+        if (shard_level) {
             // exchange step of the level: removed edges (het: AND of the bitmaps; individual-level:
             // minimum of the separating-set ranks), after which every rank holds the same graph again
             CUSK_CUDA(cudaStreamSynchronize(st));

@@ -7,6 +7,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# edge-sharded runs: deal out every level, however few tests it has (the product keeps levels below
+# CUSK_SHARD_MIN_TESTS whole on every rank; the test problems are all far below the default)
+os.environ.setdefault("CUSK_SHARD_MIN_TESTS", "0")
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
