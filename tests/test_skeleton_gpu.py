@@ -260,3 +260,50 @@ def test_edge_sharded_hetcor_identical(ctx):
     res = _run_group(3, [0], lambda c: c.hetcor_skeleton(Cm, G0, N, th, 14, ti))
     for r in res:
         assert r["l"] == one["l"] and (r["G"] == one["G"]).all()
+
+
+# ---- all levels through all three CI kernels ---------------------------------------------------------------------
+# The bench generator (strong LD, 12 causal markers per trait) at 400 markers + 17 traits runs to level 14: level 1-2
+# rows have 33..160+ neighbours (ci_mid.cu and ci_level.cu), from level 3 on every row is short (ci_small.cu, register
+# variants to l = 10 and the shared-memory variants above).  No test of this case lies within 1e-9 of its threshold.
+def _deep_case():
+    import bench
+    from cigwas_b200 import synth
+
+    m, p = 400, 17
+    return m, p, synth.sem_correlation(m, p, stream=8, num_samples=NS, **bench.C2_KW)
+
+
+def test_all_levels_individual_level_engine(ctx, oracle):
+    m, p, Cm = _deep_case()
+    Th = oracle.threshold_array(NS, ALPHA)
+    ro = oracle.skeleton(Cm, Th, 14, near_band=NEAR_BAND)
+    assert ro["l"] == 15 and len(ro["near"]) == 0
+    rg = ctx.skeleton(Cm, Th, 14)
+    assert rg["l"] == ro["l"]
+    assert (rg["G"] == ro["G"]).all()
+    assert rg["stats"]["tests_canonical"][:15] == ro["stats"][:15].tolist()
+    assert (rg["SepSet"] == ro["SepSet"]).all()  # lowest-rank separating set of every removed edge, at every level
+    assert np.allclose(rg["pMax"], ro["pMax"], rtol=1e-5, atol=1e-7)
+    by_level = np.bincount([int(r["level"]) for r in rg["seps"]], minlength=15)
+    assert by_level[1] > 0 and by_level[2] > 0 and by_level[3:11].sum() > 0  # removals on every kernel's levels
+
+
+@pytest.mark.parametrize("general_n", [False, True])
+def test_all_levels_hetcor_engine(ctx, oracle, general_n):
+    import cigwas_b200
+    from cigwas_b200 import synth
+
+    m, p, Cm = _deep_case()
+    n = m + p
+    N = (synth.het_sample_sizes(n, m, NS, stream=9, lo=50000, na_rate=0.005) if general_n
+         else np.full((n, n), float(NS), np.float32))
+    th = cigwas_b200.hetcor_threshold(ALPHA)
+    ti = np.zeros(n, np.int32)
+    ti[m:] = 1
+    G0 = np.ones((n, n), np.int32)
+    ro = oracle.hetcor_skeleton(Cm, G0, N, th, 14, ti, near_band=NEAR_BAND)
+    rg = ctx.hetcor_skeleton(Cm, None, N, th, 14, ti)
+    assert ro["l"] == 15 and rg["l"] == ro["l"]
+    _assert_adj_equal(rg["G"], ro["G"], ro["near"])
+    assert rg["stats"]["tests_canonical"][:15] == ro["stats"][:15].tolist()
