@@ -12,6 +12,8 @@
 //     (sorted neighbours -> a few sectors per warp load), four loads in flight per thread.
 //   * level 2: the submatrix is staged in shared memory once per item (each entry serves ~d tests).
 // Quantities, pivot rule and decision are those of ci_small.cu / ci_level.cu.
+#include <atomic>
+
 #include "skeleton.cuh"
 
 #define CM_NTHREADS 256
@@ -213,7 +215,12 @@ static int cm_launch(cudaStream_t st, const CiParams &p)
 {
     constexpr int base = ((LT == 1) ? CI_MID_DMAX1 : CI_MID_DMAX) * (4 + 4 + 4 + 4 + 8);
     constexpr int dyn = base + (LT == 2 ? CI_MID_DMAX * (CI_MID_DMAX | 1) * 4 : 0);
-    static int ctas_per_sm = 0;  // per instantiation
+    // per instantiation AND per device (see ci_small.cu)
+    static std::atomic<int> ctas_of_device[CUSK_MAX_DEVICES];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = (dev >= 0 && dev < CUSK_MAX_DEVICES) ? dev : 0;
+    int ctas_per_sm = ctas_of_device[dev].load(std::memory_order_acquire);
     if (!ctas_per_sm) {
         if (cudaFuncSetAttribute(ci_mid_kernel<HET, LT>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn) != cudaSuccess) {
             cusk_set_error("cudaFuncSetAttribute(ci_mid_kernel<%d>, %d B): %s", LT, dyn,
@@ -225,6 +232,7 @@ static int cm_launch(cudaStream_t st, const CiParams &p)
             nb < 1)
             nb = 1;
         ctas_per_sm = nb;
+        ctas_of_device[dev].store(nb, std::memory_order_release);
     }
     ci_mid_kernel<HET, LT><<<148 * ctas_per_sm, CM_NTHREADS, dyn, st>>>(p);
     return CUSK_OK;

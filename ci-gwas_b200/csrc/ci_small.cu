@@ -20,6 +20,8 @@
 // start, removals clear bits (het engine) or lower the slot's minimum rank (individual-level engine).
 //
 // Algorithmic bytes per test: 4 (l + 2).
+#include <atomic>
+
 #include "skeleton.cuh"
 
 #define CS_DMAX CI_SMALL_DMAX  // rows up to this degree (plan_kernel picks the kernel per level)
@@ -295,7 +297,13 @@ static int cs_launch(cudaStream_t st, const CiParams &p)
 {
     constexpr int NT = CS_NTHREADS(LT);
     constexpr int dyn = (LT <= CS_LREG) ? 0 : LT * (LT - 1) / 2 * 8 * NT;
-    static int ctas_per_sm = 0;  // per instantiation
+    // per instantiation AND per device: function attributes belong to the device's context, and the block
+    // scheduler / the threaded sharded mode drive several devices from one process
+    static std::atomic<int> ctas_of_device[CUSK_MAX_DEVICES];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = (dev >= 0 && dev < CUSK_MAX_DEVICES) ? dev : 0;
+    int ctas_per_sm = ctas_of_device[dev].load(std::memory_order_acquire);
     if (!ctas_per_sm) {
         if (dyn > 0 && cudaFuncSetAttribute(ci_small_kernel<HET, LT>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn) !=
                            cudaSuccess) {
@@ -307,6 +315,7 @@ static int cs_launch(cudaStream_t st, const CiParams &p)
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ci_small_kernel<HET, LT>, NT, dyn) != cudaSuccess || nb < 1)
             nb = 1;
         ctas_per_sm = nb;
+        ctas_of_device[dev].store(nb, std::memory_order_release);
     }
     ci_small_kernel<HET, LT><<<148 * ctas_per_sm, NT, dyn, st>>>(p);
     return CUSK_OK;

@@ -2,6 +2,7 @@
 #pragma once
 #include "common.cuh"
 
+#define CUSK_MAX_DEVICES 64     // per-device launch state of the CI kernels
 #define CI_NWARPS 16
 #define CI_NTHREADS (CI_NWARPS * 32)
 #define CI_ZB 4                 // leaf (z) register blocking
