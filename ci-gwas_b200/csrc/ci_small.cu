@@ -88,8 +88,15 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
     const bool het_general = HET && p.N != nullptr;
     const bool use_time = HET && p.time_index != nullptr;
     const double npairs = 0.5 * (double)((l + 2) * (l + 1));
-    for (int e = tid; e < (CS_DMAX + 1) * (CUSK_ML + 1); e += NT)
-        s_binom[e] = (unsigned)binom64(e / (CUSK_ML + 1), e % (CUSK_ML + 1));
+    if (tid < 32) {
+        // Pascal's triangle, one row per step: lane r holds C(m, r)
+        unsigned prev = (lane == 0) ? 1u : 0u;  // row m = 0
+        for (int m = 0; m <= CS_DMAX; m++) {
+            if (lane <= CUSK_ML) s_binom[m * (CUSK_ML + 1) + lane] = prev;
+            const unsigned left = __shfl_up_sync(FULLMASK, prev, 1);
+            prev = (lane == 0) ? 1u : prev + left;  // C(m+1, r) = C(m, r) + C(m, r-1); < 2^32 for m <= 33, r <= 14
+        }
+    }
     __syncthreads();
     CsWarp &S = s_w[warp];
     u64 my_tests = 0;

@@ -167,6 +167,15 @@ __device__ __forceinline__ u64 block_scan_excl_u64(u64 v, u64 *s_warp, u64 *tota
     return s_warp[wid] + inc - v;
 }
 
+// ceil(a / b) with the 32-bit divider when both operands fit (they nearly always do; a 64-bit division is
+// ~4x the instructions, and the plan phase below is one CTA on the critical path of every level)
+__device__ __forceinline__ u64 ceil_div_u64(u64 a, u64 b)
+{
+    if (a == 0) return 0;
+    if (((a | b) >> 32) == 0) return (u64)(((unsigned)a - 1u) / (unsigned)b + 1u);
+    return (a - 1) / b + 1;
+}
+
 // Degrees and level plan in one launch.  Row phase (every CTA, a warp per row): popcount of the bitmap
 // row, C(d, l) and the row's share of the level totals.  The CTA that finishes last then plans the level:
 // CSR offsets, whether the level runs (src/cuPC-S.cu:154-159: iff max_degree - 1 >= l), the work items of
@@ -327,17 +336,17 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
             // with d <= 64 stage in a couple of round trips whatever the item size)
             const u64 stage_cost = (cls == 0 && d > 64 && d <= 200) ? 4 * (u64)d * (u64)d : 0;
             if (tgt < stage_cost) tgt = stage_cost;
-            items = (tests + tgt - 1) / tgt;
+            items = ceil_div_u64(tests, tgt);
             if (items > c) items = c;
             if (items < 1) items = 1;
-            u64 ch = (c + items - 1) / items;
+            u64 ch = ceil_div_u64(c, items);
             if (cls == 1 && ch < 32) ch = (c < 32) ? c : 32;  // a lane per rank
             if (cls == 2) {
                 // a thread per (rank, 32-neighbour chunk): at least a CTA's worth of them per item
                 const u64 minr = (u64)((256 + ((d + 31) >> 5) - 1) / ((d + 31) >> 5));
                 if (ch < minr) ch = (c < minr) ? c : minr;
             }
-            items = (c + ch - 1) / ch;
+            items = ceil_div_u64(c, ch);
             chunk[r] = ch;
         } else if (r < n) {
             chunk[r] = 0;
@@ -380,7 +389,7 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint32_t *__restrict
         if (chx != 0) {
             const int dd = deg[r];
             const u64 nc = binom64(dd, l);
-            const u64 cnt = (nc + chx - 1) / chx;
+            const u64 cnt = ceil_div_u64(nc, chx);
             const int is = itemstart[r];
             const int cls = is >> 24;
             CiItem *table = (cls == 1) ? items_small : ((cls == 2) ? items_mid : items);
