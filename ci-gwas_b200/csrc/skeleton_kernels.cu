@@ -167,6 +167,44 @@ __device__ __forceinline__ u64 block_scan_excl_u64(u64 v, u64 *s_warp, u64 *tota
     return s_warp[wid] + inc - v;
 }
 
+// two exclusive block scans behind one set of barriers (s_warp: 2 x 33 entries)
+__device__ __forceinline__ void block_scan_excl_2u64(u64 v0, u64 v1, u64 *s_warp, u64 *ex0, u64 *ex1, u64 *tot0,
+                                                     u64 *tot1)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    u64 i0 = v0, i1 = v1;
+    for (int o = 1; o < 32; o <<= 1) {
+        const u64 t0 = __shfl_up_sync(0xffffffffu, i0, o);
+        const u64 t1 = __shfl_up_sync(0xffffffffu, i1, o);
+        if (lane >= o) {
+            i0 += t0;
+            i1 += t1;
+        }
+    }
+    __syncthreads();
+    if (lane == 31) {
+        s_warp[wid] = i0;
+        s_warp[33 + wid] = i1;
+    }
+    __syncthreads();
+    if (wid < 2) {
+        u64 *sw = s_warp + 33 * wid;
+        const u64 w = (lane < (int)(blockDim.x >> 5)) ? sw[lane] : 0;
+        u64 winc = w;
+        for (int o = 1; o < 32; o <<= 1) {
+            const u64 t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += t;
+        }
+        sw[lane] = winc - w;
+        if (lane == 31) sw[32] = winc;
+    }
+    __syncthreads();
+    *tot0 = s_warp[32];
+    *tot1 = s_warp[33 + 32];
+    *ex0 = s_warp[wid] + i0 - v0;
+    *ex1 = s_warp[33 + wid] + i1 - v1;
+}
+
 // ceil(a / b) with the 32-bit divider when both operands fit (they nearly always do; a 64-bit division is
 // ~4x the instructions, and the plan phase below is one CTA on the critical path of every level)
 __device__ __forceinline__ u64 ceil_div_u64(u64 a, u64 b)
@@ -188,7 +226,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                                                            int *work_counter_small, int *work_counter_mid, int world,
                                                            int ipsm_shallow, int ipsm_deep, int ipsm_small, int ipsm_mid)
 {
-    __shared__ u64 s_warp[33];
+    __shared__ u64 s_warp2[66];
     __shared__ u64 s_acc[4];
     __shared__ int s_maxdeg, s_infeasible, s_last;
     __shared__ u64 s_target, s_target_small, s_target_mid;
@@ -259,33 +297,8 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
     const u64 tot_small = *(volatile u64 *)&ctl->acc_small;
     const u64 tot_canon = *(volatile u64 *)&ctl->acc_canon;
     const u64 tot_mid = *(volatile u64 *)&ctl->acc_mid;
-    // CSR offsets
-    u64 carry = 0;
-    for (int base = 0; base < n; base += blockDim.x) {
-        const int r = base + tid;
-        const int d = (r < n) ? __ldcg(&deg[r]) : 0;
-        u64 tot;
-        const u64 ex = block_scan_excl_u64((u64)d, s_warp, &tot);
-        if (r < n) rowptr[r] = (int)(carry + ex);
-        carry += tot;
-    }
-    if (tid == 0) rowptr[n] = (int)carry;
     const bool runs = (maxdeg - 1 >= l) && !infeasible;
     if (tid == 0) {
-        ctl->maxdeg = maxdeg;
-        ctl->nnz = carry;
-        ctl->canon = (maxdeg - 1 >= l) ? tot_canon : 0;
-        ctl->executed = 0;
-        ctl->singular = 0;
-        ctl->infeasible = infeasible;
-        ctl->done = runs ? 0 : 1;
-        double th = th_level;
-        if (th_level < 0) {
-            const double m = (double)__float2int_rz(n_uniform);
-            th = th_het / sqrt(m - (double)l - 3.0);
-        }
-        const double t = tanh(th);
-        ctl->T2 = t * t;
         // Items per SM of ci_level_kernel: the first two levels are throughput-bound with very uneven rows
         // and want many items for balance; from level 3 on an item's cost is dominated by the per-prefix
         // factorisation, which consecutive conditioning sets share, so few large items win (sweep on the
@@ -302,33 +315,29 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         u64 tm = tot_mid / ((u64)148 * (u64)(ipsm_mid > 0 ? ipsm_mid : 1) * (u64)world);
         if (tm < 32) tm = 32;
         s_target_mid = tm;
-        *work_counter = 0;
-        *work_counter_small = 0;
-        *work_counter_mid = 0;
     }
     __syncthreads();
-    if (!runs) {
-        if (tid == 0) {
-            ctl->nitems = 0;
-            ctl->nitems_small = 0;
-            ctl->nitems_mid = 0;
-        }
-        return;
-    }
-    // Work items.  A row's C(d,l) conditioning sets are cut into items of `chunk` ranks; the two kernels
-    // have separate item tables, itemstart[r] is the row's offset in its own (stored as ~offset for a
-    // short row).
-    // The three kernels have separate item tables; itemstart[r] = class * 2^24 + offset in the class's table
-    // (class 0: ci_level_kernel, 1: ci_small_kernel, 2: ci_mid_kernel).
+    // One pass over the rows: CSR offsets (scan of the degrees) and work items.  A row's C(d,l) conditioning
+    // sets are cut into items of `chunk` ranks.  The three kernels have separate item tables; itemstart[r] =
+    // class * 2^24 + offset in the class's table (class 0: ci_level_kernel, 1: ci_small_kernel, 2:
+    // ci_mid_kernel).  The next block of rows is loaded before the current one is scanned.
     const u64 target = s_target, target_small = s_target_small, target_mid = s_target_mid;
-    carry = 0;  // three 21-bit fields: items of ci_level_kernel, ci_small_kernel, ci_mid_kernel
+    u64 carry = 0;        // directed edges so far
+    u64 carry_items = 0;  // three 21-bit fields: items of ci_level_kernel, ci_small_kernel, ci_mid_kernel
+    int d_next = (tid < n) ? __ldcg(&deg[tid]) : 0;
+    u64 c_next = (tid < n) ? __ldcg(&chunk[tid]) : 0;
     for (int base = 0; base < n; base += blockDim.x) {
         const int r = base + tid;
-        const int d = (r < n) ? __ldcg(&deg[r]) : 0;
+        const int d = d_next;
+        const u64 c = c_next;
+        {
+            const int rn = r + (int)blockDim.x;
+            d_next = (rn < n) ? __ldcg(&deg[rn]) : 0;
+            c_next = (rn < n) ? __ldcg(&chunk[rn]) : 0;
+        }
         u64 items = 0;
         const int cls = (d <= dsmall) ? 1 : ((d <= dmid) ? 2 : 0);
-        if (r < n && d > l) {
-            const u64 c = __ldcg(&chunk[r]);
+        if (runs && r < n && d > l) {
             const u64 tests = c * (u64)(d - l);
             u64 tgt = (cls == 1) ? target_small : ((cls == 2) ? target_mid : target);
             // an item of ci_level_kernel re-stages the row's d x d submatrix: keep at least ~4 tests per
@@ -348,21 +357,41 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
             }
             items = ceil_div_u64(c, ch);
             chunk[r] = ch;
-        } else if (r < n) {
+        } else if (runs && r < n) {
             chunk[r] = 0;
         }
-        u64 tot;
-        const u64 ex = block_scan_excl_u64(items << (21 * cls), s_warp, &tot);
+        u64 ex_d, ex_i, tot_d, tot_i;
+        block_scan_excl_2u64((u64)d, items << (21 * cls), s_warp2, &ex_d, &ex_i, &tot_d, &tot_i);
         if (r < n) {
-            const u64 at = carry + ex;
+            rowptr[r] = (int)(carry + ex_d);
+            const u64 at = carry_items + ex_i;
             itemstart[r] = (cls << 24) | (int)((at >> (21 * cls)) & 0x1fffffu);
         }
-        carry += tot;
+        carry += tot_d;
+        carry_items += tot_i;
     }
     if (tid == 0) {
-        ctl->nitems = (int)(carry & 0x1fffffu);
-        ctl->nitems_small = (int)((carry >> 21) & 0x1fffffu);
-        ctl->nitems_mid = (int)((carry >> 42) & 0x1fffffu);
+        rowptr[n] = (int)carry;
+        ctl->maxdeg = maxdeg;
+        ctl->nnz = carry;
+        ctl->canon = (maxdeg - 1 >= l) ? tot_canon : 0;
+        ctl->executed = 0;
+        ctl->singular = 0;
+        ctl->infeasible = infeasible;
+        double th = th_level;
+        if (th_level < 0) {
+            const double m = (double)__float2int_rz(n_uniform);
+            th = th_het / sqrt(m - (double)l - 3.0);
+        }
+        const double t = tanh(th);
+        ctl->T2 = t * t;
+        *work_counter = 0;
+        *work_counter_small = 0;
+        *work_counter_mid = 0;
+        ctl->nitems = runs ? (int)(carry_items & 0x1fffffu) : 0;
+        ctl->nitems_small = runs ? (int)((carry_items >> 21) & 0x1fffffu) : 0;
+        ctl->nitems_mid = runs ? (int)((carry_items >> 42) & 0x1fffffu) : 0;
+        ctl->done = runs ? 0 : 1;
     }
 }
 
