@@ -27,6 +27,9 @@ ALPHA = 1e-4
 NUM_SAMPLES = 458000
 M_MARKERS, P_TRAITS, MAXLEVEL = 3000, 17, 14
 C2_KW = dict(causal_per_trait=12, window=12, max_parents=4, wlo=0.6, whi=0.95)
+WORKLOAD = ("cuskss single LD block 3000 markers + 17 traits (n_var 3017), max level 14, alpha 1e-4, 458000 samples, "
+            "time index markers 0 / traits 1 as `mps cuskss` sets it (BASELINE.json configs[1]); one block per GPU "
+            "per step")
 SAMPLE_MARKERS = M_MARKERS  # cpu_baseline / reference arm: the whole block finishes in seconds on the host cores
 
 
@@ -135,8 +138,7 @@ def run_reference_arm(args, rank, world):
     line = {"impl": "reference", "metric": "ci_tests_per_s", "value": val, "unit": "tests/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "cuskss single LD block 3000 markers + 17 traits, max level 14, alpha 1e-4 "
-                                   "(BASELINE.json configs[1])", "sample": sample},
+            "config": {"workload": WORKLOAD, "generator": dict(C2_KW, seed_stream="2+rank"), "sample": sample},
             "cpu_baseline": {"value": val, "unit": "tests/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "tests/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -288,9 +290,7 @@ def main():
             "metric": "ci_tests_per_s", "value": tests_all / (dev_ms_max * 1e-3), "unit": "tests/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "cuskss single LD block 3000 markers + 17 traits (n_var 3017), max level 14, "
-                                   "alpha 1e-4, 458000 samples, time index markers 0 / traits 1 as `mps cuskss` sets it "
-                                   "(BASELINE.json configs[1]); one block per GPU per step",
+            "config": {"workload": WORKLOAD,
                        "generator": dict(C2_KW, seed_stream="2+rank"), "l2": "flushed between timed iterations "
                        "(256 MB write)", "tests_per_block": tests_total // args.steps,
                        "tests_canonical_per_level": last_stats["tests_canonical"],
