@@ -14,6 +14,8 @@ from .lib import (  # noqa: F401
     hetcor_threshold,
     library_path,
     load_library,
+    merge_block_outputs,
     mps_path,
+    reformat_cuskss_merged,
     threshold_array,
 )

@@ -167,6 +167,10 @@ int run_cusk_all(const CuskArgs &a, const std::vector<int> &devices, bool resume
 int run_cuskss_all(const CuskssArgs &a, const std::string &mxm_pattern, const std::vector<int> &devices, bool resume);
 std::vector<int> devices_from_env();
 
+// post-processing of the block outputs (merge.cpp; cusk_postprocessing/merge_blocks.py:361-425): host only
+int merge_block_outputs(const std::string &blockfile, const std::string &outdir, const std::string &out_base);
+int reformat_cuskss_merged(const std::string &cusk_dir);
+
 int mps_main(int argc, char **argv);
 
 }  // namespace cuskhost

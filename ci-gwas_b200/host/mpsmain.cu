@@ -31,6 +31,8 @@ commands:
     cuskss                  Run cuda-skeleton on a block of markers and traits with pre-computed correlations.
     cusk-all                cusk for every block of a .blocks file, scheduled over all visible GPUs
     cuskss-all              cuskss for every block of a .blocks file, scheduled over all visible GPUs
+    merge                   Merge the outputs of all blocks (ci-gwas.py merge-block-outputs): <blockfile> <outdir>
+    reformat-merged         Rewrite <outdir>/cuskss_merged.* in the merged-blocks format: <outdir>
 )";
 
 const char *CUSK_USAGE = R"(
@@ -158,6 +160,22 @@ int dispatch(int argc, char **argv)
         std::cout << MPS_USAGE << std::endl;
         return EXIT_SUCCESS;
     }
+    // host-only post-processing (cusk_postprocessing/merge_blocks.py; no device is touched)
+    if (cmd == "merge") {
+        if (argc != 4) {
+            std::cout << "\nusage: mps merge <.blocks> <cusk-output-dir>\n" << std::endl;
+            return 1;
+        }
+        std::string dir = argv[3];
+        return merge_block_outputs(argv[2], dir, dir + "/merged_blocks");  // ci-gwas.py:459-464
+    }
+    if (cmd == "reformat-merged") {
+        if (argc != 3) {
+            std::cout << "\nusage: mps reformat-merged <cusk-output-dir>\n" << std::endl;
+            return 1;
+        }
+        return reformat_cuskss_merged(argv[2]);  // ci-gwas.py:452-456
+    }
     const std::vector<int> devs = devices_from_env();
     const int dev0 = devs.empty() ? 0 : devs[0];
     if (cmd == "cuskss") {
@@ -282,6 +300,36 @@ extern "C" int cusk_prep_bed(cusk_ctx *ctx, const char *bfiles)
     }
     try {
         return cuskhost::run_prep(ctx, bfiles, false);
+    } catch (const cuskhost::HostError &e) {
+        cusk_set_error("%s", e.msg.c_str());
+        return CUSK_E_ARG;
+    }
+}
+
+// merge_block_outputs(blockfile, outdir).write_mm(out_base) and reformat_cuskss_merged_output(dir).write_mm(...)
+// (cusk_postprocessing/merge_blocks.py:361-425, :300-325); host only
+extern "C" int cusk_merge_block_outputs(const char *blockfile, const char *outdir, const char *out_base)
+{
+    if (!blockfile || !outdir || !out_base) {
+        cusk_set_error("cusk_merge_block_outputs: NULL argument");
+        return CUSK_E_ARG;
+    }
+    try {
+        return cuskhost::merge_block_outputs(blockfile, outdir, out_base);
+    } catch (const cuskhost::HostError &e) {
+        cusk_set_error("%s", e.msg.c_str());
+        return CUSK_E_ARG;
+    }
+}
+
+extern "C" int cusk_reformat_cuskss_merged(const char *cusk_dir)
+{
+    if (!cusk_dir) {
+        cusk_set_error("cusk_reformat_cuskss_merged: NULL argument");
+        return CUSK_E_ARG;
+    }
+    try {
+        return cuskhost::reformat_cuskss_merged(cusk_dir);
     } catch (const cuskhost::HostError &e) {
         cusk_set_error("%s", e.msg.c_str());
         return CUSK_E_ARG;

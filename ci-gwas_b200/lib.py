@@ -172,6 +172,26 @@ def hetcor_threshold(alpha):
     return float(load_library().cusk_hetcor_threshold(C.c_float(alpha)))
 
 
+def merge_block_outputs(blockfile, outdir, out_base=None):
+    """merge_block_outputs(blockfile, outdir).write_mm(out_base) (cusk_postprocessing/merge_blocks.py:361-403, :300-325;
+    ci-gwas.py:459-464): <out_base>_sam.mtx, _scm.mtx, .mdim, .ixs; host only"""
+    lib = load_library()
+    lib.cusk_merge_block_outputs.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
+    if out_base is None:
+        out_base = os.path.join(outdir, "merged_blocks")
+    if lib.cusk_merge_block_outputs(os.fsencode(blockfile), os.fsencode(outdir), os.fsencode(out_base)) != 0:
+        raise CuskError(lib.cusk_last_error().decode())
+
+
+def reformat_cuskss_merged(cusk_dir):
+    """reformat_cuskss_merged_output(cusk_dir).write_mm(cusk_dir/cuskss_merged) (merge_blocks.py:406-425;
+    ci-gwas.py:452-456); host only"""
+    lib = load_library()
+    lib.cusk_reformat_cuskss_merged.argtypes = [C.c_char_p]
+    if lib.cusk_reformat_cuskss_merged(os.fsencode(cusk_dir)) != 0:
+        raise CuskError(lib.cusk_last_error().decode())
+
+
 class Context:
     """One device + stream + reusable workspace (cusk_ctx)."""
 

@@ -1,13 +1,15 @@
 #!/usr/bin/env python
 """Command-line front end of the B200 skeleton path: the `prep-bed`, `cusk` and `cuskss` sub-commands of the
 reference's `ci-gwas.py` (ci-gwas.py:55-62, :95-150, :152-252; the het and merged modes are `cuskss` with
-`--mxp-se/--pxp-se` and `--marker-indices`), with the same arguments, defaults and input checks
-(ci-gwas.py:386-457), driving `ci-gwas_b200/mps` instead of `cusk/build/apps/mps`.
+`--mxp-se/--pxp-se` and `--marker-indices`) and `merge-block-outputs` (ci-gwas.py:254-270, :459-464), with the same
+arguments, defaults and input checks (ci-gwas.py:386-457), driving `ci-gwas_b200/mps` instead of
+`cusk/build/apps/mps`; the merge and the reformatting of a merged skeleton's output (ci-gwas.py:452-456) are the
+native `mps merge` / `mps reformat-merged` instead of cusk_postprocessing/merge_blocks.py.
 
 Additions: `cusk-all` / `cuskss-all` run every block of a block file on all GPUs of the box (LPT schedule, resume
 by existing outputs); `--gpus` picks the devices; `cuskss --shard-gpus N` deals the level-l tests of ONE merged
-skeleton to N GPUs (NCCL exchange per level).  Everything else of ci-gwas.py (block, merge-block-outputs,
-sepselect, srfci, mvivw, ...) is outside this path: run it from the reference on the files written here.
+skeleton to N GPUs (NCCL exchange per level).  Everything else of ci-gwas.py (block, sepselect, srfci, mvivw, ...)
+is outside this path: run it from the reference on the files written here.
 """
 import argparse
 import os
@@ -87,15 +89,12 @@ def cuskss(args):
     check_cuskss(args)
     run(["cuskss"] + cuskss_argv(args, args.block_index, args.marker_indices), args)
     if args.marker_indices != "NULL":
-        # ci-gwas.py:452-456 rewrites the merged output in the merge-block-outputs format with the reference's
-        # own post-processing package; that package is not part of this path: use it when it is importable
-        try:
-            from cusk_postprocessing.merge_blocks import reformat_cuskss_merged_output
-        except ImportError:
-            print("cusk_postprocessing not importable: left cuskss_merged.{mdim,ixs,adj,corr} as written by mps",
-                  file=sys.stderr)
-            return
-        reformat_cuskss_merged_output(cusk_dir=args.outdir).write_mm(basepath=f"{args.outdir}/cuskss_merged")
+        # ci-gwas.py:452-456: rewrite the merged output in the merge-block-outputs format
+        run(["reformat-merged", args.outdir], args)
+
+
+def merge_blocks(args):
+    run(["merge", args.blockfile, args.cusk_output_dir], args)  # ci-gwas.py:459-464
 
 
 def cuskss_all(args):
@@ -181,6 +180,10 @@ def build_parser():
     p = sub.add_parser("cuskss-all", help="cuskss for every block of the block file, on all GPUs")
     add_cuskss_args(p, False)
     p.set_defaults(func=cuskss_all)
+    p = sub.add_parser("merge-block-outputs", help="Merge outputs from multiple blocks processed with cusk or cuskss")
+    p.add_argument("cusk_output_dir", metavar="cusk-output-dir", type=str, help="output directory of cusk or cuskss")
+    p.add_argument("blockfile", type=str, help="file with genomic block definitions (output of ci-gwas block)")
+    p.set_defaults(func=merge_blocks)
     return ap
 
 

@@ -179,6 +179,14 @@ int cusk_cuskss_square_inputs(const char *mxm, const char *mxp, const char *mxp_
 int cusk_subset_variables(const int *G, int num_var, int num_markers, int max_depth, int *out_sel);
 int cusk_load_phen(const char *path, int64_t *num_samples, int64_t *num_phen, float **data_out);
 void cusk_free(void *p);
+/* post-processing of the block outputs, host only.
+ * cusk_merge_block_outputs = merge_block_outputs(blockfile, outdir).write_mm(out_base)
+ * (cusk_postprocessing/merge_blocks.py:361-403, :300-325; `ci-gwas.py merge-block-outputs`, ci-gwas.py:459-464):
+ * writes <out_base>_sam.mtx, <out_base>_scm.mtx, <out_base>.mdim, <out_base>.ixs, byte-identical to the reference.
+ * cusk_reformat_cuskss_merged = reformat_cuskss_merged_output(cusk_dir).write_mm(cusk_dir/cuskss_merged)
+ * (merge_blocks.py:406-425; the step after `mps cuskss` with marker indices, ci-gwas.py:452-456). */
+int cusk_merge_block_outputs(const char *blockfile, const char *outdir, const char *out_base);
+int cusk_reformat_cuskss_merged(const char *cusk_dir);
 
 /* ---- drop-in signatures of the reference -------------------------------------------------- */
 /* include/mps/corr_host.h: cu_marker_phen_corr_pearson / cu_corr_pearson_npn (C++ linkage in the

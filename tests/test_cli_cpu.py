@@ -17,9 +17,10 @@ CLI = os.path.join(ROOT, "ci_gwas_b200.py")
 def fake_mps(tmp_path):
     rec = tmp_path / "argv.json"
     exe = tmp_path / "mps"
-    exe.write_text("#!%s\nimport json, os, sys\njson.dump({'argv': sys.argv[1:], 'devices': os.environ.get('CUSK_DEVICES'), "
-                   "'shard': os.environ.get('CUSK_SHARD_GPUS')}, open(%r, 'w'))\nsys.exit(int(os.environ.get('FAKE_RC', '0')))\n"
-                   % (sys.executable, str(rec)))
+    exe.write_text("#!%s\nimport json, os, sys\np = %r\nprev = json.load(open(p))['calls'] if os.path.exists(p) else []\n"
+                   "json.dump({'argv': sys.argv[1:], 'devices': os.environ.get('CUSK_DEVICES'), "
+                   "'shard': os.environ.get('CUSK_SHARD_GPUS'), 'calls': prev + [sys.argv[1:]]}, open(p, 'w'))\n"
+                   "sys.exit(int(os.environ.get('FAKE_RC', '0')))\n" % (sys.executable, str(rec)))
     exe.chmod(exe.stat().st_mode | stat.S_IEXEC)
     return str(exe), str(rec)
 
@@ -62,13 +63,22 @@ def test_cuskss_modes_and_checks(fake_mps):
     assert cli(base + ["--marker-indices", "ix.bin", "--mxm", "m.bin", "--mxp", "mxp.txt", "--mxp-se", "a", "--pxp-se", "b",
                        "--shard-gpus", "4"], mps).returncode == 0
     r = json.load(open(rec))
-    assert r["argv"][:10] == ["cuskss", "m.bin", "mxp.txt", "a", "pxp.txt", "b", "NULL", "0", "NULL", "ix.bin"]
+    assert r["calls"][-2][:10] == ["cuskss", "m.bin", "mxp.txt", "a", "pxp.txt", "b", "NULL", "0", "NULL", "ix.bin"]
     assert r["shard"] == "4"
+    # ci-gwas.py:452-456: a merged skeleton's output is then rewritten in the merge-block-outputs format
+    assert r["calls"][-1] == ["reformat-merged", "./"]
     # all blocks
     assert cli(["cuskss-all", "--pxp", "pxp.txt", "--alpha", "0.01", "--num-samples", "1000", "--blockfile", "b",
                 "--mxm", "mxm/{}.bin", "--mxp", "mxp.txt"], mps).returncode == 0
     assert json.load(open(rec))["argv"] == ["cuskss-all", "mxm/{}.bin", "mxp.txt", "NULL", "pxp.txt", "NULL", "NULL", "b",
                                             "0.01", "3", "14", "1", "1000", "./"]
+
+
+def test_merge_block_outputs(fake_mps):
+    mps, rec = fake_mps
+    # ci-gwas.py:254-270: positional <cusk-output-dir> <blockfile>
+    assert cli(["merge-block-outputs", "out/dir", "all.blocks"], mps).returncode == 0
+    assert json.load(open(rec))["argv"] == ["merge", "all.blocks", "out/dir"]
 
 
 def test_exit_status_propagates(fake_mps):
