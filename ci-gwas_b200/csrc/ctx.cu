@@ -194,6 +194,9 @@ static double qnorm(double p)
 }
 
 // src/cuPC_call_prep.cpp:13-23
+// scipy.stats.norm.ppf in double precision (cusk_postprocessing/sepselect.py:26-27)
+extern "C" double cusk_qnorm(double p) { return qnorm(p); }
+
 extern "C" void cusk_threshold_array(int n, float alpha, float *out15)
 {
     const float p = 0.5f * alpha;

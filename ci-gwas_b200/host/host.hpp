@@ -170,6 +170,10 @@ std::vector<int> devices_from_env();
 // post-processing of the block outputs (merge.cpp; cusk_postprocessing/merge_blocks.py:361-425): host only
 int merge_block_outputs(const std::string &blockfile, const std::string &outdir, const std::string &out_base);
 int reformat_cuskss_merged(const std::string &cusk_dir);
+// separating-set selection + v-structure orientation on a merged skeleton (sepselect.cpp;
+// cusk_postprocessing/sepselect.py:429-584); the search runs on ctx's device
+int run_sepselect(cusk_ctx *ctx, const std::string &stem, double alpha, long num_samples, const std::string &prior_path,
+                  const std::string &out_stem);
 
 int mps_main(int argc, char **argv);
 

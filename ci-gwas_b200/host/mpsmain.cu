@@ -33,6 +33,8 @@ commands:
     cuskss-all              cuskss for every block of a .blocks file, scheduled over all visible GPUs
     merge                   Merge the outputs of all blocks (ci-gwas.py merge-block-outputs): <blockfile> <outdir>
     reformat-merged         Rewrite <outdir>/cuskss_merged.* in the merged-blocks format: <outdir>
+    sepselect               Maximal separating sets and v-structures of a merged skeleton (ci-gwas.py sepselect,
+                            orient-v-structs): <merged-stem> <alpha> <num-samples> [<orientation-prior>|NULL [<out-stem>]]
 )";
 
 const char *CUSK_USAGE = R"(
@@ -197,6 +199,23 @@ int dispatch(int argc, char **argv)
         cusk_ctx_destroy(ctx);
         return finish(rc);
     }
+    if (cmd == "sepselect") {
+        if (argc < 5 || argc > 7) {
+            std::cout << "\nusage: mps sepselect <merged-stem> <alpha> <num-samples> [<orientation-prior>|NULL [<out-stem>]]\n"
+                      << std::endl;
+            return 1;
+        }
+        const std::string stem = argv[2];
+        const std::string prior = (argc > 5 && strcmp(argv[5], "NULL")) ? argv[5] : "";
+        // ci-gwas.py:469,475: <dirname of the stem>/max_sep_min_pc
+        const size_t sl = stem.rfind('/');
+        const std::string out = argc > 6 ? argv[6] : (sl == std::string::npos ? std::string(".") : stem.substr(0, sl)) + "/max_sep_min_pc";
+        cusk_ctx *ctx = make_ctx(dev0);
+        const int rc = run_sepselect(ctx, stem, std::stod(argv[3]), std::stol(argv[4]), prior, out);
+        cusk_ctx_destroy(ctx);
+        if (rc == CUSK_OK) std::cout << "Sepselect / v-structs done." << std::endl;  // ci-gwas.py:476
+        return finish(rc);
+    }
     if (cmd == "prep") {
         if (argc != 3 || !strcmp(argv[2], "--help") || !strcmp(argv[2], "-h")) {
             std::cout << "\nusage: mps prep <.bfiles>\n" << std::endl;
@@ -316,6 +335,25 @@ extern "C" int cusk_merge_block_outputs(const char *blockfile, const char *outdi
     }
     try {
         return cuskhost::merge_block_outputs(blockfile, outdir, out_base);
+    } catch (const cuskhost::HostError &e) {
+        cusk_set_error("%s", e.msg.c_str());
+        return CUSK_E_ARG;
+    }
+}
+
+extern "C" int cusk_sepselect(cusk_ctx *ctx, const char *stem, double alpha, int64_t num_samples, const char *prior_path,
+                              const char *out_stem)
+{
+    if (!stem || !out_stem) {
+        cusk_set_error("cusk_sepselect: NULL argument");
+        return CUSK_E_ARG;
+    }
+    if (!ctx) {
+        cusk_set_error("cusk_sepselect: no context (there is no CPU path)");
+        return CUSK_E_NODEVICE;
+    }
+    try {
+        return cuskhost::run_sepselect(ctx, stem, alpha, (long)num_samples, prior_path ? prior_path : "", out_stem);
     } catch (const cuskhost::HostError &e) {
         cusk_set_error("%s", e.msg.c_str());
         return CUSK_E_ARG;

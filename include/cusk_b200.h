@@ -188,6 +188,29 @@ void cusk_free(void *p);
 int cusk_merge_block_outputs(const char *blockfile, const char *outdir, const char *out_base);
 int cusk_reformat_cuskss_merged(const char *cusk_dir);
 
+/* ---- separating-set selection on a merged skeleton -----------------------------------
+ * cusk_sepselect = orient_v_structures_merged(stem, alpha, num_samples, prior).to_file(out_stem)
+ * (cusk_postprocessing/sepselect.py:576-584, :545-573; `ci-gwas.py sepselect` / `orient-v-structs`,
+ * ci-gwas.py:467-476): reads <stem>.mdim, <stem>_sam.mtx, <stem>_scm.mtx (what merge-block-outputs writes) and an
+ * optional orientation prior (int32 [P x P], NULL = none); writes <out_stem>.mdim, _sam.mtx, _scm.mtx, _spm.mtx,
+ * .atr, .ut, .ssm.  The greedy search of find_maximal_and_min_pcorr_sepsets_incr (sepselect.py:262-329) runs on
+ * the device, one thread per outer pair; fewer than 32 traits.
+ * cusk_sepselect_pairs is that search alone on host buffers: Ct = rows 0..P of the symmetric correlation matrix
+ * ([(P+1) x ld] doubles), pairs = [npairs][2] variable indices (i, j) with at least one end <= P, tmask[v] = bit t
+ * set when trait t < P is a neighbour of variable v, thr[l] = qnorm(1 - alpha/2) / sqrt(num_samples - l - 3) for
+ * l = 0..P.  cusk_qnorm: the normal quantile in double precision (scipy.stats.norm.ppf, sepselect.py:26-27). */
+#define CUSK_SS_MAXP 32
+typedef struct cusk_sepselect_result {
+    int32_t len;                /* size of the maximal separating set */
+    int32_t found_minimum;      /* the pair also has a "minimal partial correlation" set (sepselect.py:287-289) */
+    int32_t set[CUSK_SS_MAXP];  /* traits in the order they were added, -1 padded */
+} cusk_sepselect_result;
+int cusk_sepselect(cusk_ctx *ctx, const char *stem, double alpha, int64_t num_samples, const char *prior_path,
+                   const char *out_stem);
+int cusk_sepselect_pairs(cusk_ctx *ctx, const double *Ct, int64_t ld, int P, int n_var, const int *pairs,
+                         int64_t npairs, const uint32_t *tmask, const double *thr, cusk_sepselect_result *out);
+double cusk_qnorm(double p);
+
 /* ---- drop-in signatures of the reference -------------------------------------------------- */
 /* include/mps/corr_host.h: cu_marker_phen_corr_pearson / cu_corr_pearson_npn (C++ linkage in the
  * reference; exported here with C linkage and the same argument order) */
