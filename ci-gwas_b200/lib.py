@@ -220,6 +220,28 @@ class Context:
         if rc != 0:
             raise CuskError(f"rc={rc}: {self.lib.cusk_last_error().decode()}")
 
+    # -- separating-set selection on a merged skeleton (include/cusk_b200.h) ------------------
+    def sepselect(self, stem, alpha, num_samples, out_stem, prior_path=None):
+        """orient_v_structures_merged(stem, alpha, num_samples, prior).to_file(out_stem)
+        (cusk_postprocessing/sepselect.py:576-584, :545-573); the search runs on this context's device"""
+        self.lib.cusk_sepselect.argtypes = [C.c_void_p, C.c_char_p, C.c_double, C.c_int64, C.c_char_p, C.c_char_p]
+        self._check(self.lib.cusk_sepselect(self.h, os.fsencode(stem), float(alpha), int(num_samples),
+                                            None if prior_path is None else os.fsencode(prior_path), os.fsencode(out_stem)))
+
+    def sepselect_pairs(self, Ct, P, pairs, tmask, thr):
+        """The greedy search alone (sepselect.py:262-304) for a batch of outer pairs: Ct = rows 0..P of the correlation
+        matrix (float64 [(P+1), n_var]); returns (len[npairs], found_minimum[npairs], set[npairs, 32])"""
+        Ct = np.ascontiguousarray(Ct, np.float64)
+        pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+        tmask = np.ascontiguousarray(tmask, np.uint32)
+        thr = np.ascontiguousarray(thr, np.float64)
+        out = np.zeros((pairs.shape[0], 34), np.int32)  # cusk_sepselect_result: len, found_minimum, set[32]
+        self.lib.cusk_sepselect_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_int64,
+                                                  C.c_void_p, C.c_void_p, C.c_void_p]
+        self._check(self.lib.cusk_sepselect_pairs(self.h, Ct.ctypes.data, Ct.shape[1], int(P), Ct.shape[1], pairs.ctypes.data,
+                                                  pairs.shape[0], tmask.ctypes.data, thr.ctypes.data, out.ctypes.data))
+        return out[:, 0].copy(), out[:, 1].copy(), out[:, 2:].copy()
+
     # -- edge-sharded mode (one skeleton over several GPUs; include/cusk_b200.h "multi-GPU") --------
     def attach_comm(self, rank, world, unique_id):
         """Joins the NCCL communicator of `world` ranks; later skeleton calls on this context take every

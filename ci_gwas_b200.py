@@ -1,14 +1,15 @@
 #!/usr/bin/env python
 """Command-line front end of the B200 skeleton path: the `prep-bed`, `cusk` and `cuskss` sub-commands of the
 reference's `ci-gwas.py` (ci-gwas.py:55-62, :95-150, :152-252; the het and merged modes are `cuskss` with
-`--mxp-se/--pxp-se` and `--marker-indices`) and `merge-block-outputs` (ci-gwas.py:254-270, :459-464), with the same
+`--mxp-se/--pxp-se` and `--marker-indices`), `merge-block-outputs` (ci-gwas.py:254-270, :459-464), `sepselect` and
+`orient-v-structs` (ci-gwas.py:302-358, :467-476), with the same
 arguments, defaults and input checks (ci-gwas.py:386-457), driving `ci-gwas_b200/mps` instead of
 `cusk/build/apps/mps`; the merge and the reformatting of a merged skeleton's output (ci-gwas.py:452-456) are the
 native `mps merge` / `mps reformat-merged` instead of cusk_postprocessing/merge_blocks.py.
 
 Additions: `cusk-all` / `cuskss-all` run every block of a block file on all GPUs of the box (LPT schedule, resume
 by existing outputs); `--gpus` picks the devices; `cuskss --shard-gpus N` deals the level-l tests of ONE merged
-skeleton to N GPUs (NCCL exchange per level).  Everything else of ci-gwas.py (block, sepselect, srfci, mvivw, ...)
+skeleton to N GPUs (NCCL exchange per level).  Everything else of ci-gwas.py (block, srfci, mvivw, ...)
 is outside this path: run it from the reference on the files written here.
 """
 import argparse
@@ -95,6 +96,13 @@ def cuskss(args):
 
 def merge_blocks(args):
     run(["merge", args.blockfile, args.cusk_output_dir], args)  # ci-gwas.py:459-464
+
+
+def sepselect(args):
+    # ci-gwas.py:467-476: `sepselect` and `orient-v-structs` both end in MergedCuskResults.to_file(<dir>/max_sep_min_pc);
+    # the reference's `sepselect` stops there on its missing PAG, so both sub-commands run the orient-v-structs flow
+    prior = getattr(args, "orientation_prior", None)
+    run(["sepselect", args.cusk_result_stem, repr(args.alpha), args.num_samples, prior or "NULL"], args)
 
 
 def cuskss_all(args):
@@ -184,6 +192,18 @@ def build_parser():
     p.add_argument("cusk_output_dir", metavar="cusk-output-dir", type=str, help="output directory of cusk or cuskss")
     p.add_argument("blockfile", type=str, help="file with genomic block definitions (output of ci-gwas block)")
     p.set_defaults(func=merge_blocks)
+    for name, hlp in [("sepselect", "Compute maximal and partial-correlation-minimizing separation sets on merged cusk skeletons"),
+                      ("orient-v-structs", "Orient v-structures using maximal separation sets on merged cusk skeletons.")]:
+        p = sub.add_parser(name, help=hlp)  # ci-gwas.py:302-358
+        p.add_argument("cusk_result_stem", metavar="cusk-result-stem", type=str, help="outdir + stem of merged cusk results")
+        p.add_argument("alpha", type=Checked(float, "alpha", 0.0, 1.0), help="significance level for conditional independence tests")
+        p.add_argument("num_samples", metavar="num-samples", type=Checked(int, "num-samples", 1, None),
+                       help="number of samples used for computing correlations")
+        if name == "orient-v-structs":
+            p.add_argument("--orientation-prior", metavar="orientation-prior", type=str, default=None,
+                           help="matrix of (0, 1) (32 bit integers, binary) of dims (n_trait, n_trait) indicating directions to be forced.")
+        add_device_args(p)
+        p.set_defaults(func=sepselect)
     return ap
 
 

@@ -35,7 +35,7 @@ def triples(raw):
 
 
 def dense(raw):
-    return mmread(io.BytesIO(raw)).toarray()
+    return mmread(io.BytesIO(raw), spmatrix=False).toarray()
 
 
 def compare_outputs(case, d, stem="max_sep_min_pc"):

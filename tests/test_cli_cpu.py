@@ -81,6 +81,17 @@ def test_merge_block_outputs(fake_mps):
     assert json.load(open(rec))["argv"] == ["merge", "all.blocks", "out/dir"]
 
 
+def test_sepselect_and_orient_v_structs(fake_mps):
+    mps, rec = fake_mps
+    # ci-gwas.py:335-358 / :302-333: positional <cusk-result-stem> <alpha> <num-samples> [--orientation-prior]
+    assert cli(["sepselect", "out/merged_blocks", "0.0001", "458000"], mps).returncode == 0
+    assert json.load(open(rec))["argv"] == ["sepselect", "out/merged_blocks", "0.0001", "458000", "NULL"]
+    assert cli(["orient-v-structs", "out/merged_blocks", "0.001", "1000", "--orientation-prior", "p.bin", "--gpus", "2"], mps).returncode == 0
+    r = json.load(open(rec))
+    assert r["argv"] == ["sepselect", "out/merged_blocks", "0.001", "1000", "p.bin"] and r["devices"] == "2"
+    assert cli(["sepselect", "s", "1.5", "10"], mps).returncode == 2  # alpha above 1
+
+
 def test_exit_status_propagates(fake_mps):
     mps, _ = fake_mps
     assert cli(["prep-bed", "x"], mps, rc_env=1).returncode == 1
