@@ -49,6 +49,15 @@ extern "C" int cusk_sepselect_pairs(cusk_ctx *ctx, const double *Ct, int64_t ld,
             cusk_set_error("cusk_sepselect_pairs: pair %lld = (%d, %d) has no end among variables 0..%d", (long long)p, i, j, P);
             return CUSK_E_ARG;
         }
+        // an outer pair of an unshielded triple: i is not its own neighbour and j is not adjacent to i.  With an end of
+        // the pair among the candidates the reference inverts a matrix with a repeated index (LinAlgError, or a
+        // result decided by rounding noise)
+        const uint32_t mi = tmask[i];
+        if ((i < P && (mi >> i & 1u)) || (j < P && (mi >> j & 1u))) {
+            cusk_set_error("cusk_sepselect_pairs: pair %lld = (%d, %d): an end of the pair is among the trait neighbours of %d",
+                           (long long)p, i, j, i);
+            return CUSK_E_ARG;
+        }
     }
     if (npairs == 0) return CUSK_OK;
     CUSK_CUDA(cudaSetDevice(ctx->device));

@@ -197,8 +197,8 @@ int cusk_reformat_cuskss_merged(const char *cusk_dir);
  * the device, one thread per outer pair; fewer than 32 traits.
  * cusk_sepselect_pairs is that search alone on host buffers: Ct = rows 0..P of the symmetric correlation matrix
  * ([(P+1) x ld] doubles), pairs = [npairs][2] variable indices (i, j) with at least one end <= P, tmask[v] = bit t
- * set when trait t < P is a neighbour of variable v, thr[l] = qnorm(1 - alpha/2) / sqrt(num_samples - l - 3) for
- * l = 0..P.  cusk_qnorm: the normal quantile in double precision (scipy.stats.norm.ppf, sepselect.py:26-27). */
+ * set when trait t < P is a neighbour of variable v (never v itself, and never j for a pair (v, j): CUSK_E_ARG),
+ * thr[l] = qnorm(1 - alpha/2) / sqrt(num_samples - l - 3) for l = 0..P.  cusk_qnorm: the normal quantile in double precision (scipy.stats.norm.ppf, sepselect.py:26-27). */
 #define CUSK_SS_MAXP 32
 typedef struct cusk_sepselect_result {
     int32_t len;                /* size of the maximal separating set */

@@ -59,7 +59,7 @@ def test_pair_batch_matches_host_compiled_device_routine(ctx, tmp_path):
                            os.path.join(ROOT, "tests", "sepselect_host_core.cpp"), "-o", so])
     host = C.CDLL(so)
     rng = np.random.default_rng(20261104)
-    P, n, npairs = 17, 3000, 40000
+    P, n, npairs = 17, 3000, 54000
     F = rng.standard_normal((n, 40))
     Cm = F @ F.T + 20.0 * np.eye(n)
     d = np.sqrt(np.diag(Cm))
@@ -68,8 +68,12 @@ def test_pair_batch_matches_host_compiled_device_routine(ctx, tmp_path):
     pairs = np.stack([rng.integers(0, n, npairs), rng.integers(0, P, npairs)], axis=1).astype(np.int32)
     swap = rng.random(npairs) < 0.5
     pairs[swap] = pairs[swap][:, ::-1]
-    pairs = pairs[pairs[:, 0] != pairs[:, 1]]
     tmask = rng.integers(0, 1 << P, n, dtype=np.uint32)
+    tmask[:P] &= ~(np.uint32(1) << np.arange(P, dtype=np.uint32))  # no variable is its own neighbour
+    # outer pairs of unshielded triples: j is not adjacent to i (with an end of the pair among the candidates the
+    # Schur complement is singular and rounding noise decides; the C ABI rejects such a pair, tested below)
+    i, j = pairs[:, 0], pairs[:, 1]
+    pairs = pairs[(i != j) & ~((j < P) & ((tmask[i] >> np.minimum(j, 31).astype(np.uint32)) & 1).astype(bool))]
     thr = 3.89 / np.sqrt(20000.0 - np.arange(P + 1) - 3)
     ln, fm, st = ctx.sepselect_pairs(Ct, P, pairs, tmask, thr)
     want = np.zeros((pairs.shape[0], 34), np.int32)
@@ -80,4 +84,10 @@ def test_pair_batch_matches_host_compiled_device_routine(ctx, tmp_path):
     differ = np.flatnonzero((want[:, 0] != ln) | (want[:, 1] != fm) | (want[:, 2:] != st).any(axis=1))
     # log() of the two maths libraries may differ in the last place: allow a decision to flip on a razor-edge comparison
     assert differ.size <= pairs.shape[0] // 2000, (differ.size, differ[:10])
-    assert ln.max() > 3 and (ln == 0).any()
+    assert pairs.shape[0] > 39000 and ln.max() > 3 and (ln == 0).any()
+    # an end of the pair among its own candidates: rejected (CUSK_E_ARG), not searched
+    for bad_pair, var, bit in (((0, P + 5), 0, 0), ((P + 7, 3), P + 7, 3)):
+        bad_mask = tmask.copy()
+        bad_mask[var] |= np.uint32(1 << bit)
+        with pytest.raises(Exception, match="among the trait neighbours"):
+            ctx.sepselect_pairs(Ct, P, np.array([bad_pair], np.int32), bad_mask, thr)
