@@ -175,6 +175,19 @@ int reformat_cuskss_merged(const std::string &cusk_dir);
 int run_sepselect(cusk_ctx *ctx, const std::string &stem, double alpha, long num_samples, const std::string &prior_path,
                   const std::string &out_stem);
 
+// LD blocking (blocking.cpp; src/blocking.cpp:8-136): host only
+struct BlockPartition {
+    std::vector<size_t> first, last;  // inclusive marker ranges, in order
+    size_t largest = 0;
+    int window = 0;  // Hann window that produced them
+};
+std::vector<double> hanning_smoothing(const float *v, size_t nv, int window);
+BlockPartition blocks_for_window(const float *row_sums, size_t m, int window);
+BlockPartition block_chr(const float *row_sums, size_t m, int max_block_size);
+// `mps block` (block.cu; src/cli.cpp:362-411): banded correlations on ctx's device, blocking on the host
+int run_block(cusk_ctx *ctx, const std::string &bfiles, int max_block_size, float device_mem_gb, size_t corr_width,
+              bool verbose);
+
 int mps_main(int argc, char **argv);
 
 }  // namespace cuskhost

@@ -27,6 +27,7 @@ usage: mps <command> [<args>]
 
 commands:
     prep                    Prepare input (PLINK) .bed file for mps
+    block                   Group markers into approximately unlinked blocks (banded correlations + LD blocking)
     cusk                    Run cuda-skeleton on a single block of block diagonal genomic covariance matrix
     cuskss                  Run cuda-skeleton on a block of markers and traits with pre-computed correlations.
     cusk-all                cusk for every block of a .blocks file, scheduled over all visible GPUs
@@ -278,11 +279,35 @@ int dispatch(int argc, char **argv)
         check_cuskss_paths(a, false);
         return run_cuskss_all(a, argv[2], devs, getenv("CUSK_NO_RESUME") == nullptr);
     }
-    if (cmd == "block") {
-        std::cout << "mps block: LD blocking is outside this build's scope (DESIGN.md section 7); use the reference's "
-                     "`mps block` to produce the .blocks file"
-                  << std::endl;
-        return 1;
+    if (cmd == "block") {  // make_blocks, src/cli.cpp:362-411 (6 argv)
+        if (argc != 6 || !strcmp(argv[2], "--help") || !strcmp(argv[2], "-h")) {
+            std::cout << "\nGroup markers into approximately unlinked blocks\n\n"
+                         "usage: mps block <bfiles> <max-block-size> <device-mem-gb> <corr-width>\n\n"
+                         "arguments:\n"
+                         "    bfiles          stem of .bed, .bim, .fam files\n"
+                         "    max-block-size  maximum number of markers per block\n"
+                         "    device-mem-gb   maximum memory available on gpu in GB (0: all that is free)\n"
+                         "    corr-width      max distance at which to compute correlations\n"
+                      << std::endl;
+            return 1;
+        }
+        int max_block_size = 0;
+        float device_mem_gb = 0.f;
+        long corr_width = 0;
+        try {
+            max_block_size = std::stoi(argv[3]);
+            device_mem_gb = std::stof(argv[4]);
+            corr_width = std::stol(argv[5]);
+        } catch (const std::exception &) {
+            fail("mps block: max-block-size, device-mem-gb and corr-width must be numbers");
+        }
+        if (max_block_size < 1 || corr_width < 1) fail("mps block: max-block-size and corr-width must be positive");
+        std::cout << "Checking paths" << std::endl;
+        for (const char *sfx : {".bed", ".bim", ".fam"}) check_path(std::string(argv[2]) + sfx);
+        cusk_ctx *ctx = make_ctx(dev0);
+        const int rc = run_block(ctx, argv[2], max_block_size, device_mem_gb, (size_t)corr_width, true);
+        cusk_ctx_destroy(ctx);
+        return finish(rc);
     }
     std::cout << MPS_USAGE << std::endl;
     return EXIT_SUCCESS;
@@ -323,6 +348,49 @@ extern "C" int cusk_prep_bed(cusk_ctx *ctx, const char *bfiles)
         cusk_set_error("%s", e.msg.c_str());
         return CUSK_E_ARG;
     }
+}
+
+// make_blocks (src/cli.cpp:362-411) with a status return, and its host-only pieces (src/blocking.cpp)
+extern "C" int cusk_make_blocks(cusk_ctx *ctx, const char *bfiles, int max_block_size, float device_mem_gb,
+                                size_t corr_width)
+{
+    if (!ctx || !bfiles || max_block_size < 1 || corr_width < 1) {
+        cusk_set_error("cusk_make_blocks: invalid argument");
+        return CUSK_E_ARG;
+    }
+    try {
+        return cuskhost::run_block(ctx, bfiles, max_block_size, device_mem_gb, corr_width, false);
+    } catch (const cuskhost::HostError &e) {
+        cusk_set_error("%s", e.msg.c_str());
+        return CUSK_E_ARG;
+    }
+}
+
+extern "C" int cusk_hanning_smoothing(const float *v, size_t nv, int window_size, double *out)
+{
+    if (!v || !out || window_size < 1) {
+        cusk_set_error("cusk_hanning_smoothing: invalid argument");
+        return CUSK_E_ARG;
+    }
+    const std::vector<double> s = cuskhost::hanning_smoothing(v, nv, window_size);
+    std::copy(s.begin(), s.end(), out);
+    return CUSK_OK;
+}
+
+extern "C" int64_t cusk_block_chr(const float *row_sums, size_t m, int max_block_size, int64_t *first, int64_t *last,
+                                  int *window)
+{
+    if (!row_sums || !first || !last || m == 0 || max_block_size < 1) {
+        cusk_set_error("cusk_block_chr: invalid argument");
+        return CUSK_E_ARG;
+    }
+    const cuskhost::BlockPartition bp = cuskhost::block_chr(row_sums, m, max_block_size);
+    for (size_t i = 0; i < bp.first.size(); i++) {
+        first[i] = (int64_t)bp.first[i];
+        last[i] = (int64_t)bp.last[i];
+    }
+    if (window) *window = bp.window;
+    return (int64_t)bp.first.size();
 }
 
 // merge_block_outputs(blockfile, outdir).write_mm(out_base) and reformat_cuskss_merged_output(dir).write_mm(...)

@@ -550,4 +550,70 @@ int run_prep(cusk_ctx *ctx, const std::string &bfiles, bool verbose)
     return CUSK_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// `mps block <bfiles> <max-block-size> <device-mem-gb> <corr-width>` (make_blocks, src/cli.cpp:362-411): per
+// chromosome of the .bim, banded correlations + row |r| sums on the device (cusk_mcorrk_banded; only the m row
+// sums come back), Hann smoothing / minima / window bisection on the host (blocking.cpp), blocks APPENDED to
+// <bfiles>_m<max-block-size>.blocks (write_marker_blocks_to_file, src/io.cpp:266-277).
+// ---------------------------------------------------------------------------------------------------------
+int run_block(cusk_ctx *ctx, const std::string &bfiles, int max_block_size, float device_mem_gb, size_t corr_width,
+              bool verbose)
+{
+    for (const char *sfx : {".bed", ".bim", ".fam"}) check_path(bfiles + sfx);
+    if (!has_valid_bed_prefix(bfiles + ".bed")) fail("Invalid prefix bytes in bed");
+    const size_t n = count_lines(bfiles + ".fam");
+    BimInfo bim(bfiles + ".bim");
+    const size_t col_bytes = (n + 3) / 4;
+    const std::string out_path = bfiles + "_m" + std::to_string(max_block_size) + ".blocks";
+    FILE *bed = fopen((bfiles + ".bed").c_str(), "rb");
+    if (!bed) fail("file or directory not found: " + bfiles + ".bed");
+    for (size_t c = 0; c < bim.chr_ids.size(); c++) {
+        const std::string &cid = bim.chr_ids[c];
+        const size_t m = bim.num_on_chr[c];
+        if (verbose)
+            std::cout << "[Chr " << cid << "]: Loading bed data for " << m << " markers." << std::endl;
+        Pinned stage;
+        unsigned char *h = (unsigned char *)stage.get(m * col_bytes);
+        if (!h) {
+            fclose(bed);
+            fail("out of host memory for chromosome " + cid);
+        }
+        if (fseek(bed, (long)(3 + bim.chr_start[c] * col_bytes), SEEK_SET) != 0 ||
+            fread(h, 1, m * col_bytes, bed) != m * col_bytes) {
+            fclose(bed);
+            fail("short read of " + bfiles + ".bed (chromosome " + cid + ")");
+        }
+        if (verbose) std::cout << "[Chr " << cid << "]: Computing correlations and row sums." << std::endl;
+        std::vector<float> sums(m, 0.f);
+        cusk_band_stats bs;
+        const int rc = cusk_mcorrk_banded(ctx, h, m, n, corr_width, device_mem_gb, nullptr, sums.data(), &bs);
+        if (rc != CUSK_OK) {
+            fclose(bed);
+            if (rc == CUSK_E_ARG) fail(cusk_last_error());  // exit(1) like the reference's batch-size check
+            return rc;
+        }
+        if (verbose) std::cout << "[Chr " << cid << "]: Making blocks." << std::endl;
+        const BlockPartition bp = block_chr(sums.data(), m, max_block_size);
+        if (verbose) {
+            std::cout << "[Chr " << cid << "]: Partitioned into " << bp.first.size() << " blocks." << std::endl;
+            std::cout << "[Chr " << cid << "]: Writing blocks to output file." << std::endl;
+            printf("{\"event\": \"block_chr\", \"chr\": \"%s\", \"markers\": %zu, \"pairs\": %lld, \"chunks\": %d, "
+                   "\"h2d_ms\": %.3f, \"kernel_ms\": %.3f, \"window\": %d, \"blocks\": %zu, \"largest\": %zu}\n",
+                   cid.c_str(), m, (long long)bs.pairs, bs.chunks, bs.h2d_ms, bs.kernel_ms, bp.window, bp.first.size(),
+                   bp.largest);
+            fflush(stdout);
+        }
+        FILE *out = fopen(out_path.c_str(), "a");
+        if (!out) {
+            fclose(bed);
+            fail("cannot write " + out_path);
+        }
+        for (size_t b = 0; b < bp.first.size(); b++) fprintf(out, "%s\t%zu\t%zu\n", cid.c_str(), bp.first[b], bp.last[b]);
+        fclose(out);
+    }
+    fclose(bed);
+    if (verbose) std::cout << "Done." << std::endl;
+    return CUSK_OK;
+}
+
 }  // namespace cuskhost

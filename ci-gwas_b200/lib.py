@@ -61,6 +61,14 @@ class CorrStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class BandStats(C.Structure):
+    _fields_ = [(k, C.c_float) for k in ("h2d_ms", "kernel_ms", "d2h_ms", "total_ms")] + [
+        ("chunks", C.c_int32), ("pairs", C.c_int64), ("bed_bytes", C.c_int64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
 SEPSET_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("level", "<i4"), ("pmax", "<f4"), ("s", "<i4", (ML,))])
 
 _LIB = None
@@ -123,6 +131,12 @@ def load_library():
                                           c_float_p, c_float_p, c_float_p, C.POINTER(CorrStats)]
     lib.cusk_corr_block_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                         C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(CorrStats)]
+    lib.cusk_mcorrk_banded.argtypes = [C.c_void_p, c_ubyte_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float, c_float_p,
+                                       c_float_p, C.POINTER(BandStats)]
+    lib.cusk_hanning_smoothing.argtypes = [c_float_p, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
+    lib.cusk_block_chr.restype = C.c_int64
+    lib.cusk_block_chr.argtypes = [c_float_p, C.c_size_t, C.c_int, c_i64_p, c_i64_p, c_int_p]
+    lib.cusk_make_blocks.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_float, C.c_size_t]
     lib.cusk_comm_unique_id.argtypes = [C.c_char_p]
     lib.cusk_comm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]
     lib.cusk_comm_destroy.argtypes = [C.c_void_p]
@@ -181,6 +195,30 @@ def merge_block_outputs(blockfile, outdir, out_base=None):
         out_base = os.path.join(outdir, "merged_blocks")
     if lib.cusk_merge_block_outputs(os.fsencode(blockfile), os.fsencode(outdir), os.fsencode(out_base)) != 0:
         raise CuskError(lib.cusk_last_error().decode())
+
+
+def hanning_smoothing(v, window):
+    """hanning_smoothing (src/blocking.cpp:13-36): float64 [len(v)]; host only"""
+    lib = load_library()
+    v = np.ascontiguousarray(v, np.float32)
+    out = np.zeros(len(v), np.float64)
+    if lib.cusk_hanning_smoothing(_p(v, c_float_p), len(v), int(window), out.ctypes.data_as(C.POINTER(C.c_double))) != 0:
+        raise CuskError(lib.cusk_last_error().decode())
+    return out
+
+
+def block_chr(row_sums, max_block_size):
+    """block_chr (src/blocking.cpp:97-136) -> (blocks int64 [nb, 2] = (first, last) inclusive, Hann window used); host only"""
+    lib = load_library()
+    v = np.ascontiguousarray(row_sums, np.float32)
+    first = np.zeros(len(v), np.int64)
+    last = np.zeros(len(v), np.int64)
+    win = C.c_int(0)
+    nb = lib.cusk_block_chr(_p(v, c_float_p), len(v), int(max_block_size), _p(first, c_i64_p), _p(last, c_i64_p),
+                            C.byref(win))
+    if nb < 0:
+        raise CuskError(lib.cusk_last_error().decode())
+    return np.stack([first[:nb], last[:nb]], 1), win.value
 
 
 def reformat_cuskss_merged(cusk_dir):
@@ -323,6 +361,22 @@ class Context:
         self._check(self.lib.cusk_bed_marker_stats(self.h, _p(bed, c_ubyte_p), m, n, _p(means, c_float_p),
                                                    _p(stds, c_float_p), _p(modes, c_int_p), _p(counts, c_i64_p)))
         return means, stds, modes, counts
+
+    def mcorrk_banded(self, bed, m, n, corr_width, device_mem_gb=0.0, want_corrs=True, want_sums=True):
+        """cal_mcorrk_banded + marker_corr_banded_mat_row_abs_sums (corr_host.cu:64-128)
+        -> dict(corrs [m, corr_width] | None, row_abs_sums [m] | None, stats)"""
+        bed = np.ascontiguousarray(bed, np.uint8).reshape(-1)
+        corrs = np.zeros((m, corr_width), np.float32) if want_corrs else None
+        sums = np.zeros(m, np.float32) if want_sums else None
+        st = BandStats()
+        self._check(self.lib.cusk_mcorrk_banded(self.h, _p(bed, c_ubyte_p), m, n, corr_width, float(device_mem_gb),
+                                                _p(corrs, c_float_p), _p(sums, c_float_p), C.byref(st)))
+        return {"corrs": corrs, "row_abs_sums": sums, "stats": st.as_dict()}
+
+    def make_blocks(self, bfiles, max_block_size, corr_width, device_mem_gb=0.0):
+        """make_blocks (cli.cpp:362-411): appends to <bfiles>_m<max_block_size>.blocks"""
+        self._check(self.lib.cusk_make_blocks(self.h, os.fsencode(bfiles), int(max_block_size), float(device_mem_gb),
+                                              int(corr_width)))
 
     def corr_block(self, bed, phen, m, n, p, mean, std, mode=0, want_mxm=True, want_tables=False):
         """cu_corr_pearson_npn (corr_host.cu:1094) -> dict(mxm, mxp, pxp[, tables], stats)"""

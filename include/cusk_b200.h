@@ -147,6 +147,32 @@ int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, const float *
                         size_t n, size_t p, const float *d_mean, const float *d_std, int mode,
                         float *d_Csq, cusk_corr_stats *stats);
 
+/* ---- LD blocking (`mps block`) ----------------------------------------------------------
+ * cusk_mcorrk_banded replaces cal_mcorrk_banded (src/corr_host.cu:64-110; launch loop
+ * cu_marker_corr_pearson_npn_batched_sparse, :1199-1319) and marker_corr_banded_mat_row_abs_sums (:112-128):
+ * corrs[row * corr_width + k] = sin(pi/2 tau_b) of markers (row, row + 1 + k), 0 where row + 1 + k >= m;
+ * row_abs_sums[row] = sum_k |corrs[row][k]| accumulated in float, left to right.  Either output may be NULL.
+ * bed: the chromosome's packed columns (read_chr_from_bed, src/io.cpp:251).  device_mem_gb > 0 bounds the device
+ * memory used (the reference's <device-mem-gb>; 0 = what is free): the chromosome is then processed in chunks of
+ * rows.  Needs 0 < corr_width < m (the reference exits or reads out of bounds otherwise). */
+typedef struct cusk_band_stats {
+    float h2d_ms, kernel_ms, d2h_ms, total_ms; /* summed over chunks (CUDA events) */
+    int32_t chunks;
+    int64_t pairs;     /* marker pairs inside the band */
+    int64_t bed_bytes; /* packed genotype bytes copied to the device (chunk overlaps included) */
+} cusk_band_stats;
+int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_t m, size_t n, size_t corr_width,
+                       float device_mem_gb, float *corrs, float *row_abs_sums, cusk_band_stats *stats);
+/* host only.  hanning_smoothing (src/blocking.cpp:13-36): out[nv] doubles.  block_chr (src/blocking.cpp:97-136):
+ * blocks [first[i], last[i]] (0-based, inclusive) of one chromosome from its row sums; first/last need room for m
+ * entries; returns the number of blocks (< 0 on error), *window (may be NULL) the Hann window finally used. */
+int cusk_hanning_smoothing(const float *v, size_t nv, int window_size, double *out);
+int64_t cusk_block_chr(const float *row_sums, size_t m, int max_block_size, int64_t *first, int64_t *last,
+                       int *window);
+/* make_blocks (src/cli.cpp:362-411) = `mps block <bfiles> <max-block-size> <device-mem-gb> <corr-width>`:
+ * appends every chromosome's blocks to <bfiles>_m<max-block-size>.blocks ("chr\tfirst\tlast" lines). */
+int cusk_make_blocks(cusk_ctx *ctx, const char *bfiles, int max_block_size, float device_mem_gb, size_t corr_width);
+
 /* ---- multi-GPU: one skeleton sharded over several GPUs (cuskss --marker-indices) ------
  * The level-l work items are dealt round-robin to the ranks; after each level the ranks exchange what
  * they removed (NCCL all-gather of one removed-flag byte per CSR slot for the summary-statistic engine,
@@ -222,6 +248,10 @@ void cu_corr_pearson_npn(const unsigned char *marker_vals, const float *phen_val
                          const size_t num_markers, const size_t num_individuals, const size_t num_phen,
                          const float *marker_mean, const float *marker_std, float *marker_corrs,
                          float *marker_phen_corrs, float *phen_corrs);
+/* include/mps/corr_host.h: cu_marker_corr_pearson_npn_batched_sparse (src/corr_host.cu:1199); batch_size is ignored */
+void cu_marker_corr_pearson_npn_batched_sparse(const unsigned char *marker_vals, const size_t num_markers,
+                                               const size_t num_individuals, const size_t corr_width,
+                                               const size_t batch_size, float *corrs);
 /* include/mps/cuPC-S.h:192-194 */
 void Skeleton(float *C, int *P, int *G, float *Th, int *l, const int *maxlevel, float *pMax,
               int *SepSet);

@@ -7,7 +7,9 @@
 // Parity status: PINNED against the reference's own golden vectors (tests/golden/*, made
 // by tests/golden/make_golden.py from /root/reference/cusk/include/test_data and
 // cusk/tests/*.cpp): C_N10 -> A_N10 for both engines, threshold 0.0081045, the 10x3x2 and
-// 100x7x5 BED correlation sets, small.bed means/stds, parent-set BFS sets.
+// 100x7x5 BED correlation sets, small.bed means/stds, parent-set BFS sets; and
+// (tests/golden/make_block_golden.py) the banded 100x7 correlations, the Hann smoothing vector and the 17
+// blocks of block_chr(TEST_V, 500).
 //
 // All file:line citations are relative to /root/reference/cusk/.  The reference computes in
 // float32 with --use_fast_math on a GPU (src/CMakeLists.txt:27-35); this restatement follows
@@ -900,6 +902,124 @@ void orc_corr_npn(const unsigned char *bed, const float *phen, size_t m, size_t 
                 pxp[lin] = s / cnt;
             }
     }
+}
+
+// ---- `mps block` (src/cli.cpp:362-411): banded marker correlations, row sums, LD blocking ----
+
+// cal_mcorrk_banded (src/corr_host.cu:64-110) through cu_marker_corr_pearson_npn_batched_sparse
+// (:1199-1319) and bed_marker_corr_pearson_npn_sparse_scan (src/corr_kernels.cu:920-1010):
+// corrs[row * W + k] = npn correlation of markers (row, row + 1 + k) for row + 1 + k < m, else 0.
+// (The device-memory batching of the reference does not change any value.)  Table exact, formula
+// in FP64, stored as float like the reference's result array.
+void orc_mcorrk_banded(const unsigned char *bed, size_t m, size_t n, size_t W, float *corrs)
+{
+#pragma omp parallel for schedule(dynamic, 4)
+    for (long long row = 0; row < (long long)m; row++)
+        for (size_t k = 0; k < W; k++) {
+            const size_t col = (size_t)row + 1 + k;
+            float r = 0.0f;
+            if (col < m) {
+                long long t[9];
+                orc_bed_pair_table(bed, n, (size_t)row, col, t);
+                r = (float)orc_npn_from_table(t);
+            }
+            corrs[(size_t)row * W + k] = r;
+        }
+}
+
+// marker_corr_banded_mat_row_abs_sums (src/corr_host.cu:112-128): float accumulator, columns in order.
+void orc_banded_row_abs_sums(const float *corrs, size_t m, size_t W, float *sums)
+{
+    for (size_t row = 0; row < m; row++) {
+        float s = 0.0f;
+        for (size_t col = 0; col < W; col++) s += std::fabs(corrs[row * W + col]);
+        sums[row] = s;
+    }
+}
+
+// hann (src/blocking.cpp:8-11): the cosine is taken in single precision (cosf of the double argument
+// rounded to float); the rest is double.  window_size 1 gives 0/0 -> NaN weights, as in the reference.
+static double orc_hann(int i, int window_size)
+{
+    return 0.5 - 0.5 * cosf(2.0 * M_PI * (double)i / ((double)window_size - 1.0));
+}
+
+// hanning_smoothing (src/blocking.cpp:13-36): res[c] = sum_i w[i] v[c - margin + i] for margin <= c < nv - margin,
+// 0 outside.  (The reference compares `int center` against the unsigned nv - margin; every window block_chr
+// tries has margin <= nv / 4, where the two readings agree.)
+void orc_hanning_smoothing(const float *v, size_t nv, int window_size, double *res)
+{
+    std::vector<double> w(window_size);
+    for (int i = 0; i < window_size; i++) w[i] = orc_hann(i, window_size);
+    const long long margin = window_size / 2;
+    for (size_t i = 0; i < nv; i++) res[i] = 0.0;
+    for (long long c = margin; c < (long long)nv - margin; c++)
+        for (int i = 0; i < window_size; i++) res[c] += w[i] * (double)v[c - margin + i];
+}
+
+// local_minima (src/blocking.cpp:38-55): i is a minimum when the running maximum since the last
+// minimum exceeds v[i] and v[i] < v[i+1]; the running maximum restarts at 0 after each minimum.
+static std::vector<size_t> orc_local_minima(const std::vector<double> &v)
+{
+    std::vector<size_t> res;
+    double left = 0.0;
+    for (size_t i = 1; i + 1 < v.size(); i++) {
+        if (left > v[i] && v[i] < v[i + 1]) {
+            res.push_back(i);
+            left = 0.0;
+        } else if (v[i] > left)
+            left = v[i];
+    }
+    return res;
+}
+
+// block_chr_with_window_size (src/blocking.cpp:87-95) + blocks_from_minima (:57-70): blocks
+// [prev, minimum], next block starts after the minimum; the last block ends at nv - 1.
+static long long orc_blocks_with_window(const float *v, size_t nv, int window_size, std::vector<long long> *first,
+                                        std::vector<long long> *last)
+{
+    std::vector<double> smooth(nv);
+    orc_hanning_smoothing(v, nv, window_size, smooth.data());
+    const std::vector<size_t> minima = orc_local_minima(smooth);
+    first->clear();
+    last->clear();
+    long long prev = 0, largest = 0;
+    for (size_t pos : minima) {
+        first->push_back(prev);
+        last->push_back((long long)pos);
+        prev = (long long)pos + 1;
+    }
+    first->push_back(prev);
+    last->push_back((long long)nv - 1);
+    for (size_t i = 0; i < first->size(); i++) largest = std::max(largest, (*last)[i] - (*first)[i] + 1);
+    return largest;  // largest_block_size (:72-85)
+}
+
+// block_chr (src/blocking.cpp:97-136): bisection on the (odd) window size between 3 and nv until the largest
+// block is within MAX_BLOCK_SIZE_TOL = 100 below max_block_size, or the window stops changing.
+// first/last need room for nv entries; returns the number of blocks, *final_window the window used.
+long long orc_block_chr(const float *v, size_t nv, int max_block_size, long long *first, long long *last,
+                        int *final_window)
+{
+    auto make_odd = [](int x) { return x % 2 == 0 ? x - 1 : x; };
+    int too_large = (int)nv, too_small = 3;
+    int window = make_odd((too_large + too_small) / 2);
+    std::vector<long long> f, l;
+    int lbs = (int)orc_blocks_with_window(v, nv, window, &f, &l);
+    while (std::abs(lbs - max_block_size) > 100 || lbs > max_block_size) {
+        if (lbs > max_block_size) too_large = std::min(too_large, window);
+        else too_small = std::max(too_small, window);
+        const int next = make_odd((too_large + too_small) / 2);
+        if (next == window) break;
+        window = next;
+        lbs = (int)orc_blocks_with_window(v, nv, window, &f, &l);
+    }
+    for (size_t i = 0; i < f.size(); i++) {
+        first[i] = f[i];
+        last[i] = l[i];
+    }
+    if (final_window) *final_window = window;
+    return (long long)f.size();
 }
 
 // src/parent_set.cpp:8-53 (subset_variables): all traits + markers within max_depth hops of

@@ -125,6 +125,38 @@ class Oracle:
                               _p(mxp, c_double_p), _p(pxp, c_double_p))
         return mxm, mxp, pxp
 
+    def mcorrk_banded(self, bed, m, n, corr_width):
+        """cal_mcorrk_banded: [m, corr_width] float32, entry (row, k) = npn corr of (row, row + 1 + k)"""
+        bed = np.ascontiguousarray(bed, np.uint8)
+        out = np.zeros((m, corr_width), np.float32)
+        self.lib.orc_mcorrk_banded(_p(bed, c_ubyte_p), C.c_size_t(m), C.c_size_t(n), C.c_size_t(corr_width),
+                                   _p(out, c_float_p))
+        return out
+
+    def banded_row_abs_sums(self, corrs):
+        corrs = np.ascontiguousarray(corrs, np.float32)
+        m, w = corrs.shape
+        out = np.zeros(m, np.float32)
+        self.lib.orc_banded_row_abs_sums(_p(corrs, c_float_p), C.c_size_t(m), C.c_size_t(w), _p(out, c_float_p))
+        return out
+
+    def hanning_smoothing(self, v, window):
+        v = np.ascontiguousarray(v, np.float32)
+        out = np.zeros(len(v), np.float64)
+        self.lib.orc_hanning_smoothing(_p(v, c_float_p), C.c_size_t(len(v)), int(window), _p(out, c_double_p))
+        return out
+
+    def block_chr(self, v, max_block_size):
+        """-> (blocks [nb, 2] int64 (first, last), final window size)"""
+        v = np.ascontiguousarray(v, np.float32)
+        first = np.zeros(len(v), np.int64)
+        last = np.zeros(len(v), np.int64)
+        win = C.c_int(0)
+        self.lib.orc_block_chr.restype = C.c_longlong
+        nb = self.lib.orc_block_chr(_p(v, c_float_p), C.c_size_t(len(v)), int(max_block_size), _p(first, c_ll_p),
+                                    _p(last, c_ll_p), C.byref(win))
+        return np.stack([first[:nb], last[:nb]], 1), win.value
+
     def subset_variables(self, G, num_var, num_markers, max_depth):
         G = np.ascontiguousarray(G, np.int32)
         sel = np.zeros(num_var, np.int32)
