@@ -8,9 +8,11 @@ from .lib import (  # noqa: F401
     CuskError,
     Context,
     Stats,
+    block_chr,
     build_library,
     comm_unique_id,
     local_group,
+    hanning_smoothing,
     hetcor_threshold,
     library_path,
     load_library,
