@@ -1,6 +1,6 @@
 #!/usr/bin/env python
-"""Command-line front end of the B200 skeleton path: the `prep-bed`, `cusk` and `cuskss` sub-commands of the
-reference's `ci-gwas.py` (ci-gwas.py:55-62, :95-150, :152-252; the het and merged modes are `cuskss` with
+"""Command-line front end of the B200 skeleton path: the `prep-bed`, `block`, `cusk` and `cuskss` sub-commands of the
+reference's `ci-gwas.py` (ci-gwas.py:55-62, :64-93, :95-150, :152-252; the het and merged modes are `cuskss` with
 `--mxp-se/--pxp-se` and `--marker-indices`), `merge-block-outputs` (ci-gwas.py:254-270, :459-464), `sepselect` and
 `orient-v-structs` (ci-gwas.py:302-358, :467-476), with the same
 arguments, defaults and input checks (ci-gwas.py:386-457), driving `ci-gwas_b200/mps` instead of
@@ -9,7 +9,7 @@ native `mps merge` / `mps reformat-merged` instead of cusk_postprocessing/merge_
 
 Additions: `cusk-all` / `cuskss-all` run every block of a block file on all GPUs of the box (LPT schedule, resume
 by existing outputs); `--gpus` picks the devices; `cuskss --shard-gpus N` deals the level-l tests of ONE merged
-skeleton to N GPUs (NCCL exchange per level).  Everything else of ci-gwas.py (block, srfci, mvivw, ...)
+skeleton to N GPUs (NCCL exchange per level).  Everything else of ci-gwas.py (srfci, mvivw, ...)
 is outside this path: run it from the reference on the files written here.
 """
 import argparse
@@ -56,6 +56,11 @@ def run(argv, args):
 
 def prep_bed(args):
     run(["prep", args.bfiles], args)
+
+
+def block(args):
+    # ci-gwas.py:390-401
+    run(["block", args.bfiles, args.max_block_size, args.device_mem_gb, args.corr_width], args)
 
 
 def cusk_argv(args):
@@ -176,6 +181,16 @@ def build_parser():
     p.add_argument("bfiles", type=str, help="filestem of .bed, .bim, .fam fileset")
     add_device_args(p)
     p.set_defaults(func=prep_bed)
+    p = sub.add_parser("block", help="Tile whole-genome LD matrix into block diagonal matrix")  # ci-gwas.py:64-93
+    p.add_argument("bfiles", type=str, help="filestem of .bed, .bim, .fam fileset")
+    p.add_argument("max_block_size", metavar="max-block-size", type=Checked(int, "max-block-size", 2),
+                   help="maximum number of markers per block")
+    p.add_argument("device_mem_gb", metavar="device-mem-gb", type=Checked(int, "device-mem-gb", 0),
+                   help="maximum memory available on GPU in GB (0: all that is free)")
+    p.add_argument("corr_width", metavar="corr-width", type=Checked(int, "corr-width", 2),
+                   help="width of banded-correlation matrix")
+    add_device_args(p)
+    p.set_defaults(func=block)
     p = sub.add_parser("cusk", help="Skeleton of one genomic block from individual-level data")
     add_cusk_args(p, True)
     p.set_defaults(func=cusk)

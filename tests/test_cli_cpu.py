@@ -46,6 +46,18 @@ def test_prep_bed_and_cusk(fake_mps):
     assert cli(["cusk", "0", "b", "g", "p", "0.1", "15"], mps).returncode == 2  # max level above 14
 
 
+def test_block(fake_mps):
+    mps, rec = fake_mps
+    # ci-gwas.py:64-93, :390-401: bfiles max-block-size device-mem-gb corr-width, all positional
+    assert cli(["block", "/data/geno", "11000", "10", "2000", "--gpus", "2"], mps).returncode == 0
+    r = json.load(open(rec))
+    assert r["argv"] == ["block", "/data/geno", "11000", "10", "2000"] and r["devices"] == "2"
+    assert cli(["block", "/data/geno", "1", "10", "2000"], mps).returncode == 2   # max-block-size >= 2
+    assert cli(["block", "/data/geno", "100", "10", "1"], mps).returncode == 2    # corr-width >= 2
+    assert cli(["block", "/data/geno", "100", "1.5", "20"], mps).returncode == 2  # device-mem-gb is an int
+    assert cli(["block", "/data/geno", "100"], mps).returncode == 2
+
+
 def test_cuskss_modes_and_checks(fake_mps):
     mps, rec = fake_mps
     base = ["cuskss", "--pxp", "pxp.txt", "--alpha", "0.0001", "--num-samples", "458000"]
