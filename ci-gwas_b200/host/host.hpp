@@ -187,6 +187,9 @@ BlockPartition block_chr(const float *row_sums, size_t m, int max_block_size);
 // `mps block` (block.cu; src/cli.cpp:362-411): banded correlations on ctx's device, blocking on the host
 int run_block(cusk_ctx *ctx, const std::string &bfiles, int max_block_size, float device_mem_gb, size_t corr_width,
               bool verbose);
+// the chromosomes of the file set spread over several devices (largest first, no exchange); same output file
+int run_block_all(const std::string &bfiles, int max_block_size, float device_mem_gb, size_t corr_width,
+                  const std::vector<int> &devices);
 
 int mps_main(int argc, char **argv);
 

@@ -304,6 +304,8 @@ int dispatch(int argc, char **argv)
         if (max_block_size < 1 || corr_width < 1) fail("mps block: max-block-size and corr-width must be positive");
         std::cout << "Checking paths" << std::endl;
         for (const char *sfx : {".bed", ".bim", ".fam"}) check_path(std::string(argv[2]) + sfx);
+        if (devs.size() > 1)  // chromosomes are independent: one worker per device (CUSK_DEVICES selects them)
+            return finish(run_block_all(argv[2], max_block_size, device_mem_gb, (size_t)corr_width, devs));
         cusk_ctx *ctx = make_ctx(dev0);
         const int rc = run_block(ctx, argv[2], max_block_size, device_mem_gb, (size_t)corr_width, true);
         cusk_ctx_destroy(ctx);

@@ -5,10 +5,13 @@
 // adjacency travels as a bitmap; separating sets come back sparse; the marker x trait screen is
 // computed once instead of twice.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <iostream>
+#include <mutex>
+#include <thread>
 #include <unordered_map>
 
 #include "../csrc/engine.h"
@@ -556,6 +559,59 @@ int run_prep(cusk_ctx *ctx, const std::string &bfiles, bool verbose)
 // sums come back), Hann smoothing / minima / window bisection on the host (blocking.cpp), blocks APPENDED to
 // <bfiles>_m<max-block-size>.blocks (write_marker_blocks_to_file, src/io.cpp:266-277).
 // ---------------------------------------------------------------------------------------------------------
+// One chromosome: its columns from the open .bed, banded correlations + row sums on ctx's device, blocks on the host.
+int block_chromosome(cusk_ctx *ctx, FILE *bed, const std::string &bfiles, const BimInfo &bim, size_t c, size_t n,
+                     int max_block_size, float device_mem_gb, size_t corr_width, bool verbose, BlockPartition *out,
+                     cusk_band_stats *bs)
+{
+    const std::string &cid = bim.chr_ids[c];
+    const size_t m = bim.num_on_chr[c], col_bytes = (n + 3) / 4;
+    if (verbose) std::cout << "[Chr " << cid << "]: Loading bed data for " << m << " markers." << std::endl;
+    Pinned stage;
+    unsigned char *h = (unsigned char *)stage.get(m * col_bytes);
+    if (!h) fail("out of host memory for chromosome " + cid);
+    if (fseeko(bed, (off_t)(3 + bim.chr_start[c] * col_bytes), SEEK_SET) != 0 ||
+        fread(h, 1, m * col_bytes, bed) != m * col_bytes)
+        fail("short read of " + bfiles + ".bed (chromosome " + cid + ")");
+    if (verbose) std::cout << "[Chr " << cid << "]: Computing correlations and row sums." << std::endl;
+    std::vector<float> sums(m, 0.f);
+    const int rc = cusk_mcorrk_banded(ctx, h, m, n, corr_width, device_mem_gb, nullptr, sums.data(), bs);
+    if (rc == CUSK_E_ARG) fail(cusk_last_error());  // exit(1) like the reference's batch-size check
+    if (rc != CUSK_OK) return rc;
+    if (verbose) std::cout << "[Chr " << cid << "]: Making blocks." << std::endl;
+    *out = block_chr(sums.data(), m, max_block_size);
+    return CUSK_OK;
+}
+
+namespace {
+
+void append_blocks(const std::string &out_path, const std::string &cid, const BlockPartition &bp)
+{
+    FILE *out = fopen(out_path.c_str(), "a");
+    if (!out) fail("cannot write " + out_path);
+    for (size_t b = 0; b < bp.first.size(); b++) fprintf(out, "%s\t%zu\t%zu\n", cid.c_str(), bp.first[b], bp.last[b]);
+    fclose(out);
+}
+
+void log_chromosome(const std::string &cid, size_t m, int device, const cusk_band_stats &bs, const BlockPartition &bp)
+{
+    printf("{\"event\": \"block_chr\", \"chr\": \"%s\", \"device\": %d, \"markers\": %zu, \"pairs\": %lld, "
+           "\"chunks\": %d, \"h2d_ms\": %.3f, \"kernel_ms\": %.3f, \"window\": %d, \"blocks\": %zu, \"largest\": %zu}\n",
+           cid.c_str(), device, m, (long long)bs.pairs, bs.chunks, bs.h2d_ms, bs.kernel_ms, bp.window, bp.first.size(),
+           bp.largest);
+    fflush(stdout);
+}
+
+struct FileCloser {
+    FILE *f;
+    ~FileCloser()
+    {
+        if (f) fclose(f);
+    }
+};
+
+}  // namespace
+
 int run_block(cusk_ctx *ctx, const std::string &bfiles, int max_block_size, float device_mem_gb, size_t corr_width,
               bool verbose)
 {
@@ -563,56 +619,94 @@ int run_block(cusk_ctx *ctx, const std::string &bfiles, int max_block_size, floa
     if (!has_valid_bed_prefix(bfiles + ".bed")) fail("Invalid prefix bytes in bed");
     const size_t n = count_lines(bfiles + ".fam");
     BimInfo bim(bfiles + ".bim");
-    const size_t col_bytes = (n + 3) / 4;
     const std::string out_path = bfiles + "_m" + std::to_string(max_block_size) + ".blocks";
-    FILE *bed = fopen((bfiles + ".bed").c_str(), "rb");
-    if (!bed) fail("file or directory not found: " + bfiles + ".bed");
+    FileCloser bed{fopen((bfiles + ".bed").c_str(), "rb")};
+    if (!bed.f) fail("file or directory not found: " + bfiles + ".bed");
     for (size_t c = 0; c < bim.chr_ids.size(); c++) {
         const std::string &cid = bim.chr_ids[c];
-        const size_t m = bim.num_on_chr[c];
-        if (verbose)
-            std::cout << "[Chr " << cid << "]: Loading bed data for " << m << " markers." << std::endl;
-        Pinned stage;
-        unsigned char *h = (unsigned char *)stage.get(m * col_bytes);
-        if (!h) {
-            fclose(bed);
-            fail("out of host memory for chromosome " + cid);
-        }
-        if (fseek(bed, (long)(3 + bim.chr_start[c] * col_bytes), SEEK_SET) != 0 ||
-            fread(h, 1, m * col_bytes, bed) != m * col_bytes) {
-            fclose(bed);
-            fail("short read of " + bfiles + ".bed (chromosome " + cid + ")");
-        }
-        if (verbose) std::cout << "[Chr " << cid << "]: Computing correlations and row sums." << std::endl;
-        std::vector<float> sums(m, 0.f);
+        BlockPartition bp;
         cusk_band_stats bs;
-        const int rc = cusk_mcorrk_banded(ctx, h, m, n, corr_width, device_mem_gb, nullptr, sums.data(), &bs);
-        if (rc != CUSK_OK) {
-            fclose(bed);
-            if (rc == CUSK_E_ARG) fail(cusk_last_error());  // exit(1) like the reference's batch-size check
-            return rc;
-        }
-        if (verbose) std::cout << "[Chr " << cid << "]: Making blocks." << std::endl;
-        const BlockPartition bp = block_chr(sums.data(), m, max_block_size);
+        const int rc = block_chromosome(ctx, bed.f, bfiles, bim, c, n, max_block_size, device_mem_gb, corr_width, verbose,
+                                        &bp, &bs);
+        if (rc != CUSK_OK) return rc;
         if (verbose) {
             std::cout << "[Chr " << cid << "]: Partitioned into " << bp.first.size() << " blocks." << std::endl;
             std::cout << "[Chr " << cid << "]: Writing blocks to output file." << std::endl;
-            printf("{\"event\": \"block_chr\", \"chr\": \"%s\", \"markers\": %zu, \"pairs\": %lld, \"chunks\": %d, "
-                   "\"h2d_ms\": %.3f, \"kernel_ms\": %.3f, \"window\": %d, \"blocks\": %zu, \"largest\": %zu}\n",
-                   cid.c_str(), m, (long long)bs.pairs, bs.chunks, bs.h2d_ms, bs.kernel_ms, bp.window, bp.first.size(),
-                   bp.largest);
-            fflush(stdout);
+            log_chromosome(cid, bim.num_on_chr[c], ctx->device, bs, bp);
         }
-        FILE *out = fopen(out_path.c_str(), "a");
-        if (!out) {
-            fclose(bed);
-            fail("cannot write " + out_path);
-        }
-        for (size_t b = 0; b < bp.first.size(); b++) fprintf(out, "%s\t%zu\t%zu\n", cid.c_str(), bp.first[b], bp.last[b]);
-        fclose(out);
+        append_blocks(out_path, cid, bp);
     }
-    fclose(bed);
     if (verbose) std::cout << "Done." << std::endl;
+    return CUSK_OK;
+}
+
+// Chromosomes are independent units (no collective): one worker thread per device takes them largest
+// first; the blocks are appended in .bim order once all are done, so the file equals the one-device run's.
+int run_block_all(const std::string &bfiles, int max_block_size, float device_mem_gb, size_t corr_width,
+                  const std::vector<int> &devices)
+{
+    for (const char *sfx : {".bed", ".bim", ".fam"}) check_path(bfiles + sfx);
+    if (!has_valid_bed_prefix(bfiles + ".bed")) fail("Invalid prefix bytes in bed");
+    if (devices.empty()) fail("no CUDA device available");
+    const size_t n = count_lines(bfiles + ".fam");
+    BimInfo bim(bfiles + ".bim");
+    const size_t nchr = bim.chr_ids.size();
+    std::vector<size_t> order(nchr);
+    for (size_t i = 0; i < nchr; i++) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return bim.num_on_chr[a] > bim.num_on_chr[b]; });
+    std::vector<BlockPartition> parts(nchr);
+    std::atomic<size_t> next{0};
+    std::mutex mu;
+    int first_rc = CUSK_OK, exit_code = 0;
+    std::string first_error;
+    std::vector<std::thread> workers;
+    for (int dev : devices) {
+        workers.emplace_back([&, dev]() {
+            cusk_ctx *ctx = nullptr;
+            FileCloser bed{fopen((bfiles + ".bed").c_str(), "rb")};
+            int rc = bed.f ? cusk_ctx_create(dev, &ctx) : CUSK_E_ARG;
+            std::string err = rc ? (bed.f ? cusk_last_error() : "file or directory not found: " + bfiles + ".bed") : "";
+            int code = 0;
+            while (rc == CUSK_OK) {
+                const size_t k = next.fetch_add(1);
+                if (k >= nchr) break;
+                const size_t c = order[k];
+                cusk_band_stats bs;
+                try {
+                    rc = block_chromosome(ctx, bed.f, bfiles, bim, c, n, max_block_size, device_mem_gb, corr_width, false,
+                                          &parts[c], &bs);
+                    if (rc) err = cusk_last_error();
+                } catch (const HostError &e) {
+                    rc = CUSK_E_ARG;
+                    err = e.msg;
+                    code = e.code;
+                }
+                if (rc == CUSK_OK) {
+                    std::lock_guard<std::mutex> lk(mu);
+                    log_chromosome(bim.chr_ids[c], bim.num_on_chr[c], dev, bs, parts[c]);
+                }
+            }
+            if (ctx) cusk_ctx_destroy(ctx);
+            if (rc != CUSK_OK) {
+                next.store(nchr);  // let the other workers finish what they hold and stop
+                std::lock_guard<std::mutex> lk(mu);
+                if (first_rc == CUSK_OK) {
+                    first_rc = rc;
+                    first_error = err;
+                    exit_code = code;
+                }
+            }
+        });
+    }
+    for (auto &w : workers) w.join();
+    if (first_rc != CUSK_OK) {
+        if (exit_code) fail(first_error, exit_code);
+        cusk_set_error("%s", first_error.c_str());
+        return first_rc;
+    }
+    const std::string out_path = bfiles + "_m" + std::to_string(max_block_size) + ".blocks";
+    for (size_t c = 0; c < nchr; c++) append_blocks(out_path, bim.chr_ids[c], parts[c]);
+    std::cout << "Done." << std::endl;
     return CUSK_OK;
 }
 

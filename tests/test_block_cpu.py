@@ -163,3 +163,38 @@ def test_plane_tables_match_oracle(hostcore, orc, n):
                 seen.add(used.value)
     if n >= 15:
         assert seen == {0, 1}  # both the four-count and the nine-count route were exercised
+
+
+# ---- the `mps block` process without a device: argument handling, and no CPU route --------------------------
+
+def test_mps_block_arguments_and_no_cpu_fallback(tmp_path):
+    import cigwas_b200
+
+    mps = cigwas_b200.mps_path()
+    r = subprocess.run([mps, "block", "x", "10"], capture_output=True, text=True)
+    assert r.returncode == 1 and "usage: mps block <bfiles> <max-block-size> <device-mem-gb> <corr-width>" in r.stdout
+    r = subprocess.run([mps, "block", str(tmp_path / "absent"), "10", "1", "5"], capture_output=True, text=True)
+    assert r.returncode == 1 and "file or directory not found" in r.stdout  # check_path, io.cpp:399-406
+    # a valid file set: without a CUDA device the command must fail, not compute on the host
+    rng = np.random.default_rng(1)
+    n, m = 40, 30
+    bed = random_bed(rng, m, n)
+    stem = str(tmp_path / "g")
+    with open(stem + ".bed", "wb") as f:
+        f.write(bytes([0x6C, 0x1B, 0x01]) + bed.tobytes())
+    with open(stem + ".bim", "w") as f:
+        f.writelines(f"1\trs{i}\t0\t{i + 1}\tA\tG\n" for i in range(m))
+    with open(stem + ".fam", "w") as f:
+        f.writelines(f"f{i} i{i} 0 0 0 -9\n" for i in range(n))
+    have_gpu = subprocess.run(["nvidia-smi", "-L"], capture_output=True).returncode == 0 if _which("nvidia-smi") else False
+    r = subprocess.run([mps, "block", stem, "10", "1", "5"], capture_output=True, text=True)
+    if have_gpu:
+        assert r.returncode == 0 and os.path.exists(stem + "_m10.blocks")
+    else:
+        assert r.returncode != 0 and not os.path.exists(stem + "_m10.blocks")
+
+
+def _which(name):
+    import shutil
+
+    return shutil.which(name)
