@@ -165,6 +165,15 @@ struct DevBuf {  // chromosome-sized scratch: allocated per call, not from the c
     }
 };
 
+struct Events4 {
+    cudaEvent_t e[4] = {nullptr, nullptr, nullptr, nullptr};
+    ~Events4()
+    {
+        for (auto &x : e)
+            if (x) cudaEventDestroy(x);
+    }
+};
+
 }  // namespace
 
 // Markers [0, Mc) of the chunk are on the device in d_bed; computes rows [0, R).
@@ -227,8 +236,9 @@ extern "C" int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_
     CUSK_CUDA(cudaMalloc(&b_counts.p, batch * 16));
     CUSK_CUDA(cudaMalloc(&b_out.p, rows_per_chunk * W * sizeof(float)));
     CUSK_CUDA(cudaMalloc(&b_sums.p, rows_per_chunk * sizeof(float)));
-    cudaEvent_t ev[4];
-    for (auto &e : ev) CUSK_CUDA(cudaEventCreate(&e));
+    Events4 evs;
+    cudaEvent_t *ev = evs.e;
+    for (auto &e : evs.e) CUSK_CUDA(cudaEventCreate(&e));
     int rc = CUSK_OK;
     for (size_t r0 = 0; r0 < m && rc == CUSK_OK; r0 += rows_per_chunk) {
         const size_t R = std::min(rows_per_chunk, m - r0);
@@ -266,7 +276,6 @@ extern "C" int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_
         st->chunks += 1;
         st->bed_bytes += (int64_t)(Mc * col_bytes);
     }
-    for (auto &e : ev) cudaEventDestroy(e);
     // pairs inside the band: row r has min(W, m - 1 - r) of them
     st->pairs = (int64_t)((m - W) * W + W * (W - 1) / 2);
     return rc;

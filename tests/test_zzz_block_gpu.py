@@ -63,6 +63,27 @@ def test_banded_golden(ctx, golden):
     assert r["stats"]["pairs"] == 4 * 3 + 3  # rows 0..3 full, then 2 + 1 + 0
 
 
+def test_reference_named_entry_point(golden):
+    """cu_marker_corr_pearson_npn_batched_sparse with the reference's own arguments (corr_tests.cpp:76-99: corr_width 3,
+    batch_size 5) -- the batch size only bounded the reference's device buffers"""
+    import ctypes as C
+
+    import cigwas_b200
+
+    lib = cigwas_b200.load_library()
+    with open(os.path.join(ROOT, "tests", "golden", "block_golden.json")) as f:
+        g = json.load(f)["bmt2_sparse_mcorrs"]
+    b = golden["bmt2"]
+    bed = np.array(b["bed"], np.uint8)
+    out = np.zeros(3 * b["m"], np.float32)
+    lib.cu_marker_corr_pearson_npn_batched_sparse.restype = None
+    lib.cu_marker_corr_pearson_npn_batched_sparse.argtypes = [C.POINTER(C.c_ubyte), C.c_size_t, C.c_size_t, C.c_size_t,
+                                                              C.c_size_t, C.POINTER(C.c_float)]
+    lib.cu_marker_corr_pearson_npn_batched_sparse(bed.ctypes.data_as(C.POINTER(C.c_ubyte)), b["m"], b["n"], 3, 5,
+                                                  out.ctypes.data_as(C.POINTER(C.c_float)))
+    assert np.abs(out - np.array(g["expected"])).max() < g["tol"]
+
+
 @pytest.mark.parametrize("m,n,w,miss", [
     (7, 100, 3, 0.0), (40, 33, 5, 0.0), (40, 33, 39, 0.05), (70, 1023, 31, 0.0), (70, 1025, 32, 0.0),
     (100, 2050, 33, 0.02), (130, 4097, 64, 0.0), (97, 777, 96, 0.0), (300, 1500, 20, 0.0),
