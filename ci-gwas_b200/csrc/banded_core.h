@@ -60,3 +60,33 @@ BANDC_HD inline void bandc_table_from_joint(long long s11, long long s12, long l
     s[7] = (double)s21;
     s[8] = (double)s22;
 }
+
+// Tensor-core route (CUSK_BLOCK_TC=1): tiles of the indicator Gram kernel (corr_gram.cu) that hold at least one pair
+// of the band.  Markers sit MI to a 128-row group; tile (tm, tn) pairs the markers of group tm (A side) with those of
+// groups 2 tn, 2 tn + 1 (B side).  A pair (i, j), i < j, lies in exactly one tile (tm = i / MI, tn = j / (2 MI)), so
+// every band pair 0 < j - i <= W with i < R, j < Mc is computed once when the tiles below are run.
+// Returns the number of tiles; writes (tm, tn) pairs to out when out != nullptr (capacity cap, in tiles).
+inline size_t bandc_gram_tiles(size_t Mc, size_t R, size_t W, size_t MI, int *out, size_t cap)
+{
+    const size_t groups = (Mc + MI - 1) / MI, n_tn = (groups + 1) / 2;
+    size_t cnt = 0;
+    for (size_t tm = 0; tm < groups; tm++) {
+        const size_t a_min = tm * MI;
+        if (a_min >= R) break;
+        size_t a_max = a_min + MI - 1;
+        if (a_max > R - 1) a_max = R - 1;
+        // B blocks holding some j in (a_min, a_max + W]
+        const size_t tn_lo = (a_min + 1) / (2 * MI);
+        size_t j_hi = a_max + W;
+        if (j_hi > Mc - 1) j_hi = Mc - 1;
+        const size_t tn_hi = j_hi / (2 * MI);
+        for (size_t tn = tn_lo; tn <= tn_hi && tn < n_tn; tn++) {
+            if (out && cnt < cap) {
+                out[2 * cnt] = (int)tm;
+                out[2 * cnt + 1] = (int)tn;
+            }
+            cnt++;
+        }
+    }
+    return cnt;
+}

@@ -29,6 +29,10 @@ struct GramParams {
     const double *Ty;           // [p] sum of valid y
     const int *cnty;            // [p] number of valid y
     float *mxp;                 // [m*p] out
+    // banded output (`mps block`, corr_banded.cu): when band != nullptr the pairs 0 < j - i <= band_w with
+    // i < band_rows go to band[i * band_w + (j - i - 1)] and nothing is written to C
+    float *band;
+    int band_w, band_rows;
 };
 
 #define CUSK_TC_MXP_MAX_TRAITS 32

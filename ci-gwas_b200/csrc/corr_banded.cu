@@ -13,11 +13,21 @@
 // operands staged through shared memory as 32 x 32 marker tiles so that every plane word fetched from L2 serves 32
 // pairs.  Algorithmic bytes: the chunk's planes once per tile row/column it takes part in (L2 resident), 4 W bytes
 // written per row.  The tensor-core route (band-restricted tile list on the tcgen05 indicator Gram of
-// corr_gram.cu) is the planned replacement once it can be measured on a GPU.
+// corr_gram.cu, banded_chunk_device_tc below) is selected with CUSK_BLOCK_TC=1; it has not run on a GPU yet and
+// becomes the default only after scripts/r2_first_gpu_call.sh has shown it equal and faster.
 #include "banded_core.h"
 #include "corr.cuh"
 
+#include <cuda.h>
+
+#include <vector>
+
 void launch_bed_counts(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int *counts);
+// tensor-core route (corr_kernels.cu, corr_gram.cu)
+void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int parts, int MI,
+                   size_t Kp, unsigned char *ind);
+int launch_gram(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMap &map_b, const GramParams &p, int grid);
+int gram_make_maps(const unsigned char *ind, size_t rows, size_t Kp, CUtensorMap *map_a, CUtensorMap *map_b);
 cusk_ctx *cusk_default_ctx();
 
 #define BT 32        // markers per tile edge
@@ -194,6 +204,61 @@ static int banded_chunk_device(cusk_ctx *ctx, const unsigned char *d_bed, int Mc
     return CUSK_OK;
 }
 
+// Tensor-core route, CUSK_BLOCK_TC=1 (NOT the default: written after the round's GPU budget was spent, see DESIGN.md
+// section 7): the chunk's columns become uint8 indicator rows (decode_indicators_kernel), the tcgen05 int8 Gram kernel
+// of corr_gram.cu runs over the tiles that intersect the band (bandc_gram_tiles) and its epilogue writes band
+// coordinates.  Same exact integer tables and the same FP64 npn_from_table as banded_npn_kernel -> same floats.
+// Operand rows per marker: 2 when the chunk has no missing call, else 3 (a host look at the counts decides).
+static size_t tc_ind_rows(size_t markers, size_t MI) { return ((((markers + MI - 1) / MI) * 128 + 255) / 256) * 256; }
+
+static int banded_chunk_device_tc(cusk_ctx *ctx, const unsigned char *d_bed, int Mc, int R, size_t n, int W,
+                                  unsigned char *d_ind, int *d_counts, int2 *d_tiles, size_t tiles_cap,
+                                  std::vector<int> &h_scratch, float *d_out, float *d_sums)
+{
+    cudaStream_t s = ctx->stream;
+    const size_t col_bytes = (n + 3) / 4, Kp = align_up(n, 128);
+    launch_bed_counts(s, d_bed, Mc, (int)n, col_bytes, d_counts);
+    h_scratch.resize(std::max<size_t>(4 * (size_t)Mc, 2 * tiles_cap));
+    CUSK_CUDA(cudaMemcpyAsync(h_scratch.data(), d_counts, sizeof(int) * 4 * (size_t)Mc, cudaMemcpyDeviceToHost, s));
+    CUSK_CUDA(cudaStreamSynchronize(s));
+    bool any_missing = false;
+    for (int i = 0; i < Mc; i++) any_missing |= h_scratch[4 * (size_t)i + 3] != 0;
+    const int parts = any_missing ? 3 : 2, MI = 128 / parts;
+    const size_t rows = tc_ind_rows((size_t)Mc, (size_t)MI);
+    CUSK_CUDA(cudaMemsetAsync(d_ind, 0, rows * Kp, s));  // padding rows of every group and the tail of K must be zero
+    launch_decode(s, d_bed, Mc, (int)n, col_bytes, parts, MI, Kp, d_ind);
+    const size_t ntiles = bandc_gram_tiles((size_t)Mc, (size_t)R, (size_t)W, (size_t)MI, h_scratch.data(), tiles_cap);
+    if (ntiles > tiles_cap) {
+        cusk_set_error("cusk_mcorrk_banded: tile list overflow (%zu > %zu)", ntiles, tiles_cap);
+        return CUSK_E_ARG;
+    }
+    CUSK_CUDA(cudaMemcpyAsync(d_tiles, h_scratch.data(), sizeof(int2) * ntiles, cudaMemcpyHostToDevice, s));
+    CUSK_CUDA(cudaMemsetAsync(d_out, 0, sizeof(float) * (size_t)R * W, s));
+    CUtensorMap map_a, map_b;
+    int rc = gram_make_maps(d_ind, rows, Kp, &map_a, &map_b);
+    if (rc) return rc;
+    GramParams gp = {};
+    gp.parts = parts;
+    gp.MI = MI;
+    gp.m = Mc;
+    gp.n_samples = (int)n;
+    gp.num_k = (int)(Kp / 128);
+    gp.ntiles = (int)ntiles;
+    gp.tiles = d_tiles;
+    gp.counts = d_counts;
+    gp.mode = 0;
+    gp.trait_tn = -1;
+    gp.band = d_out;
+    gp.band_w = W;
+    gp.band_rows = R;
+    rc = launch_gram(s, map_a, map_b, gp, std::min<int>(ctx->sm_count, (int)ntiles));
+    if (rc) return rc;
+    if (d_sums) band_row_abs_sums_kernel<<<(R + 127) / 128, 128, 0, s>>>(d_out, R, W, d_sums);
+    CUSK_CUDA(cudaGetLastError());
+    CUSK_CUDA(cudaStreamSynchronize(s));  // h_scratch (the host tile list) is reused by the next chunk
+    return CUSK_OK;
+}
+
 extern "C" int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_t m, size_t n, size_t corr_width,
                                   float device_mem_gb, float *corrs, float *row_abs_sums, cusk_band_stats *stats)
 {
@@ -217,13 +282,21 @@ extern "C" int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_
     const size_t Kw = align_up((n + 31) / 32, BKC);
     const size_t W = corr_width;
     // device bytes per marker held (bed + planes + counts) and per row computed (band + sum)
-    const size_t per_marker = col_bytes + 12 * Kw + 16, per_row = 4 * W + 4;
+    const char *tc_env = getenv("CUSK_BLOCK_TC");
+    const bool tc = tc_env && atoi(tc_env) != 0;
+    const size_t Kp = align_up(n, 128);
+    // tensor-core route: uint8 indicator rows, at most 3 per marker with 42 markers to a 128-row group, plus one
+    // 256-row block of padding; 8 bytes of tile list per marker are more than the band ever needs per group
+    const size_t per_marker = tc ? col_bytes + (128 * Kp + 41) / 42 + 16 + 8 * (W / 84 + 4) : col_bytes + 12 * Kw + 16;
+    const size_t per_row = 4 * W + 4;
     size_t free_b = 0, total_b = 0;
     CUSK_CUDA(cudaMemGetInfo(&free_b, &total_b));
     double budget = 0.9 * (double)free_b;
     if (device_mem_gb > 0.f) budget = std::min(budget, (double)device_mem_gb * 1e9);
-    size_t batch = (size_t)(budget / (double)(per_marker + per_row));
+    if (tc) budget -= 384.0 * (double)Kp;
+    size_t batch = budget > 0 ? (size_t)(budget / (double)(per_marker + per_row)) : 0;
     if (batch > m) batch = m;
+    if (tc && batch > 65535) batch = 65535;  // decode_indicators_kernel takes the marker from blockIdx.y
     if (batch < m && batch <= W) {  // a chunk holds its rows plus the W markers to their right
         cusk_set_error("Maximal batch size (%zu) <= corr width (%zu). Decrease distance threshold or increase device memory.",
                        batch, W);
@@ -232,7 +305,14 @@ extern "C" int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_
     const size_t rows_per_chunk = batch == m ? m : batch - W;
     DevBuf b_bed, b_planes, b_counts, b_out, b_sums;
     CUSK_CUDA(cudaMalloc(&b_bed.p, batch * col_bytes));
-    CUSK_CUDA(cudaMalloc(&b_planes.p, batch * 12 * Kw));
+    const size_t tiles_cap = tc ? batch * (W / 84 + 4) : 0;  // per 42-marker group at most W / 84 + 3 B blocks
+    DevBuf b_tiles;
+    std::vector<int> h_scratch;
+    if (tc) {
+        CUSK_CUDA(cudaMalloc(&b_planes.p, tc_ind_rows(batch, 42) * Kp));
+        CUSK_CUDA(cudaMalloc(&b_tiles.p, std::max<size_t>(tiles_cap, 1) * sizeof(int2)));
+    } else
+        CUSK_CUDA(cudaMalloc(&b_planes.p, batch * 12 * Kw));
     CUSK_CUDA(cudaMalloc(&b_counts.p, batch * 16));
     CUSK_CUDA(cudaMalloc(&b_out.p, rows_per_chunk * W * sizeof(float)));
     CUSK_CUDA(cudaMalloc(&b_sums.p, rows_per_chunk * sizeof(float)));
@@ -252,8 +332,14 @@ extern "C" int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_
             break;
         }
         cudaEventRecord(ev[1], s);
-        rc = banded_chunk_device(ctx, (const unsigned char *)b_bed.p, (int)Mc, (int)R, n, (int)W, Kw, (uint32_t *)b_planes.p,
-                                 (int *)b_counts.p, (float *)b_out.p, row_abs_sums ? (float *)b_sums.p : nullptr);
+        if (tc)
+            rc = banded_chunk_device_tc(ctx, (const unsigned char *)b_bed.p, (int)Mc, (int)R, n, (int)W,
+                                        (unsigned char *)b_planes.p, (int *)b_counts.p, (int2 *)b_tiles.p, tiles_cap,
+                                        h_scratch, (float *)b_out.p, row_abs_sums ? (float *)b_sums.p : nullptr);
+        else
+            rc = banded_chunk_device(ctx, (const unsigned char *)b_bed.p, (int)Mc, (int)R, n, (int)W, Kw,
+                                     (uint32_t *)b_planes.p, (int *)b_counts.p, (float *)b_out.p,
+                                     row_abs_sums ? (float *)b_sums.p : nullptr);
         if (rc) break;
         cudaEventRecord(ev[2], s);
         if (corrs) cudaMemcpyAsync(corrs + r0 * W, b_out.p, sizeof(float) * R * W, cudaMemcpyDeviceToHost, s);

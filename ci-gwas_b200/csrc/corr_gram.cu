@@ -301,6 +301,7 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         const int il = pq / EPI_MARKERS, jl = pq % EPI_MARKERS;
                         const int i = i0 + il, j = jbase_group + mc * EPI_MARKERS + jl;
                         if (mc * EPI_MARKERS + jl >= MI || i >= p.m || j >= p.m || j <= i) continue;
+                        if (p.band && (j - i > p.band_w || i >= p.band_rows)) continue;  // outside the band
                         const int *e = epi + (il * parts) * EPI_STRIDE + jl * parts;
                         double s[9];
                         if (parts == 2) {
@@ -337,6 +338,10 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             r = pearson_from_table(s, (double)p.mean[i], (double)p.mean[j], (double)p.stdv[i],
                                                    (double)p.stdv[j]);
                         const float rf = (float)r;
+                        if (p.band) {  // `mps block`: out[row][k] = correlation of (row, row + 1 + k)
+                            p.band[(size_t)i * p.band_w + (j - i - 1)] = rf;
+                            continue;
+                        }
                         p.C[(size_t)i * p.ldc + j] = rf;
                         p.C[(size_t)j * p.ldc + i] = rf;
                         if (p.tables) {

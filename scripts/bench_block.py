@@ -54,4 +54,6 @@ print(json.dumps({
     "sample_pair_rate_G": pairs * n / (st["kernel_ms"] * 1e-3) / 1e9, "pairs": pairs,
     "cpu_pairs_per_s": rows * w / cpu_s, "cpu_cores": orc.num_threads(), "cpu_sample": f"{rows} rows x {w}",
     "max_abs_diff_head": diff, "max_abs_diff_tail": dtail,
+    "route": "tcgen05 indicator Gram (CUSK_BLOCK_TC=1)" if os.environ.get("CUSK_BLOCK_TC", "0") not in ("", "0")
+    else "AND + POPC bit planes (default)",
 }))

@@ -45,3 +45,9 @@ extern "C" void bandc_host_pair_table(const unsigned char *bed, size_t n, size_t
     bandc_table_from_joint(j[0][0], j[0][1], j[1][0], j[1][1], ca, cb, (long long)n, s);
     for (int i = 0; i < 9; i++) s9[i] = (long long)s[i];
 }
+
+// tile list of the tensor-core route: number of tiles, (tm, tn) pairs into out
+extern "C" size_t bandc_host_gram_tiles(size_t Mc, size_t R, size_t W, size_t MI, int *out, size_t cap)
+{
+    return bandc_gram_tiles(Mc, R, W, MI, out, cap);
+}

@@ -165,6 +165,35 @@ def test_plane_tables_match_oracle(hostcore, orc, n):
         assert seen == {0, 1}  # both the four-count and the nine-count route were exercised
 
 
+# ---- tile list of the tensor-core route (CUSK_BLOCK_TC=1): every band pair lies in exactly one listed tile ------
+
+@pytest.mark.parametrize("Mc,R,W,MI", [
+    (7, 7, 3, 64), (7, 7, 3, 42), (200, 200, 40, 64), (500, 470, 30, 42), (1000, 488, 512, 64), (1000, 488, 512, 42),
+    (129, 129, 128, 64), (4096, 4096, 1, 64), (85, 43, 42, 42), (3000, 2000, 1000, 64),
+])
+def test_gram_band_tiles_cover_the_band_once(hostcore, Mc, R, W, MI):
+    hostcore.bandc_host_gram_tiles.restype = C.c_size_t
+    hostcore.bandc_host_gram_tiles.argtypes = [C.c_size_t] * 4 + [C.POINTER(C.c_int), C.c_size_t]
+    cap = Mc * (W // 84 + 4)  # the capacity cusk_mcorrk_banded reserves
+    buf = np.zeros(2 * cap, np.int32)
+    cnt = hostcore.bandc_host_gram_tiles(Mc, R, W, MI, buf.ctypes.data_as(C.POINTER(C.c_int)), cap)
+    assert 0 < cnt <= cap
+    assert hostcore.bandc_host_gram_tiles(Mc, R, W, MI, None, 0) == cnt  # counting pass
+    tiles = buf[:2 * cnt].reshape(cnt, 2)
+    groups = (Mc + MI - 1) // MI
+    assert (tiles[:, 0] >= 0).all() and (tiles[:, 0] < groups).all()
+    assert (tiles[:, 1] >= 0).all() and (tiles[:, 1] < (groups + 1) // 2).all()
+    listed = set(map(tuple, tiles.tolist()))
+    assert len(listed) == cnt  # no tile twice
+    i = np.arange(R)[:, None]
+    j = i + 1 + np.arange(W)[None, :]
+    ok = j < Mc
+    need = set(zip((np.broadcast_to(i, j.shape)[ok] // MI).tolist(), (j[ok] // (2 * MI)).tolist()))
+    assert need <= listed
+    # and the list is tight: a listed tile is at most one block beyond what the band needs
+    assert len(listed) <= len(need) + groups
+
+
 # ---- the `mps block` process without a device: argument handling, and no CPU route --------------------------
 
 def test_mps_block_arguments_and_no_cpu_fallback(tmp_path):
