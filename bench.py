@@ -94,6 +94,8 @@ def cpu_port_tests_per_s(Cm, N, steps=1):
     from tests import oracle_lib
 
     orc = oracle_lib.load()
+    # all the host cores this process may use, whatever OMP_NUM_THREADS says (torchrun sets it to 1 for its workers)
+    orc.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     Cs, Ns = sample_of(Cm, N)
     n = Cs.shape[0]
     th = orc.hetcor_threshold(ALPHA)

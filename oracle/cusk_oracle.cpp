@@ -1046,6 +1046,17 @@ void orc_subset_variables(const int *G, int num_var, int num_markers, int max_de
     }
 }
 
+// bench.py's CPU legs ask for all host cores: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+// otherwise time the CPU baseline on one thread
+void orc_set_num_threads(int t)
+{
+#ifdef _OPENMP
+    if (t > 0) omp_set_num_threads(t);
+#else
+    (void)t;
+#endif
+}
+
 int orc_num_threads(void)
 {
 #ifdef _OPENMP

@@ -50,6 +50,9 @@ class Oracle:
     def num_threads(self):
         return int(self.lib.orc_num_threads())
 
+    def set_num_threads(self, t):
+        self.lib.orc_set_num_threads(int(t))
+
     def skeleton(self, Cm, Th, maxlevel, near_band=0.0):
         """-> dict(G, l, pMax, SepSet, stats, near)"""
         Cm = np.ascontiguousarray(Cm, np.float32)
