@@ -147,6 +147,102 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_pipelined_probe(args):
+    """Extra, informational leg (key `e2e_pipelined`, N=1 only, run in a child process so that it cannot touch the
+    main line): the same reference-facing call with the same pinned host buffers, but issued from TWO host threads
+    on two contexts of the one device, so that the copies of one block overlap the level loop of the other -- what
+    the block scheduler (`mps cuskss-all`, host/sched.cu) does with a stream of blocks.  Every step still copies
+    its 109 MB in and 36 MB out inside the timed region.  First written without GPU time; its results are checked
+    against the serial call before anything is reported."""
+    import ctypes as C
+    import threading
+
+    import torch
+
+    import cigwas_b200
+
+    torch.cuda.set_device(0)
+    Cm, N = make_block(0)
+    n = Cm.shape[0]
+    th = cigwas_b200.hetcor_threshold(ALPHA)
+    ti = np.zeros(n, np.int32)
+    ti[M_MARKERS:] = 1
+    fp, ip = C.POINTER(C.c_float), C.POINTER(C.c_int)
+    hC = torch.from_numpy(Cm).pin_memory()
+    hN = torch.from_numpy(N).pin_memory()
+    steps = max(2, min(args.steps, 16))
+    steps -= steps % 2
+    bufs = [torch.ones((n, n), dtype=torch.int32).pin_memory() for _ in range(steps)]
+    ctxs = [cigwas_b200.Context(0), cigwas_b200.Context(0)]
+    lib = ctxs[0].lib
+
+    def call(ctx, hG):
+        st = cigwas_b200.Stats()
+        l = C.c_int(0)
+        rc = lib.cusk_hetcor_skeleton(ctx.h, C.cast(hC.data_ptr(), fp), n, C.cast(hG.data_ptr(), ip), 0,
+                                      C.cast(hN.data_ptr(), fp), C.c_float(th), MAXLEVEL, ti.ctypes.data_as(ip),
+                                      C.byref(l), C.byref(st))
+        if rc != 0:
+            raise RuntimeError(lib.cusk_last_error().decode())
+        return sum(st.tests_executed)
+
+    scratch = torch.ones((n, n), dtype=torch.int32).pin_memory()
+    call(ctxs[0], scratch)
+    expect = scratch.numpy().copy()
+    for _ in range(max(1, args.warmup)):  # both contexts warm, one after the other
+        for c in ctxs:
+            scratch.fill_(1)
+            call(c, scratch)
+    torch.cuda.synchronize()
+    gate = threading.Barrier(3)
+    tests = [0, 0]
+    errors = []
+
+    def worker(t):
+        try:
+            gate.wait()
+            for k in range(t, steps, 2):
+                tests[t] += call(ctxs[t], bufs[k])
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+        finally:
+            gate.wait()
+
+    th_ = [threading.Thread(target=worker, args=(t,)) for t in range(2)]
+    for t in th_:
+        t.start()
+    gate.wait()
+    t0 = time.perf_counter()
+    gate.wait()
+    wall = time.perf_counter() - t0
+    for t in th_:
+        t.join()
+    same = not errors and all(np.array_equal(b.numpy(), expect) for b in bufs)
+    nn = n * n
+    print(json.dumps({"value": sum(tests) / wall if same else None, "unit": "tests/s", "ms_per_step": 1e3 * wall / steps,
+                      "steps": steps, "host_threads": 2, "contexts_on_device": 2, "same_as_serial_call": bool(same),
+                      "errors": errors, "h2d_bytes_per_step": 3 * nn * 4, "d2h_bytes_per_step": nn * 4,
+                      "l2": "not flushed: every step's inputs arrive from host memory",
+                      "api": "cusk_hetcor_skeleton from two host threads, one context each"}), flush=True)
+    for c in ctxs:
+        c.close()
+
+
+def pipelined_probe_in_child(args):
+    import subprocess
+
+    try:
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--probe-pipelined", "--steps", str(args.steps),
+                            "--warmup", str(args.warmup)], capture_output=True, text=True, timeout=240,
+                           env=dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0")))
+        for ln in reversed(r.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)
+        return {"unavailable": f"probe exited {r.returncode}: {(r.stderr or r.stdout)[-300:]}"}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": repr(e)[:300]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -155,7 +251,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--no-pipelined-probe", action="store_true")
+    ap.add_argument("--probe-pipelined", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.probe_pipelined:
+        run_pipelined_probe(args)
+        return
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -334,6 +435,8 @@ def main():
                                            "--use_fast_math) on the same B200 and block, host buffers in/out, wall clock",
                                    "ms_per_block": ref_ms,
                                    "adjacency_entries_differing": int((rr["G"] != hG.numpy()).sum())}
+        if world == 1 and not args.no_pipelined_probe:
+            line["e2e_pipelined"] = pipelined_probe_in_child(args)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
