@@ -192,6 +192,16 @@ def test_gram_band_tiles_cover_the_band_once(hostcore, Mc, R, W, MI):
     assert need <= listed
     # and the list is tight: a listed tile is at most one block beyond what the band needs
     assert len(listed) <= len(need) + groups
+    # the epilogue's filter (corr_gram.cu: j > i, j - i <= band_w, i < band_rows, both < m) applied to the listed
+    # tiles writes every cell of the band exactly once and nothing else
+    hits = np.zeros((R, W), np.int32)
+    for tm, tn in tiles.tolist():
+        ii = np.arange(tm * MI, min((tm + 1) * MI, Mc))[:, None]
+        jj = np.arange(2 * tn * MI, min((2 * tn + 2) * MI, Mc))[None, :]
+        keep = (jj > ii) & (jj - ii <= W) & (ii < R)
+        a, b = np.nonzero(keep)
+        np.add.at(hits, (ii[a, 0], jj[0, b] - ii[a, 0] - 1), 1)
+    assert np.array_equal(hits, ok.astype(np.int32))
 
 
 # ---- the `mps block` process without a device: argument handling, and no CPU route --------------------------
