@@ -195,3 +195,51 @@ def merged_correlation(loci=400, per_locus=50, p=17, stream=5, num_samples=45800
     np.fill_diagonal(Cm, 1.0)
     Cm = np.triu(Cm) + np.triu(Cm, 1).T
     return np.ascontiguousarray(Cm.astype(dtype))
+
+
+def simulate_dag(n=10000, snp=1600, tr=10, n_latent=2, deg=3, prob_pleio=0.2, lo_mp=0.001, hi_mp=0.05, lo_pp=0.001,
+                 hi_pp=0.2, stream=1):
+    """BASELINE.json configs[0]: the small synthetic DAG of simulation/simulate_dag.R (gen_rand_dag, :3-98, called
+    with the constants of :106-116; the file uses n = 16 000, BASELINE.json names n = 10 000).
+
+    Nodes in topological order: `snp` markers, `n_latent` latent variables, `tr` traits.  Edges only point to later
+    nodes: a marker reaches each later node with probability deg/snp (:22-28); a marker with exactly one trait child
+    gets each OTHER trait with probability prob_pleio (:30-39); a latent variable or trait reaches each later node with
+    probability min(1, deg/tr) (:41-47).  |effect| ~ U(lo_mp, hi_mp) from a marker to a latent variable or trait,
+    U(lo_pp, hi_pp) otherwise, random sign (:53-78).  A node without parents is N(0,1); otherwise the parents'
+    combination plus N(0, 1 - var) noise (:80-90; a negative residual variance, NaN in R, is clipped to 1e-6 here).
+    The latent columns are dropped and the sample correlation of the rest is what cuskss gets (:118-124).
+    numpy's PCG64 stream, not R's Mersenne twister: the same distributions, not the same draws.
+    Returns (C [snp+tr, snp+tr] float32, true adjacency [snp+tr, snp+tr] bool of the DAG without latent variables)."""
+    rng = rng_for(1000 + stream)
+    pq = snp + n_latent + tr
+    first_trait = snp + n_latent
+    G = np.zeros((pq, pq), bool)
+    for i in range(snp):
+        G[i, i + 1:] = rng.random(pq - i - 1) < deg / snp
+    for i in range(snp):
+        kids = np.flatnonzero(G[i, first_trait:])
+        if kids.size == 1:
+            others = np.setdiff1d(np.arange(tr), kids)
+            G[i, first_trait + others] = rng.random(tr - 1) < prob_pleio
+    for j in range(snp, pq):
+        G[j, j + 1:] = rng.random(pq - j - 1) < min(1.0, deg / tr)
+    A = np.zeros((pq, pq))
+    for i in range(pq):
+        kids = np.flatnonzero(G[i])
+        lo = np.where((i < snp) & (kids >= snp), lo_mp, lo_pp)
+        hi = np.where((i < snp) & (kids >= snp), hi_mp, hi_pp)
+        A[i, kids] = rng.uniform(lo, hi) * np.where(rng.random(kids.size) < 0.5, -1.0, 1.0)
+    x = np.empty((n, pq))
+    for i in range(pq):
+        anc = np.flatnonzero(G[:, i])
+        if anc.size == 0:
+            x[:, i] = rng.standard_normal(n)
+        else:
+            g = x[:, anc] @ A[anc, i]
+            x[:, i] = g + rng.standard_normal(n) * np.sqrt(max(1.0 - g.var(ddof=1), 1e-6))
+    keep = np.r_[np.arange(snp), np.arange(first_trait, pq)]
+    C = np.corrcoef(x[:, keep], rowvar=False).astype(np.float32)
+    np.fill_diagonal(C, 1.0)
+    truth = G[np.ix_(keep, keep)]
+    return C, truth | truth.T
