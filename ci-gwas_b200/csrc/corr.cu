@@ -204,8 +204,6 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         rc = launch_gram(s, map_a, map_b, gp, std::min<int>(ctx->sm_count, (int)tiles.size()));
         if (rc) return rc;
         t_gram.stop();
-        if (tc_mxp && d_Csq)
-            scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
         CUSK_CUDA(cudaGetLastError());
         CUSK_CUDA(cudaStreamSynchronize(s));  // the host tile list must outlive the copy
         if (st) {
@@ -214,6 +212,10 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
             st->gram_int8_ops = (int64_t)tiles.size() * 2 * 128 * 256 * (int64_t)Kp;
         }
     }
+    // tensor-core mxp route: d_mxp is valid here whether this call computed it (trait tiles above) or the caller's
+    // screen did (mxp_ready) -- also for a one-marker block, which has no Gram tile at all
+    if (tc_mxp && d_Csq)
+        scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
     if (d_Csq) launch_set_diag(s, d_Csq, nvar, nvar);
     CUSK_CUDA(cudaGetLastError());
     if (st) {

@@ -486,15 +486,21 @@ SquareInputs make_square_cuskss_inputs(const std::vector<float> &mxm_sq, size_t 
 // ---- outputs -----------------------------------------------------------------------------------------
 void Reduced::to_file(const std::string &base) const
 {
-    {
-        std::ofstream f(base + ".mdim", std::ios::out);
-        if (!f) fail("cannot write " + base + ".mdim");
-        f << num_var << "\t" << num_phen << "\t" << max_level << std::endl;
-    }
+    // .mdim is what `cusk-all` / `cuskss-all` take as "this block is done" when they resume (host/sched.cu), so it is
+    // written LAST and moved into place in one step: a run killed mid-write leaves no .mdim and the block is redone.
+    std::remove((base + ".mdim").c_str());
     write_ints_to_binary(new_to_old.data(), new_to_old.size(), base + ".ixs");
     write_ints_to_binary(G.data(), G.size(), base + ".adj");
     write_floats_to_binary(C.data(), C.size(), base + ".corr");
     if (has_sep) write_ints_to_binary(S.data(), S.size(), base + ".sep");
+    const std::string tmp = base + ".mdim.tmp";
+    {
+        std::ofstream f(tmp, std::ios::out);
+        if (!f) fail("cannot write " + tmp);
+        f << num_var << "\t" << num_phen << "\t" << max_level << std::endl;
+        if (!f) fail("cannot write " + tmp);
+    }
+    if (std::rename(tmp.c_str(), (base + ".mdim").c_str()) != 0) fail("cannot move " + tmp + " to " + base + ".mdim");
 }
 
 }  // namespace cuskhost

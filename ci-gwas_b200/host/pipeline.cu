@@ -186,7 +186,10 @@ void load_cuskss_shared(const CuskssArgs &a, CuskssShared *s)
     s->blocks = read_blocks(a.block_path);
     s->pxp = load_pxp(a.pxp_path, a.hetcor ? a.pxp_se_path : std::string(), a.pearson_sample_size);
     s->time_index_traits.assign(s->pxp.num_phen, 1);
-    if (a.time_indexed) s->time_index_traits = read_ints_from_lines(a.time_index_path);
+    if (a.time_indexed) {
+        s->time_index_traits = read_ints_from_lines(a.time_index_path);
+        if (s->time_index_traits.size() < s->pxp.num_phen) fail("time index file has fewer entries than traits");
+    }
     s->mxp_all = load_mxp(a.mxp_path, a.hetcor ? a.mxp_se_path : std::string(), true, 0, (size_t)-1, {});
 }
 
@@ -357,10 +360,11 @@ int run_cusk_block(cusk_ctx *ctx, const CuskArgs &a, const CuskShared &s, size_t
     {
         FILE *f = fopen((a.bfiles + ".bed").c_str(), "rb");
         if (!f) fail("file or directory not found: " + a.bfiles + ".bed");
-        fseek(f, (long)(3 + g0 * col_bytes), SEEK_SET);
-        const size_t got = fread(h_bed, 1, m * col_bytes, f);
+        // a short read must fail: code 00 is a valid genotype, so zero fill would give plausible wrong correlations
+        const bool seek_ok = fseeko(f, (off_t)(3 + g0 * col_bytes), SEEK_SET) == 0;
+        const size_t got = seek_ok ? fread(h_bed, 1, m * col_bytes, f) : 0;
         fclose(f);
-        if (got < m * col_bytes) memset(h_bed + got, 0, m * col_bytes - got);
+        if (got < m * col_bytes) fail("short read of " + a.bfiles + ".bed (block " + block.stem() + ")");
     }
     rep->load_s = now_s() - t0;
     const double t1 = now_s();

@@ -85,6 +85,61 @@ def c2_single_block(m=3000, p=17, num_samples=458000, stream=2):
     return sem_correlation(m, p, stream=stream, num_samples=num_samples)
 
 
+def c2_dense_block(m=3000, p=17, stream=2, sub_block=50, rho=0.9, cross=0.3, causal_per_trait=30, trait_density=0.3,
+                   num_samples=458000, beta_lo=0.01, beta_hi=0.05, dtype=np.float32):
+    """SURVEY 8d, config C2 as specified: marker LD is AR(1) inside sub-blocks of `sub_block` markers
+    (r_ij = rho^|i-j|), `cross` times that between markers of neighbouring sub-blocks and 0 beyond, projected to
+    positive definite (eigenvalues clipped at 1e-3, unit diagonal restored); every trait has `causal_per_trait`
+    causal markers (|beta| ~ U(beta_lo, beta_hi), random sign) plus lower-triangular trait-trait effects
+    U(-0.3, 0.3) with density `trait_density`; marker x trait and trait x trait correlations follow analytically
+    (R beta, beta' R beta).  Sampling noise N(0, 1/num_samples) is added off the diagonal as in sem_correlation.
+    Returns C [m+p, m+p] float32, markers first."""
+    rng = rng_for(stream + 200)
+    idx = np.arange(m)
+    dist = np.abs(idx[:, None] - idx[None, :]).astype(np.float64)
+    blk = idx // sub_block
+    dblk = np.abs(blk[:, None] - blk[None, :])
+    R = np.where(dblk == 0, rho ** dist, np.where(dblk == 1, cross * rho ** dist, 0.0))
+    w, V = np.linalg.eigh(R)
+    R = (V * np.clip(w, 1e-3, None)) @ V.T
+    s = 1.0 / np.sqrt(np.diag(R))
+    R = R * s[:, None] * s[None, :]
+    nv = m + p
+    Wm = np.zeros((p, m))  # trait = Wm g + Wn e (e: the traits' own unit noises)
+    Wn = np.zeros((p, p))
+    for t in range(p):
+        k = min(causal_per_trait, m)
+        par = rng.choice(m, size=k, replace=False)
+        Wm[t, par] += rng.uniform(beta_lo, beta_hi, size=k) * rng.choice([-1.0, 1.0], size=k)
+        for u in range(t):
+            if rng.random() < trait_density:
+                a = rng.uniform(-0.3, 0.3)
+                Wm[t] += a * Wm[u]
+                Wn[t] += a * Wn[u]
+        v = float(Wm[t] @ R @ Wm[t] + Wn[t] @ Wn[t])
+        if v > 0.9:
+            sc = np.sqrt(0.9 / v)
+            Wm[t] *= sc
+            Wn[t] *= sc
+            v = 0.9
+        Wn[t, t] = np.sqrt(1.0 - v)
+    Cm = np.zeros((nv, nv))
+    Cm[:m, :m] = R
+    Cm[:m, m:] = R @ Wm.T
+    Cm[m:, :m] = Cm[:m, m:].T
+    Cm[m:, m:] = Wm @ R @ Wm.T + Wn @ Wn.T
+    if num_samples:
+        E = rng.standard_normal((nv, nv)) / np.sqrt(float(num_samples))
+        E = np.triu(E, 1)
+        Cm = Cm + E + E.T
+    np.fill_diagonal(Cm, 1.0)
+    Cm = np.clip(Cm, -0.999999, 0.999999)
+    np.fill_diagonal(Cm, 1.0)
+    Cm = Cm.astype(dtype)
+    Cm = np.triu(Cm) + np.triu(Cm, 1).T
+    return np.ascontiguousarray(Cm)
+
+
 def het_sample_sizes(nv, m, num_samples, stream=5, lo=50000, na_rate=0.005):
     """Effective sample sizes of a heterologous-correlation run: marker-marker entries are the
     nominal sample size, marker-trait / trait-trait entries are U(lo, num_samples) and a fraction
