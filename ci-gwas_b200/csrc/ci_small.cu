@@ -324,7 +324,7 @@ static int cs_launch(cudaStream_t st, const CiParams &p)
         ctas_per_sm = nb;
         ctas_of_device[dev].store(nb, std::memory_order_release);
     }
-    ci_small_kernel<HET, LT><<<148 * ctas_per_sm, NT, dyn, st>>>(p);
+    ci_small_kernel<HET, LT><<<(p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm, NT, dyn, st>>>(p);
     return CUSK_OK;
 }
 

@@ -13,8 +13,9 @@
 // operands staged through shared memory as 32 x 32 marker tiles so that every plane word fetched from L2 serves 32
 // pairs.  Algorithmic bytes: the chunk's planes once per tile row/column it takes part in (L2 resident), 4 W bytes
 // written per row.  The tensor-core route (band-restricted tile list on the tcgen05 indicator Gram of
-// corr_gram.cu, banded_chunk_device_tc below) is selected with CUSK_BLOCK_TC=1; it has not run on a GPU yet and
-// becomes the default only after scripts/r2_first_gpu_call.sh has shown it equal and faster.
+// corr_gram.cu, banded_chunk_device_tc below) gives the same floats 4.7x faster (8 192 markers x 65 536 samples,
+// corr_width 512: 1.90 ms against 8.88 ms, profiles/r2_bench_block_tc.json) and is the default from
+// CUSK_BLOCK_TC_MIN_MARKERS (512) markers on; CUSK_BLOCK_TC=0 / 1 force one route.
 #include "banded_core.h"
 #include "corr.cuh"
 
@@ -204,8 +205,7 @@ static int banded_chunk_device(cusk_ctx *ctx, const unsigned char *d_bed, int Mc
     return CUSK_OK;
 }
 
-// Tensor-core route, CUSK_BLOCK_TC=1 (NOT the default: written after the round's GPU budget was spent, see DESIGN.md
-// section 7): the chunk's columns become uint8 indicator rows (decode_indicators_kernel), the tcgen05 int8 Gram kernel
+// Tensor-core route (default for 512 markers and more, see the file header): the chunk's columns become uint8 indicator rows (decode_indicators_kernel), the tcgen05 int8 Gram kernel
 // of corr_gram.cu runs over the tiles that intersect the band (bandc_gram_tiles) and its epilogue writes band
 // coordinates.  Same exact integer tables and the same FP64 npn_from_table as banded_npn_kernel -> same floats.
 // Operand rows per marker: 2 when the chunk has no missing call, else 3 (a host look at the counts decides).
@@ -283,7 +283,9 @@ extern "C" int cusk_mcorrk_banded(cusk_ctx *ctx, const unsigned char *bed, size_
     const size_t W = corr_width;
     // device bytes per marker held (bed + planes + counts) and per row computed (band + sum)
     const char *tc_env = getenv("CUSK_BLOCK_TC");
-    const bool tc = tc_env && atoi(tc_env) != 0;
+    const char *tc_min = getenv("CUSK_BLOCK_TC_MIN_MARKERS");
+    const size_t tc_min_markers = (tc_min && atoll(tc_min) > 0) ? (size_t)atoll(tc_min) : 512;
+    const bool tc = (tc_env && *tc_env) ? atoi(tc_env) != 0 : m >= tc_min_markers;
     const size_t Kp = align_up(n, 128);
     // tensor-core route: uint8 indicator rows, at most 3 per marker with 42 markers to a 128-row group, plus one
     // 256-row block of padding; 8 bytes of tile list per marker are more than the band ever needs per group

@@ -15,7 +15,8 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
 void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
                         int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
                         double th_het, float n_uniform, int *work_counter, int *work_counter_small,
-                        int *work_counter_mid, int world);
+                        int *work_counter_mid, int world, int sm_count);
+unsigned ci_classes_possible(int l, int maxdeg);
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
                     u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
                     CiItem *items, CiItem *items_small, CiItem *items_mid, int item_cap);
@@ -29,6 +30,7 @@ void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx,
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
 int launch_ci_small(cudaStream_t st, bool het, const CiParams &p);
 int launch_ci_mid(cudaStream_t st, bool het, const CiParams &p);
+int launch_ci_dfs(cudaStream_t st, bool het, const CiParams &p, bool wide);
 void launch_and_reduce(cudaStream_t st, const uint32_t *gathered, int world, size_t words, uint32_t *bits);
 void launch_apply_removed(cudaStream_t st, const unsigned char *flags, int world, size_t stride, int n, int rw,
                           const int *rowptr, const int *deg, const int *adj, uint32_t *bits);
@@ -79,15 +81,16 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     int *d_itemstart = (int *)arena_take(ctx, sizeof(int) * ((size_t)n + 1));
     u64 *d_chunk = (u64 *)arena_take(ctx, sizeof(u64) * (size_t)n);
     LevelCtl *d_ctl = (LevelCtl *)arena_take(ctx, sizeof(LevelCtl) * (CUSK_ML + 2));
-    int *d_work = (int *)arena_take(ctx, sizeof(int) * 3 * (CUSK_ML + 2));  // queues of the three CI kernels
+    int *d_work = (int *)arena_take(ctx, sizeof(int) * 4 * (CUSK_ML + 2));  // queues of the CI kernels, one per level
     int *d_work_small = d_work ? d_work + (CUSK_ML + 2) : nullptr;
     int *d_work_mid = d_work ? d_work + 2 * (CUSK_ML + 2) : nullptr;
+    int *d_work_dfs2 = d_work ? d_work + 3 * (CUSK_ML + 2) : nullptr;
     unsigned long long *d_sepcount = (unsigned long long *)arena_take(ctx, sizeof(unsigned long long));
     int *d_minmax = (int *)arena_take(ctx, 2 * sizeof(int));
     if (!d_deg || !d_rowptr || !d_itemstart || !d_chunk || !d_ctl || !d_work || !d_sepcount || !d_minmax)
         return CUSK_E_CUDA;
     CUSK_CUDA(cudaMemsetAsync(d_ctl, 0, sizeof(LevelCtl) * (CUSK_ML + 2), st));
-    CUSK_CUDA(cudaMemsetAsync(d_work, 0, sizeof(int) * 3 * (CUSK_ML + 2), st));
+    CUSK_CUDA(cudaMemsetAsync(d_work, 0, sizeof(int) * 4 * (CUSK_ML + 2), st));
     CUSK_CUDA(cudaMemsetAsync(d_sepcount, 0, sizeof(unsigned long long), st));
 
     // het engine: uniform effective sample sizes take the constant-threshold fast path
@@ -122,8 +125,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         sh->exchange_ms = 0.0;
         sh->exchange_bytes = 0;
     }
-    // plan_kernel aims at up to 148 * CI_SMALL_IPSM_MAX * world items per level, plus at most one short item per row
-    const int item_cap = n + 148 * CI_SMALL_IPSM_MAX * ((sh ? sh->world : 1) + 1);
+    // plan_kernel aims at up to sm_count * CI_SMALL_IPSM_MAX * world items per level, plus at most one short item per row
+    const int item_cap = n + ctx->sm_count * CI_SMALL_IPSM_MAX * ((sh ? sh->world : 1) + 1);
     CiItem *d_items = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
     CiItem *d_items_small = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
     CiItem *d_items_mid = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
@@ -154,19 +157,28 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     const int grid = ctx->sm_count;
     const int smem_bytes = ctx->max_smem_optin - 1024;  // leave room for static shared memory
 
+    // Upper bound of every row's degree from the level it was read at (degrees only fall): decides which CI kernels a
+    // level can need at all, and ends the loop at the first level no row can reach (src/cuPC-S.cu:154-159).
+    int maxdeg_bound = 2147483647;
+    int l_stop = maxl + 1;  // first level whose kernels were not launched
     for (int l = 1; l <= maxl; l++) {
+        if (maxdeg_bound - 1 < l) {
+            l_stop = l;
+            break;
+        }
         CUSK_CUDA(cudaEventRecord(ev[l], st));
         LevelCtl *ctl = d_ctl + l;
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
         launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
                            a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l, d_work_small + l,
-                           d_work_mid + l, sh ? sh->world : 1);
+                           d_work_mid + l, sh ? sh->world : 1, ctx->sm_count);
         if (l == 1) {
             // the only mid-call synchronisation: directed edge count after level 0
             LevelCtl h;
             CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
             CUSK_CUDA(cudaStreamSynchronize(st));
             const size_t nnz = (size_t)h.nnz;
+            maxdeg_bound = h.maxdeg;
 
             d_adj = (int *)arena_take(ctx, sizeof(int) * std::max<size_t>(nnz, 1));
             if (!d_adj) return CUSK_E_CUDA;
@@ -192,13 +204,30 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             LevelCtl h;
             CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
             CUSK_CUDA(cudaStreamSynchronize(st));
-            if (h.done) break;
+            if (h.done) {
+                l_stop = l;
+                break;
+            }
+            maxdeg_bound = h.maxdeg;
             nnz_l = (size_t)h.nnz;
             // a level with few tests is cheaper run whole by every rank (same result everywhere, no exchange)
             // than dealt out and exchanged: an exchange costs a stream synchronisation plus the collective's latency
             shard_level = (h.acc_tests + h.acc_small + h.acc_mid) >= shard_min_tests;
             if (shard_level && d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, (nnz_l + 15) & ~(size_t)15, st));
         }
+        if (!sh && l == CI_DFS_LMIN && maxdeg_bound > CI_DFS_LMIN) {
+            // one more look at the plan: after level 2 most rows are short, and the bound read here lets the remaining
+            // levels launch only the kernels some row can need (and stop at the first level none can reach)
+            LevelCtl h;
+            CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
+            CUSK_CUDA(cudaStreamSynchronize(st));
+            if (h.done) {
+                l_stop = l;
+                break;
+            }
+            maxdeg_bound = h.maxdeg;
+        }
+        const unsigned classes = ci_classes_possible(l, maxdeg_bound);
         launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
                        d_items_small, d_items_mid, item_cap);
         CiParams p;
@@ -216,6 +245,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.work_counter = d_work + l;
         p.work_counter_small = d_work_small + l;
         p.work_counter_mid = d_work_mid + l;
+        p.work_counter_dfs2 = d_work_dfs2 + l;
+        p.sm_count = ctx->sm_count;
         p.minkey = d_minkey;
         p.th_het = (double)a.th_het;
         p.smem_bytes = smem_bytes;
@@ -227,12 +258,18 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.shard_rank = shard_level ? sh->rank : 0;
         p.shard_world = shard_level ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
-        int rc = launch_ci_level(st, a.het, p, grid);
+        int rc = CUSK_OK;
+        if (classes & 1u) rc = launch_ci_level(st, a.het, p, grid);  // hub rows
         if (rc) return rc;
-        rc = launch_ci_small(st, a.het, p);  // the level's short rows (thread per conditioning set)
+        if (classes & 2u) rc = launch_ci_small(st, a.het, p);  // the level's short rows (thread per conditioning set)
         if (rc) return rc;
-        if (l <= CI_MID_LMAX) {
-            rc = launch_ci_mid(st, a.het, p);  // levels 1-2: the medium rows
+        if ((classes & 4u) && l <= CI_MID_LMAX) rc = launch_ci_mid(st, a.het, p);  // levels 1-2: the medium rows
+        if (rc) return rc;
+        if ((classes & 4u) && l > CI_MID_LMAX) {
+            // deeper levels: rows of up to 63 neighbours whose sets serve many tests (lanes over the neighbours);
+            // narrow (<= 31) and wide rows share the item table, each kernel skips the other's
+            rc = launch_ci_dfs(st, a.het, p, false);
+            if (!rc && (classes & 256u)) rc = launch_ci_dfs(st, a.het, p, true);
             if (rc) return rc;
         }
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
@@ -267,9 +304,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     // final degrees (edge count) and pMax post-processing
     launch_degree_plan(st, a.dbits, n, rw, d_deg, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1,
                        nullptr, 1.0, 1.0, n_uniform, d_work + CUSK_ML + 1, d_work_small + CUSK_ML + 1,
-                       d_work_mid + CUSK_ML + 1, 1);
+                       d_work_mid + CUSK_ML + 1, 1, ctx->sm_count);
     if (!a.het && a.d_pMax) launch_pmax_final(st, a.dbits, n, rw, a.d_pMax);
-    CUSK_CUDA(cudaEventRecord(ev[maxl + 1], st));
+    const int l_end = std::min(l_stop, maxl + 1);  // event slot that closes the last launched level
+    CUSK_CUDA(cudaEventRecord(ev[l_end], st));
     CUSK_CUDA(cudaGetLastError());
 
     // ---- read back the control blocks --------------------------------------------------------
@@ -285,8 +323,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     int levels_run = 1;
     int infeasible = 0;
     for (int l = 1; l <= maxl; l++) {
-        if (h_ctl[l].infeasible) infeasible = std::max(infeasible, h_ctl[l].infeasible);
-        if (h_ctl[l].done) {
+        if (l < l_stop && h_ctl[l].infeasible) infeasible = std::max(infeasible, h_ctl[l].infeasible);
+        if (l >= l_stop || h_ctl[l].done) {
             last = l - 1;
             break;
         }
@@ -300,16 +338,16 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         stats->tests_canonical[0] = stats->tests_executed[0] = (int64_t)n * (n - 1) / 2;
         stats->edges_after[0] = (int64_t)(h_ctl[1].nnz / 2);
         for (int l = 1; l <= maxl; l++) {
-            if (h_ctl[l].done) break;
+            if (l >= l_stop || h_ctl[l].done) break;
             stats->tests_canonical[l] = (int64_t)h_ctl[l].canon;
             stats->tests_executed[l] = (int64_t)h_ctl[l].executed;
             stats->max_degree[l] = h_ctl[l].maxdeg;
             stats->singular_pivots += (int64_t)h_ctl[l].singular;
             // plan(l+1) ran (level l was not "done") and recorded nnz before deciding about l+1
-            stats->edges_after[l] = (int64_t)(((l < maxl) ? h_ctl[l + 1].nnz : h_ctl[CUSK_ML + 1].nnz) / 2);
+            stats->edges_after[l] = (int64_t)(((l + 1 < l_stop && l < maxl) ? h_ctl[l + 1].nnz : h_ctl[CUSK_ML + 1].nnz) / 2);
         }
         if (maxl == 0) stats->edges_after[0] = (int64_t)(h_ctl[CUSK_ML + 1].nnz / 2);
-        for (int l = 0; l <= maxl; l++) {
+        for (int l = 0; l < l_end; l++) {
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, ev[l], ev[l + 1]) == cudaSuccess) stats->level_ms[l] = ms;
             if (l >= 1 && !h_ctl[l].done &&
@@ -317,7 +355,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
                 stats->ci_kernel_ms[l] = ms;
         }
         float tot = 0.f;
-        if (cudaEventElapsedTime(&tot, ev[0], ev[maxl + 1]) == cudaSuccess) stats->total_ms = tot;
+        if (cudaEventElapsedTime(&tot, ev[0], ev[l_end]) == cudaSuccess) stats->total_ms = tot;
         stats->last_level = last;
         stats->levels_run = levels_run;
     }

@@ -12,6 +12,8 @@
 #define CI_MID_DMAX 160         // ci_mid.cu: level 2, rows with CI_SMALL_DMAX < degree <= this (CTA per item)
 #define CI_MID_DMAX1 1024       // ... level 1 (nothing staged, so only the row's index arrays bound it)
 #define CI_MID_LMAX 2
+#define CI_DFS_DMAX 63          // ci_dfs.cu: levels above CI_MID_LMAX, rows up to this degree whose sets serve enough tests
+#define CI_DFS_LMIN (CI_MID_LMAX + 1)
 #define CI_SMALL_IPSM_MAX 64    // upper bound of its items per SM (sizes the decoded item table)
 #define CI_MAX_COMB ((u64)1 << 48)  // per-row conditioning-set count above which a level is infeasible
 
@@ -28,7 +30,7 @@ struct LevelCtl {
     u64 singular;    // dropped pivots
     double T2;       // tanh(threshold)^2 of the level (non-het and uniform-N het)
     int nitems_small;  // work items of the thread-per-set kernel (rows with degree <= CI_SMALL_DMAX)
-    int nitems_mid;    // work items of ci_mid_kernel (levels 1-2, medium rows)
+    int nitems_mid;    // work items of ci_mid_kernel (levels 1-2, medium rows) / ci_dfs_kernel (levels >= 3)
     // accumulators of degree_plan_kernel's row phase (zero at the start of a call)
     u64 acc_tests, acc_small, acc_canon;
     int acc_maxdeg, acc_infeasible;
@@ -55,7 +57,8 @@ struct CiParams {
     LevelCtl *ctl;
     int *work_counter;
     int *work_counter_small;  // queue of ci_small_kernel
-    int *work_counter_mid;    // queue of ci_mid_kernel
+    int *work_counter_mid;    // queue of ci_mid_kernel (levels 1-2) / of ci_dfs_kernel<NS = 1> (levels >= 3)
+    int *work_counter_dfs2;   // queue of ci_dfs_kernel<NS = 2>: the same item table, each kernel skips the other's rows
     u64 *minkey;             // non-het
     double th_het;
     int smem_bytes;
@@ -65,4 +68,23 @@ struct CiParams {
     int item_cap;               // capacity of either table (plan_kernel keeps the counts below it)
     unsigned char *removed;       // edge-sharded het engine: removed[slot of (X,Y) in the level's CSR] = 1
     int shard_rank, shard_world;  // this launch takes items rank, rank + world, ... (1 GPU: 0, 1)
+    int sm_count;                 // persistent grids: CTAs per SM (occupancy) x this
 };
+
+struct DfsTuning {
+    int span, dmin, ipsm;
+};
+DfsTuning dfs_tuning();  // skeleton_kernels.cu
+
+// Which CI kernel takes a row of degree d at level l (degree_plan_kernel and its host-side mirror in skeleton.cu):
+// 0 ci_level_kernel, 1 ci_small_kernel, 2 ci_mid_kernel (l <= 2) / ci_dfs_kernel (l >= 3).
+//   dsmall: CI_SMALL_DMAX or 0 (kernel off); dmid: level-1/2 bound of ci_mid or 0; dfs_span > 0: rows with
+//   dfs_dmin <= d <= CI_DFS_DMAX and d - l >= dfs_span go to ci_dfs at l >= CI_DFS_LMIN (every set then serves at
+//   least dfs_span tests, which is what the lanes-over-neighbours mapping needs to beat a thread per set)
+__host__ __device__ inline int ci_row_class(int d, int l, int dsmall, int dmid, int dfs_span, int dfs_dmin)
+{
+    if (l >= CI_DFS_LMIN && dfs_span > 0 && d <= CI_DFS_DMAX && d >= dfs_dmin && d - l >= dfs_span) return 2;
+    if (d <= dsmall) return 1;
+    if (l <= CI_MID_LMAX && d <= dmid) return 2;
+    return 0;
+}

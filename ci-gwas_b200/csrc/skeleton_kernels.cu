@@ -224,7 +224,8 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                                                            LevelCtl *ctl, const LevelCtl *prev, double th_level,
                                                            double th_het, float n_uniform, int *work_counter,
                                                            int *work_counter_small, int *work_counter_mid, int world,
-                                                           int ipsm_shallow, int ipsm_deep, int ipsm_small, int ipsm_mid)
+                                                           int ipsm_shallow, int ipsm_deep, int ipsm_small, int ipsm_mid,
+                                                           int dfs_span, int dfs_dmin, int ipsm_dfs, int sm_count)
 {
     __shared__ u64 s_warp2[66];
     __shared__ u64 s_acc[4];
@@ -267,9 +268,11 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                     atomicAdd((unsigned long long *)&s_acc[2], (unsigned long long)canon);
                     if (cb >= CI_MAX_COMB)
                         atomicExch(&s_infeasible, 1);
-                    else
-                        atomicAdd((unsigned long long *)&s_acc[d <= dsmall ? 1 : (d <= dmid ? 3 : 0)],
+                    else {
+                        const int rc = ci_row_class(d, l, dsmall, dmid, dfs_span, dfs_dmin);
+                        atomicAdd((unsigned long long *)&s_acc[rc == 1 ? 1 : (rc == 2 ? 3 : 0)],
                                   (unsigned long long)(cb * (u64)(d - l)));
+                    }
                 }
                 chunk[r] = cb;  // C(d, l) for the plan phase, which replaces it by the row's chunk size
                 atomicMax(&s_maxdeg, d);
@@ -304,15 +307,16 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         // factorisation, which consecutive conditioning sets share, so few large items win (sweep on the
         // C2 block: profiles/r1_item_floor_sweep.txt).
         const u64 per_sm = (u64)(l <= 2 ? ipsm_shallow : ipsm_deep);
-        u64 target = tot_tests / ((u64)148 * per_sm * (u64)world);
+        u64 target = tot_tests / ((u64)sm_count * per_sm * (u64)world);
         if (target < 32) target = 32;
         s_target = target;
         // ci_small_kernel: a warp per item, a lane per rank, so many items of >= 32 ranks
-        u64 ts = tot_small / ((u64)148 * (u64)(ipsm_small > 0 ? ipsm_small : 1) * (u64)world);
+        u64 ts = tot_small / ((u64)sm_count * (u64)(ipsm_small > 0 ? ipsm_small : 1) * (u64)world);
         if (ts < 32) ts = 32;
         s_target_small = ts;
-        // ci_mid_kernel: a CTA per item
-        u64 tm = tot_mid / ((u64)148 * (u64)(ipsm_mid > 0 ? ipsm_mid : 1) * (u64)world);
+        // ci_mid_kernel (levels 1-2) / ci_dfs_kernel (levels >= 3): a CTA per item
+        const int ipsm2 = (l <= CI_MID_LMAX) ? ipsm_mid : ipsm_dfs;
+        u64 tm = tot_mid / ((u64)sm_count * (u64)(ipsm2 > 0 ? ipsm2 : 1) * (u64)world);
         if (tm < 32) tm = 32;
         s_target_mid = tm;
     }
@@ -336,7 +340,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
             c_next = (rn < n) ? __ldcg(&chunk[rn]) : 0;
         }
         u64 items = 0;
-        const int cls = (d <= dsmall) ? 1 : ((d <= dmid) ? 2 : 0);
+        const int cls = ci_row_class(d, l, dsmall, dmid, dfs_span, dfs_dmin);
         if (runs && r < n && d > l) {
             const u64 tests = c * (u64)(d - l);
             u64 tgt = (cls == 1) ? target_small : ((cls == 2) ? target_mid : target);
@@ -350,9 +354,15 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
             if (items < 1) items = 1;
             u64 ch = ceil_div_u64(c, items);
             if (cls == 1 && ch < 32) ch = (c < 32) ? c : 32;  // a lane per rank
-            if (cls == 2) {
+            if (cls == 2 && l <= CI_MID_LMAX) {
                 // a thread per (rank, 32-neighbour chunk): at least a CTA's worth of them per item
                 const u64 minr = (u64)((256 + ((d + 31) >> 5) - 1) / ((d + 31) >> 5));
+                if (ch < minr) ch = (c < minr) ? c : minr;
+            }
+            if (cls == 2 && l > CI_MID_LMAX) {
+                // ci_dfs stages (d + 1)^2 correlations per item and gives each of its 4 warps a rank sub-range:
+                // at least ~4 tests per staged entry
+                const u64 minr = ceil_div_u64(4 * (u64)(d + 1) * (u64)(d + 1), (u64)(d - l));
                 if (ch < minr) ch = (c < minr) ? c : minr;
             }
             items = ceil_div_u64(c, ch);
@@ -629,42 +639,84 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
         level0_kernel<false><<<grid, 256, 0, st>>>(C, N, n_uniform, G_in, n, rw, th, bits, pMax);
 }
 
+// ci_dfs.cu routing knobs, read on every call (tests switch them between calls of one process):
+//   CUSK_DFS=0 switches the kernel off; CUSK_DFS_MIN_SPAN: least d - l (default 8); CUSK_DFS_MIN_D: least degree
+//   (default 12); CUSK_ITEMS_PER_SM_DFS: work items per SM the plan aims at (default 48)
+DfsTuning dfs_tuning()
+{
+    DfsTuning t;
+    const char *off = getenv("CUSK_DFS");
+    const char *sp = getenv("CUSK_DFS_MIN_SPAN");
+    const char *dm = getenv("CUSK_DFS_MIN_D");
+    const char *ip = getenv("CUSK_ITEMS_PER_SM_DFS");
+    t.span = (off && atoi(off) == 0) ? 0 : (sp && atoi(sp) > 0 ? atoi(sp) : 8);
+    t.dmin = (dm && atoi(dm) > 0) ? atoi(dm) : 12;
+    const int v = ip ? atoi(ip) : 0;
+    t.ipsm = v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 48;
+    return t;
+}
+
+namespace {
+struct PlanKnobs {
+    int ipsm_shallow, ipsm_deep, ipsm_small, ipsm_mid;
+};
+int env_pos(const char *name, int dflt)
+{
+    const char *e = getenv(name);
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : dflt;
+}
+// tuning knobs, read once: work items per SM of ci_level_kernel at levels 1-2 (SHALLOW) and from level 3 on (DEEP),
+// of the thread-per-set kernel (ci_small.cu; CUSK_SMALL_KERNEL=0 switches it off) and of the level-1/2 kernel for
+// medium rows (ci_mid.cu; CUSK_MID_KERNEL=0 switches it off)
+const PlanKnobs &plan_knobs()
+{
+    static const PlanKnobs k = [] {
+        PlanKnobs q;
+        q.ipsm_shallow = env_pos("CUSK_ITEMS_PER_SM_SHALLOW", 8);
+        q.ipsm_deep = env_pos("CUSK_ITEMS_PER_SM_DEEP", 2);
+        const char *off = getenv("CUSK_SMALL_KERNEL");
+        q.ipsm_small = (off && atoi(off) == 0) ? 0 : std::min(env_pos("CUSK_ITEMS_PER_SM_SMALL", 32), CI_SMALL_IPSM_MAX);
+        off = getenv("CUSK_MID_KERNEL");
+        q.ipsm_mid = (off && atoi(off) == 0) ? 0 : std::min(env_pos("CUSK_ITEMS_PER_SM_MID", 4), CI_SMALL_IPSM_MAX);
+        return q;
+    }();
+    return k;
+}
+}  // namespace
+
+// Host-side mirror of the plan's routing: which CI kernels can get a row at level l when no row has more than
+// maxdeg neighbours (bit c = class c of ci_row_class; bit 8 = a class-2 row with 32 or more neighbours, i.e.
+// ci_dfs_kernel<NS = 2>).  Degrees only fall from level to level, so the maximum read at one level bounds the later ones.
+unsigned ci_classes_possible(int l, int maxdeg)
+{
+    const PlanKnobs &k = plan_knobs();
+    const DfsTuning dt = dfs_tuning();
+    const int dsmall = (k.ipsm_small > 0 && l <= CI_SMALL_LMAX) ? CI_SMALL_DMAX : 0;
+    const int dmid = (k.ipsm_mid > 0 && l <= CI_MID_LMAX) ? (l == 1 ? CI_MID_DMAX1 : CI_MID_DMAX) : 0;
+    unsigned mask = 0;
+    const int top = std::max(CI_DFS_DMAX, std::max(dsmall, dmid)) + 1;  // every larger degree is class 0
+    if (maxdeg > top) mask |= 1u;
+    for (int d = l + 1; d <= std::min(maxdeg, top); d++) {
+        const int c = ci_row_class(d, l, dsmall, dmid, dt.span, dt.dmin);
+        mask |= 1u << c;
+        if (c == 2 && l > CI_MID_LMAX && d >= 32) mask |= 1u << 8;
+    }
+    return mask;
+}
+
 void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
                         int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
                         double th_het, float n_uniform, int *work_counter, int *work_counter_small,
-                        int *work_counter_mid, int world)
+                        int *work_counter_mid, int world, int sm_count)
 {
-    // tuning knobs: work items per SM of ci_level_kernel at levels 1-2 and at levels >= 3
-    static const int ipsm_shallow = [] {
-        const char *e = getenv("CUSK_ITEMS_PER_SM_SHALLOW");
-        const int v = e ? atoi(e) : 0;
-        return v > 0 ? v : 8;
-    }();
-    static const int ipsm_deep = [] {
-        const char *e = getenv("CUSK_ITEMS_PER_SM_DEEP");
-        const int v = e ? atoi(e) : 0;
-        return v > 0 ? v : 2;
-    }();
-    // items per SM of the thread-per-set kernel (ci_small.cu); CUSK_SMALL_KERNEL=0 switches it off
-    static const int ipsm_small = [] {
-        const char *off = getenv("CUSK_SMALL_KERNEL");
-        if (off && atoi(off) == 0) return 0;
-        const char *e = getenv("CUSK_ITEMS_PER_SM_SMALL");
-        const int v = e ? atoi(e) : 0;
-        return v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 32;
-    }();
-    // items per SM of the level-1/2 kernel for medium rows (ci_mid.cu); CUSK_MID_KERNEL=0 switches it off
-    static const int ipsm_mid = [] {
-        const char *off = getenv("CUSK_MID_KERNEL");
-        if (off && atoi(off) == 0) return 0;
-        const char *e = getenv("CUSK_ITEMS_PER_SM_MID");
-        const int v = e ? atoi(e) : 0;
-        return v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 4;
-    }();
+    const PlanKnobs &k = plan_knobs();
+    const DfsTuning dt = dfs_tuning();
     degree_plan_kernel<<<(n + 31) / 32, 1024, 0, st>>>(bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl, prev,
                                                        th_level, th_het, n_uniform, work_counter,
-                                                       work_counter_small, work_counter_mid, world, ipsm_shallow,
-                                                       ipsm_deep, ipsm_small, ipsm_mid);
+                                                       work_counter_small, work_counter_mid, world, k.ipsm_shallow,
+                                                       k.ipsm_deep, k.ipsm_small, k.ipsm_mid, dt.span, dt.dmin, dt.ipsm,
+                                                       sm_count > 0 ? sm_count : 148);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,

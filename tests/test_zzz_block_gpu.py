@@ -132,15 +132,13 @@ def test_banded_chunked_equals_whole(ctx):
         ctx.mcorrk_banded(bed, m, n, m)
 
 
-@pytest.mark.skipif(os.environ.get("CUSK_TEST_BLOCK_TC") != "1",
-                    reason="tensor-core route of the banded correlations: written without GPU time, opt in with "
-                           "CUSK_TEST_BLOCK_TC=1 (scripts/r2_first_gpu_call.sh does)")
 @pytest.mark.parametrize("m,n,w,miss,mem_markers", [
     (7, 100, 3, 0.0, 0), (130, 4097, 64, 0.0, 0), (300, 1500, 20, 0.02, 0), (97, 777, 96, 0.0, 0),
     (700, 5000, 150, 0.0, 0), (700, 5000, 150, 0.01, 0), (900, 3000, 40, 0.005, 200),
 ])
 def test_banded_tensor_core_route_equals_default(ctx, oracle, m, n, w, miss, mem_markers):
-    """CUSK_BLOCK_TC=1 (tcgen05 indicator Gram over the band's tiles) against the default AND + POPC route: both
+    """CUSK_BLOCK_TC=1 (tcgen05 indicator Gram over the band's tiles, the default from 512 markers on) against
+    CUSK_BLOCK_TC=0 (AND + POPC bit planes): both
     build the same exact integer tables and evaluate the same FP64 expression -> the same floats"""
     rng = np.random.default_rng(m + n + w)
     bed = random_bed(rng, m, n, miss_rate=miss, miss_markers={3, m // 2} if miss else None)
@@ -149,9 +147,10 @@ def test_banded_tensor_core_route_equals_default(ctx, oracle, m, n, w, miss, mem
         kp = (n + 127) // 128 * 128
         per_marker = (n + 3) // 4 + (128 * kp + 41) // 42 + 16 + 8 * (w // 84 + 4) + 4 * w + 4
         kw["device_mem_gb"] = (per_marker * mem_markers + 384 * kp) / 1e9
-    base = ctx.mcorrk_banded(bed, m, n, w)
-    os.environ["CUSK_BLOCK_TC"] = "1"
+    os.environ["CUSK_BLOCK_TC"] = "0"
     try:
+        base = ctx.mcorrk_banded(bed, m, n, w)
+        os.environ["CUSK_BLOCK_TC"] = "1"
         tc = check_against_oracle(ctx, oracle, bed, m, n, w, **kw)
     finally:
         del os.environ["CUSK_BLOCK_TC"]
