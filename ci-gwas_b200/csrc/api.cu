@@ -1,6 +1,8 @@
 // api.cu -- host-buffer entry points and the reference's own signatures (drop-in boundary).
 #include <algorithm>
+#include <atomic>
 #include <mutex>
+#include <thread>
 
 #include "engine.h"
 
@@ -24,6 +26,119 @@ struct Timer {
 };
 }  // namespace
 
+// ---- host-side helpers of the host-buffer entry points -----------------------------------------------------------
+// The reference moves every matrix over PCIe in both directions (src/hetcor-cuPC-S.cu:99-131, :322-329): C, N and G
+// in, G out, 4 n^2 bytes each.  Here, while C is on its way to the device, the host's cores look at the other two:
+// a candidate matrix that is all ones and a sample-size matrix that is one constant (what `mps cuskss` passes for a
+// first stage without standard errors) are recognised and not uploaded, and the adjacency comes back as the bitmap
+// (n^2 / 8 bytes) and is expanded into the caller's int matrix by the host threads.  cusk_stats.h2d_bytes / d2h_bytes
+// report what was actually moved.
+namespace {
+
+int host_threads()
+{
+    static const int t = [] {
+        const char *e = getenv("CUSK_HOST_THREADS");
+        int v = e ? atoi(e) : 0;
+        if (v <= 0) {
+            v = (int)std::thread::hardware_concurrency();
+            if (v > 16) v = 16;
+        }
+        return v < 1 ? 1 : v;
+    }();
+    return t;
+}
+
+// fn(chunk_begin, chunk_end) over [0, total) on the host's threads (std::thread: torchrun exports OMP_NUM_THREADS=1)
+template <class F>
+void parallel_chunks(size_t total, size_t grain, F fn)
+{
+    const size_t nchunks = (total + grain - 1) / grain;
+    const int T = (int)std::min<size_t>((size_t)host_threads(), nchunks);
+    if (T <= 1) {
+        for (size_t c = 0; c < nchunks; c++) fn(c * grain, std::min(total, (c + 1) * grain));
+        return;
+    }
+    std::atomic<size_t> next{0};
+    std::vector<std::thread> th;
+    auto work = [&] {
+        for (;;) {
+            const size_t c = next.fetch_add(1);
+            if (c >= nchunks) break;
+            fn(c * grain, std::min(total, (c + 1) * grain));
+        }
+    };
+    for (int t = 1; t < T; t++) th.emplace_back(work);
+    work();
+    for (auto &x : th) x.join();
+}
+
+bool host_all_ones(const int *G, size_t nn)
+{
+    std::atomic<bool> ok{true};
+    parallel_chunks(nn, (size_t)1 << 18, [&](size_t a, size_t b) {
+        if (!ok.load(std::memory_order_relaxed)) return;
+        int acc = 1;
+        for (size_t i = a; i < b; i++) acc &= (G[i] == 1);
+        if (!acc) ok.store(false, std::memory_order_relaxed);
+    });
+    return ok.load();
+}
+
+// every off-diagonal entry holds the same non-negative, non-NaN value (the test ess_minmax_kernel makes on the device)
+bool host_constant_offdiag(const float *N, int n, float *value)
+{
+    if (n < 2) return false;
+    uint32_t ref;
+    memcpy(&ref, &N[1], 4);
+    if (!(N[1] >= 0.f)) return false;
+    std::atomic<bool> ok{true};
+    parallel_chunks((size_t)n, 64, [&](size_t r0, size_t r1) {
+        if (!ok.load(std::memory_order_relaxed)) return;
+        for (size_t r = r0; r < r1; r++) {
+            const uint32_t *row = (const uint32_t *)(N + r * (size_t)n);
+            uint32_t diff = 0;
+            for (size_t c = 0; c < (size_t)n; c++) diff |= (c == r) ? 0u : (row[c] ^ ref);
+            if (diff) {
+                ok.store(false, std::memory_order_relaxed);
+                return;
+            }
+        }
+    });
+    if (ok.load()) *value = N[1];
+    return ok.load();
+}
+
+void host_expand_bits(const uint32_t *bits, int n, int rw, int *G)
+{
+    parallel_chunks((size_t)n, 32, [&](size_t r0, size_t r1) {
+        for (size_t r = r0; r < r1; r++) {
+            const uint32_t *row = bits + r * (size_t)rw;
+            int *out = G + r * (size_t)n;
+            for (int w = 0; w < rw; w++) {
+                const uint32_t word = row[w];
+                const int c0 = w * 32, c1 = std::min(n, c0 + 32);
+                for (int c = c0; c < c1; c++) out[c] = (int)((word >> (c - c0)) & 1u);
+            }
+        }
+    });
+}
+
+// device bitmap -> the caller's dense int matrix (pinned staging, host expansion)
+int fetch_adjacency(cusk_ctx *ctx, const uint32_t *dbits, int n, int rw, int *G, int64_t *bytes)
+{
+    const size_t nb = (size_t)n * rw * 4;
+    uint32_t *h = (uint32_t *)host_stage(ctx, nb);
+    if (!h) return CUSK_E_CUDA;
+    CUSK_CUDA(cudaMemcpyAsync(h, dbits, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    CUSK_CUDA(cudaStreamSynchronize(ctx->stream));
+    host_expand_bits(h, n, rw, G);
+    *bytes += (int64_t)nb;
+    return CUSK_OK;
+}
+
+}  // namespace
+
 extern "C" int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const float *Th, int maxlevel,
                              int *l_out, float *pMax, int *SepSet, cusk_sepset *sep, int64_t sep_cap,
                              int64_t *sep_n, cusk_stats *stats)
@@ -39,9 +154,8 @@ extern "C" int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const
     arena_reset(ctx->io);
     float *dC = (float *)arena_take(ctx->io, nn * 4);
     uint32_t *dbits = (uint32_t *)arena_take(ctx->io, (size_t)n * rw * 4);
-    int *dG = (int *)arena_take(ctx->io, nn * 4);
     float *dP = pMax ? (float *)arena_take(ctx->io, nn * 4) : nullptr;
-    if (!dC || !dbits || !dG || (pMax && !dP)) return CUSK_E_CUDA;
+    if (!dC || !dbits || (pMax && !dP)) return CUSK_E_CUDA;
     Timer th2d(ctx, 0), td2h(ctx, 1);
     th2d.start();
     CUSK_CUDA(cudaMemcpyAsync(dC, C, nn * 4, cudaMemcpyHostToDevice, st));
@@ -52,12 +166,15 @@ extern "C" int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const
     const bool want_seps = SepSet || sep || sep_n;
     int rc = skeleton_engine(ctx, dC, n, dbits, Th, maxlevel, l_out, dP, want_seps ? &seps : nullptr, sp);
     if (rc) return rc;
+    int64_t down = (int64_t)(seps.size() * sizeof(cusk_sepset));
     td2h.start();
-    launch_expand_bits(st, dbits, n, rw, dG);
-    CUSK_CUDA(cudaMemcpyAsync(G, dG, nn * 4, cudaMemcpyDeviceToHost, st));
-    if (pMax) CUSK_CUDA(cudaMemcpyAsync(pMax, dP, nn * 4, cudaMemcpyDeviceToHost, st));
+    if (pMax) {
+        CUSK_CUDA(cudaMemcpyAsync(pMax, dP, nn * 4, cudaMemcpyDeviceToHost, st));
+        down += (int64_t)(nn * 4);
+    }
+    rc = fetch_adjacency(ctx, dbits, n, rw, G, &down);
+    if (rc) return rc;
     td2h.stop();
-    CUSK_CUDA(cudaStreamSynchronize(st));
     if (sep_n) *sep_n = (int64_t)seps.size();
     if (sep && sep_cap > 0)
         memcpy(sep, seps.data(), std::min<size_t>(seps.size(), (size_t)sep_cap) * sizeof(cusk_sepset));
@@ -71,6 +188,8 @@ extern "C" int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const
     }
     sp->h2d_ms = th2d.ms();
     sp->d2h_ms = td2h.ms();
+    sp->h2d_bytes = (int64_t)(nn * 4);
+    sp->d2h_bytes = down;
     return CUSK_OK;
 }
 
@@ -93,30 +212,49 @@ extern "C" int cusk_hetcor_skeleton(cusk_ctx *ctx, const float *C, int n, int *G
             if (time_index[i] != time_index[0]) use_time = true;
     arena_reset(ctx->io);
     float *dC = (float *)arena_take(ctx->io, nn * 4);
-    float *dN = (float *)arena_take(ctx->io, nn * 4);
     uint32_t *dbits = (uint32_t *)arena_take(ctx->io, (size_t)n * rw * 4);
-    int *dG = (int *)arena_take(ctx->io, nn * 4);
     int *dT = use_time ? (int *)arena_take(ctx->io, (size_t)n * 4) : nullptr;
-    if (!dC || !dN || !dbits || !dG || (use_time && !dT)) return CUSK_E_CUDA;
+    if (!dC || !dbits || (use_time && !dT)) return CUSK_E_CUDA;
     Timer th2d(ctx, 0), td2h(ctx, 1);
+    int64_t up = (int64_t)(nn * 4);
     th2d.start();
     CUSK_CUDA(cudaMemcpyAsync(dC, C, nn * 4, cudaMemcpyHostToDevice, st));
-    CUSK_CUDA(cudaMemcpyAsync(dN, N, nn * 4, cudaMemcpyHostToDevice, st));
-    if (!G_in_all_ones) CUSK_CUDA(cudaMemcpyAsync(dG, G, nn * 4, cudaMemcpyHostToDevice, st));
-    if (use_time) CUSK_CUDA(cudaMemcpyAsync(dT, time_index, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    if (use_time) {
+        CUSK_CUDA(cudaMemcpyAsync(dT, time_index, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        up += (int64_t)n * 4;
+    }
+    // while C travels (asynchronously when the caller's buffer is page-locked): is G all ones, is N one constant?
+    const bool all_ones = G_in_all_ones || host_all_ones(G, nn);
+    float n_uniform = 0.f;
+    const bool uniform = host_constant_offdiag(N, n, &n_uniform);
+    float *dN = nullptr;
+    int *dG = nullptr;
+    if (!uniform) {
+        dN = (float *)arena_take(ctx->io, nn * 4);
+        if (!dN) return CUSK_E_CUDA;
+        CUSK_CUDA(cudaMemcpyAsync(dN, N, nn * 4, cudaMemcpyHostToDevice, st));
+        up += (int64_t)(nn * 4);
+    }
+    if (!all_ones) {
+        dG = (int *)arena_take(ctx->io, nn * 4);
+        if (!dG) return CUSK_E_CUDA;
+        CUSK_CUDA(cudaMemcpyAsync(dG, G, nn * 4, cudaMemcpyHostToDevice, st));
+        up += (int64_t)(nn * 4);
+    }
     th2d.stop();
     cusk_stats local;
     cusk_stats *sp = stats ? stats : &local;
-    int rc = hetcor_engine(ctx, dC, n, dbits, G_in_all_ones ? nullptr : dG, false, dN, 0.f, th, maxlevel, dT, l_out,
-                           sp);
+    int rc = hetcor_engine(ctx, dC, n, dbits, dG, false, dN, n_uniform, th, maxlevel, dT, l_out, sp);
     if (rc) return rc;
+    int64_t down = 0;
     td2h.start();
-    launch_expand_bits(st, dbits, n, rw, dG);
-    CUSK_CUDA(cudaMemcpyAsync(G, dG, nn * 4, cudaMemcpyDeviceToHost, st));
+    rc = fetch_adjacency(ctx, dbits, n, rw, G, &down);  // bitmap over PCIe, expanded by the host threads
+    if (rc) return rc;
     td2h.stop();
-    CUSK_CUDA(cudaStreamSynchronize(st));
     sp->h2d_ms = th2d.ms();
     sp->d2h_ms = td2h.ms();
+    sp->h2d_bytes = up;
+    sp->d2h_bytes = down;
     return CUSK_OK;
 }
 

@@ -71,6 +71,9 @@ struct cusk_ctx {
     // pinned staging for small control blocks / statistics
     void *h_pinned = nullptr;
     size_t h_pinned_bytes = 0;
+    // pinned, grow-only: the adjacency bitmap on its way back to a host-buffer caller
+    void *h_stage = nullptr;
+    size_t h_stage_bytes = 0;
     // [0, ML+2): level boundaries; [ML+2, 3(ML+2)): CI kernel start/stop per level; last 4: copies
     cudaEvent_t ev[3 * (CUSK_ML + 2) + 4];
     bool ev_ready = false;
@@ -82,6 +85,7 @@ void arena_free(Arena &a);
 inline void arena_reset(cusk_ctx *ctx) { arena_reset(ctx->arena); }
 inline void *arena_take(cusk_ctx *ctx, size_t bytes) { return arena_take(ctx->arena, bytes); }
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+void *host_stage(cusk_ctx *ctx, size_t bytes);  // ctx->h_stage grown to at least `bytes`; nullptr + error on failure
 
 // ---- combinatorics (64-bit, saturating; the reference's BINOM / IthCombination are int32,
 //      src/cuPC-S.cu:6453-6506) --------------------------------------------------------------

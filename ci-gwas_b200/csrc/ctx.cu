@@ -75,6 +75,7 @@ extern "C" void cusk_ctx_destroy(cusk_ctx *ctx)
     arena_free(ctx->arena);
     arena_free(ctx->io);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->ev_ready)
         for (auto &ev : ctx->ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -89,6 +90,23 @@ extern "C" int cusk_ctx_sync(cusk_ctx *ctx)
     CUSK_CUDA(cudaSetDevice(ctx->device));
     CUSK_CUDA(cudaStreamSynchronize(ctx->stream));
     return CUSK_OK;
+}
+
+void *host_stage(cusk_ctx *ctx, size_t bytes)
+{
+    if (bytes <= ctx->h_stage_bytes && ctx->h_stage) return ctx->h_stage;
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    ctx->h_stage = nullptr;
+    ctx->h_stage_bytes = 0;
+    const size_t cap = align_up(bytes, (size_t)1 << 20);
+    const cudaError_t e = cudaMallocHost(&ctx->h_stage, cap);
+    if (e != cudaSuccess) {
+        cusk_set_error("cudaMallocHost(%zu bytes): %s", cap, cudaGetErrorString(e));
+        ctx->h_stage = nullptr;
+        return nullptr;
+    }
+    ctx->h_stage_bytes = cap;
+    return ctx->h_stage;
 }
 
 void arena_reset(Arena &a)

@@ -70,6 +70,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     const int n = a.n;
     const int rw = (int)cusk_row_words(n);
     cudaStream_t st = ctx->stream;
+    int64_t nl = 0;  // kernels launched by this call (counted where they are launched, reported in the statistics)
     const int maxl = std::min(a.maxlevel, CUSK_ML);
     if (n < 1 || a.maxlevel < 0) {
         cusk_set_error("skeleton: invalid n=%d maxlevel=%d", n, a.maxlevel);
@@ -99,7 +100,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     if (a.het && dN) {
         int init[2] = {2147483647, -2147483647 - 1};
         CUSK_CUDA(cudaMemcpyAsync(d_minmax, init, sizeof(init), cudaMemcpyHostToDevice, st));
-        launch_ess_minmax(st, dN, n, d_minmax, d_minmax + 1, ctx->sm_count);
+        nl++, launch_ess_minmax(st, dN, n, d_minmax, d_minmax + 1, ctx->sm_count);
         int mm[2];
         CUSK_CUDA(cudaMemcpyAsync(mm, d_minmax, sizeof(mm), cudaMemcpyDeviceToHost, st));
         CUSK_CUDA(cudaStreamSynchronize(st));
@@ -140,13 +141,13 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         // (only used by the device-resident API; the bitmap is both input and output)
         int *dG_tmp = (int *)arena_take(ctx, sizeof(int) * (size_t)n * n);
         if (!dG_tmp) return CUSK_E_CUDA;
-        launch_expand_bits(st, a.dbits, n, rw, dG_tmp);
-        launch_level0(st, true, a.dC, dN, n_uniform, dG_tmp, n, rw, (double)a.th_het, a.dbits, nullptr);
+        nl++, launch_expand_bits(st, a.dbits, n, rw, dG_tmp);
+        nl++, launch_level0(st, true, a.dC, dN, n_uniform, dG_tmp, n, rw, (double)a.th_het, a.dbits, nullptr);
     } else if (a.het) {
-        launch_level0(st, true, a.dC, dN, n_uniform, a.all_ones ? nullptr : a.dG_in, n, rw, (double)a.th_het,
+        nl++, launch_level0(st, true, a.dC, dN, n_uniform, a.all_ones ? nullptr : a.dG_in, n, rw, (double)a.th_het,
                       a.dbits, nullptr);
     } else {
-        launch_level0(st, false, a.dC, nullptr, 0.f, nullptr, n, rw, (double)a.Th[0], a.dbits, a.d_pMax);
+        nl++, launch_level0(st, false, a.dC, nullptr, 0.f, nullptr, n, rw, (double)a.Th[0], a.dbits, a.d_pMax);
     }
     CUSK_CUDA(cudaGetLastError());
 
@@ -169,7 +170,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         CUSK_CUDA(cudaEventRecord(ev[l], st));
         LevelCtl *ctl = d_ctl + l;
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
-        launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
+        nl++, launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
                            a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l, d_work_small + l,
                            d_work_mid + l, sh ? sh->world : 1, ctx->sm_count);
         if (l == 1) {
@@ -228,7 +229,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             maxdeg_bound = h.maxdeg;
         }
         const unsigned classes = ci_classes_possible(l, maxdeg_bound);
-        launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
+        nl++, launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
                        d_items_small, d_items_mid, item_cap);
         CiParams p;
         p.C = a.dC;
@@ -259,17 +260,17 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.shard_world = shard_level ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = CUSK_OK;
-        if (classes & 1u) rc = launch_ci_level(st, a.het, p, grid);  // hub rows
+        if (classes & 1u) rc = (nl++, launch_ci_level(st, a.het, p, grid));  // hub rows
         if (rc) return rc;
-        if (classes & 2u) rc = launch_ci_small(st, a.het, p);  // the level's short rows (thread per conditioning set)
+        if (classes & 2u) rc = (nl++, launch_ci_small(st, a.het, p));  // the level's short rows (thread per conditioning set)
         if (rc) return rc;
-        if ((classes & 4u) && l <= CI_MID_LMAX) rc = launch_ci_mid(st, a.het, p);  // levels 1-2: the medium rows
+        if ((classes & 4u) && l <= CI_MID_LMAX) rc = (nl++, launch_ci_mid(st, a.het, p));  // levels 1-2: the medium rows
         if (rc) return rc;
         if ((classes & 4u) && l > CI_MID_LMAX) {
             // deeper levels: rows of up to 63 neighbours whose sets serve many tests (lanes over the neighbours);
             // narrow (<= 31) and wide rows share the item table, each kernel skips the other's
-            rc = launch_ci_dfs(st, a.het, p, false);
-            if (!rc && (classes & 256u)) rc = launch_ci_dfs(st, a.het, p, true);
+            rc = (nl++, launch_ci_dfs(st, a.het, p, false));
+            if (!rc && (classes & 256u)) rc = (nl++, launch_ci_dfs(st, a.het, p, true));
             if (rc) return rc;
         }
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
@@ -283,7 +284,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
                 const size_t cnt = (nnz_l + 15) & ~(size_t)15;
                 xrc = sh->allgather(sh->user, d_removed, d_gather, cnt, st);
                 if (!xrc)
-                    launch_apply_removed(st, d_gather, sh->world, cnt, n, rw, d_rowptr, d_deg, d_adj, a.dbits);
+                    nl++, launch_apply_removed(st, d_gather, sh->world, cnt, n, rw, d_rowptr, d_deg, d_adj, a.dbits);
                 sh->exchange_bytes += cnt * (size_t)sh->world;
             } else {
                 xrc = sh->allreduce_min_u64(sh->user, d_minkey, nnz_l, st);
@@ -297,12 +298,12 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             sh->exchange_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         }
         if (!a.het)
-            launch_resolve(st, a.dC, n, rw, l, a.dbits, d_deg, d_rowptr, d_adj, d_minkey, a.d_pMax, d_seps,
+            nl++, launch_resolve(st, a.dC, n, rw, l, a.dbits, d_deg, d_rowptr, d_adj, d_minkey, a.d_pMax, d_seps,
                            d_sepcount, sep_cap, ctl);
         CUSK_CUDA(cudaGetLastError());
     }
     // final degrees (edge count) and pMax post-processing
-    launch_degree_plan(st, a.dbits, n, rw, d_deg, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1,
+    nl++, launch_degree_plan(st, a.dbits, n, rw, d_deg, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1,
                        nullptr, 1.0, 1.0, n_uniform, d_work + CUSK_ML + 1, d_work_small + CUSK_ML + 1,
                        d_work_mid + CUSK_ML + 1, 1, ctx->sm_count);
     if (!a.het && a.d_pMax) launch_pmax_final(st, a.dbits, n, rw, a.d_pMax);
@@ -358,6 +359,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         if (cudaEventElapsedTime(&tot, ev[0], ev[l_end]) == cudaSuccess) stats->total_ms = tot;
         stats->last_level = last;
         stats->levels_run = levels_run;
+        stats->kernel_launches = nl;
     }
     if (infeasible == 1) {
         cusk_set_error("skeleton: a row needs >= 2^48 conditioning sets at some level (degree too large)");

@@ -33,6 +33,9 @@ class Stats(C.Structure):
         ("total_ms", C.c_float),
         ("h2d_ms", C.c_float),
         ("d2h_ms", C.c_float),
+        ("h2d_bytes", C.c_int64),
+        ("d2h_bytes", C.c_int64),
+        ("kernel_launches", C.c_int64),
     ]
 
     def as_dict(self):
@@ -49,6 +52,9 @@ class Stats(C.Structure):
             total_ms=float(self.total_ms),
             h2d_ms=float(self.h2d_ms),
             d2h_ms=float(self.d2h_ms),
+            h2d_bytes=int(self.h2d_bytes),
+            d2h_bytes=int(self.d2h_bytes),
+            kernel_launches=int(self.kernel_launches),
         )
 
 

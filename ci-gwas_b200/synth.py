@@ -190,7 +190,7 @@ def random_bed(n_samples, m, stream=3, missing_rate=0.0, sub_block=50, copy_prob
 
 
 def merged_correlation(loci=400, per_locus=50, p=17, stream=5, num_samples=458000, causal_per_trait=12,
-                       window=12, max_parents=4, wlo=0.6, whi=0.95, dtype=np.float32):
+                       window=12, max_parents=4, wlo=0.6, whi=0.95, dtype=np.float32, beta_lo=0.01, beta_hi=0.05):
     """BASELINE.json configs[4] (cuskss-merged): `loci` independent LD loci of `per_locus` selected markers
     each, followed by p traits.  Same SEM as sem_correlation inside a locus; markers of different loci
     are independent, so the population matrix is assembled locus by locus (no dense nv x nv product).
@@ -221,7 +221,7 @@ def merged_correlation(loci=400, per_locus=50, p=17, stream=5, num_samples=45800
     AT = np.zeros((p, nv), np.float64)
     for t in range(p):
         par = rng.choice(np.arange(m), size=min(causal_per_trait, m), replace=False)
-        w = rng.uniform(0.01, 0.05, size=par.size) * rng.choice([-1.0, 1.0], size=par.size)
+        w = rng.uniform(beta_lo, beta_hi, size=par.size) * rng.choice([-1.0, 1.0], size=par.size)
         row = np.zeros(nv, np.float64)
         for i, wi in zip(par, w):
             L, j = divmod(int(i), per_locus)

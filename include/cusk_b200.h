@@ -52,6 +52,10 @@ typedef struct cusk_stats {
     int32_t levels_run;      /* number of levels that executed CI tests (incl. level 0) */
     float total_ms;          /* device time, level 0 .. last level, excluding copies */
     float h2d_ms, d2h_ms;    /* copy times of the host-buffer entry points */
+    int64_t h2d_bytes, d2h_bytes; /* bytes the host-buffer entry points actually moved over PCIe (an all-ones
+                                     candidate matrix and a constant N are recognised on the host and not uploaded;
+                                     the adjacency comes back as the bitmap and is expanded on the host) */
+    int64_t kernel_launches;      /* kernels the engine launched for this call (counted at the launch sites) */
 } cusk_stats;
 
 /* One separating set of the individual-level engine: slot [x,y] of the reference's dense

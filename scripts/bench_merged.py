@@ -31,6 +31,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--maxlevel", type=int, default=14)
     ap.add_argument("--uniform", action="store_true", help="uniform sample size (plain cuskss-merged, no het)")
+    ap.add_argument("--causal", type=int, default=12, help="causal markers per trait (30+: trait rows keep ~30 neighbours "
+                    "at every level, the hub-heavy regime)")
+    ap.add_argument("--beta-lo", type=float, default=0.01)
+    ap.add_argument("--beta-hi", type=float, default=0.05)
+    ap.add_argument("--tag", default="")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -55,7 +60,8 @@ def main():
     p = args.traits
     n = m + p
     ns = 458000
-    Cm = synth.merged_correlation(args.loci, args.per_locus, p, stream=5, num_samples=ns)
+    Cm = synth.merged_correlation(args.loci, args.per_locus, p, stream=5, num_samples=ns, causal_per_trait=args.causal,
+                                  beta_lo=args.beta_lo, beta_hi=args.beta_hi)
     dC = torch.from_numpy(Cm).cuda()
     del Cm
     if args.uniform:
@@ -116,7 +122,11 @@ def main():
         same = True
     if rank == 0:
         print(json.dumps({
-            "metric": "ci_tests_per_s", "workload": f"cuskss-merged {m} markers + {p} traits (n_var {n}), "
+            "metric": "ci_tests_per_s", "tag": args.tag, "generator": {"loci": args.loci, "per_locus": args.per_locus,
+            "causal_per_trait": args.causal, "beta": [args.beta_lo, args.beta_hi], "stream": 5},
+            "knobs": {k: v for k, v in os.environ.items() if k.startswith("CUSK_")},
+            "tests_executed_per_level": st["tests_executed"], "tests_canonical_per_level": st["tests_canonical"],
+            "workload": f"cuskss-merged {m} markers + {p} traits (n_var {n}), "
             f"{'uniform N' if args.uniform else 'heterologous N (0.5% NA)'}, max level {args.maxlevel}, alpha 1e-4; level-l "
             "work items dealt round-robin over the GPUs, ncclAllGather of one removed-flag byte per CSR slot per level",
             "n_gpus": world, "scaling": "strong", "steps": args.steps, "ms_per_skeleton": ms / args.steps,

@@ -1,0 +1,32 @@
+#!/bin/bash
+# GPU call C of round 2: ci_dfs.cu after the rewrite (scaled rows in shared memory, division-free leaves), the host-buffer
+# entry points that skip redundant uploads, the whole GPU suite.
+set -u
+OUT=gpurun_out/r2_c
+mkdir -p "$OUT"
+export PYTHONUNBUFFERED=1
+timeout 600 python -m pytest tests/test_zz_dfs_kernel_gpu.py tests/test_skeleton_gpu.py -m gpu -x -q > "$OUT/tests_dfs.log" 2>&1
+echo "dfs + skeleton tests: exit $?" | tee -a "$OUT/summary.txt"
+timeout 900 python -m pytest tests -m gpu -x -q > "$OUT/tests_all.log" 2>&1
+echo "all gpu tests: exit $?" | tee -a "$OUT/summary.txt"
+timeout 600 python bench.py --no-pipelined-probe > "$OUT/bench_n1.json" 2> "$OUT/bench_n1.err"
+echo "bench.py: exit $?" | tee -a "$OUT/summary.txt"
+H30="--loci 100 --causal 30 --steps 1 --warmup 1"
+H36="--loci 100 --causal 36 --beta-lo 0.02 --beta-hi 0.06 --steps 1 --warmup 1 --maxlevel 9"
+timeout 300 python scripts/bench_merged.py $H30 --uniform --tag heavy30_uniform_dfs > "$OUT/heavy30_uniform_dfs.json" 2> "$OUT/heavy30.err"
+echo "heavy30 uniform dfs: exit $?" | tee -a "$OUT/summary.txt"
+timeout 300 python scripts/bench_merged.py $H30 --tag heavy30_het_dfs > "$OUT/heavy30_het_dfs.json" 2>> "$OUT/heavy30.err"
+echo "heavy30 het dfs: exit $?" | tee -a "$OUT/summary.txt"
+timeout 300 python scripts/bench_merged.py $H36 --uniform --tag heavy36_l9_uniform_dfs > "$OUT/heavy36_l9_uniform_dfs.json" 2> "$OUT/heavy36.err"
+echo "heavy36 (max level 9) uniform dfs: exit $?" | tee -a "$OUT/summary.txt"
+timeout 300 python scripts/bench_merged.py $H36 --tag heavy36_l9_het_dfs > "$OUT/heavy36_l9_het_dfs.json" 2>> "$OUT/heavy36.err"
+echo "heavy36 (max level 9) het dfs: exit $?" | tee -a "$OUT/summary.txt"
+for s in 4 12 16; do
+  CUSK_DFS_MIN_SPAN=$s CUSK_DFS_MIN_D=16 timeout 300 python bench.py --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > "$OUT/bench_span$s.json" 2>> "$OUT/bench_n1.err"
+done
+CUSK_DFS=0 timeout 300 python bench.py --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > "$OUT/bench_nodfs.json" 2>> "$OUT/bench_n1.err"
+echo "bench knob sweep done" | tee -a "$OUT/summary.txt"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ci_dfs_kernel -c 8 -o "$OUT/ci_dfs_full" \
+    python scripts/bench_merged.py --loci 100 --causal 36 --beta-lo 0.02 --beta-hi 0.06 --steps 1 --warmup 0 --maxlevel 7 --uniform > "$OUT/ncu_dfs.log" 2>&1
+echo "ncu --set full ci_dfs_kernel: exit $?" | tee -a "$OUT/summary.txt"
+cat "$OUT/summary.txt"
