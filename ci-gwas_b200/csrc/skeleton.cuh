@@ -72,18 +72,23 @@ struct CiParams {
 };
 
 struct DfsTuning {
-    int span, dmin, ipsm;
+    int span, dmin, ipsm, lnarrow;
 };
 DfsTuning dfs_tuning();  // skeleton_kernels.cu
 
 // Which CI kernel takes a row of degree d at level l (degree_plan_kernel and its host-side mirror in skeleton.cu):
 // 0 ci_level_kernel, 1 ci_small_kernel, 2 ci_mid_kernel (l <= 2) / ci_dfs_kernel (l >= 3).
-//   dsmall: CI_SMALL_DMAX or 0 (kernel off); dmid: level-1/2 bound of ci_mid or 0; dfs_span > 0: rows with
-//   dfs_dmin <= d <= CI_DFS_DMAX and d - l >= dfs_span go to ci_dfs at l >= CI_DFS_LMIN (every set then serves at
-//   least dfs_span tests, which is what the lanes-over-neighbours mapping needs to beat a thread per set)
-__host__ __device__ inline int ci_row_class(int d, int l, int dsmall, int dmid, int dfs_span, int dfs_dmin)
+//   dsmall: CI_SMALL_DMAX or 0 (kernel off); dmid: level-1/2 bound of ci_mid or 0; dfs_span > 0: ci_dfs is on.
+//   At l >= CI_DFS_LMIN it takes every row with more than CI_SMALL_DMAX neighbours (up to CI_DFS_DMAX: 4.5x the rate
+//   of ci_level there) and, from level dfs_lnarrow on, the shorter rows with d >= dfs_dmin and d - l >= dfs_span
+//   (every set then serves at least dfs_span tests; measured on trait rows with ~29 neighbours the two kernels tie up
+//   to level 12 and ci_dfs is 1.5-2.2x faster at 13-14, profiles/r2_heavy_*.json; below level 8 the thread-per-set
+//   kernel wins on the small items of a light block)
+__host__ __device__ inline int ci_row_class(int d, int l, int dsmall, int dmid, int dfs_span, int dfs_dmin, int dfs_lnarrow)
 {
-    if (l >= CI_DFS_LMIN && dfs_span > 0 && d <= CI_DFS_DMAX && d >= dfs_dmin && d - l >= dfs_span) return 2;
+    if (l >= CI_DFS_LMIN && dfs_span > 0 && d <= CI_DFS_DMAX &&
+        (d > dsmall || (l >= dfs_lnarrow && d >= dfs_dmin && d - l >= dfs_span)))
+        return 2;
     if (d <= dsmall) return 1;
     if (l <= CI_MID_LMAX && d <= dmid) return 2;
     return 0;

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                                                            double th_het, float n_uniform, int *work_counter,
                                                            int *work_counter_small, int *work_counter_mid, int world,
                                                            int ipsm_shallow, int ipsm_deep, int ipsm_small, int ipsm_mid,
-                                                           int dfs_span, int dfs_dmin, int ipsm_dfs, int sm_count)
+                                                           int dfs_span, int dfs_dmin, int dfs_lnarrow, int ipsm_dfs, int sm_count)
 {
     __shared__ u64 s_warp2[66];
     __shared__ u64 s_acc[4];
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                     if (cb >= CI_MAX_COMB)
                         atomicExch(&s_infeasible, 1);
                     else {
-                        const int rc = ci_row_class(d, l, dsmall, dmid, dfs_span, dfs_dmin);
+                        const int rc = ci_row_class(d, l, dsmall, dmid, dfs_span, dfs_dmin, dfs_lnarrow);
                         atomicAdd((unsigned long long *)&s_acc[rc == 1 ? 1 : (rc == 2 ? 3 : 0)],
                                   (unsigned long long)(cb * (u64)(d - l)));
                     }
@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
             c_next = (rn < n) ? __ldcg(&chunk[rn]) : 0;
         }
         u64 items = 0;
-        const int cls = ci_row_class(d, l, dsmall, dmid, dfs_span, dfs_dmin);
+        const int cls = ci_row_class(d, l, dsmall, dmid, dfs_span, dfs_dmin, dfs_lnarrow);
         if (runs && r < n && d > l) {
             const u64 tests = c * (u64)(d - l);
             u64 tgt = (cls == 1) ? target_small : ((cls == 2) ? target_mid : target);
@@ -640,8 +640,9 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
 }
 
 // ci_dfs.cu routing knobs, read on every call (tests switch them between calls of one process):
-//   CUSK_DFS=0 switches the kernel off; CUSK_DFS_MIN_SPAN: least d - l (default 8); CUSK_DFS_MIN_D: least degree
-//   (default 12); CUSK_ITEMS_PER_SM_DFS: work items per SM the plan aims at (default 48)
+//   CUSK_DFS=0 switches the kernel off; for rows of at most CI_SMALL_DMAX neighbours: CUSK_DFS_NARROW_LEVEL, the first
+//   level at which they may leave ci_small (default 8), CUSK_DFS_MIN_SPAN: least d - l (default 8), CUSK_DFS_MIN_D:
+//   least degree (default 20); CUSK_ITEMS_PER_SM_DFS: work items per SM the plan aims at (default 48)
 DfsTuning dfs_tuning()
 {
     DfsTuning t;
@@ -649,8 +650,10 @@ DfsTuning dfs_tuning()
     const char *sp = getenv("CUSK_DFS_MIN_SPAN");
     const char *dm = getenv("CUSK_DFS_MIN_D");
     const char *ip = getenv("CUSK_ITEMS_PER_SM_DFS");
+    const char *ln = getenv("CUSK_DFS_NARROW_LEVEL");
     t.span = (off && atoi(off) == 0) ? 0 : (sp && atoi(sp) > 0 ? atoi(sp) : 8);
-    t.dmin = (dm && atoi(dm) > 0) ? atoi(dm) : 12;
+    t.dmin = (dm && atoi(dm) > 0) ? atoi(dm) : 20;
+    t.lnarrow = (ln && atoi(ln) > 0) ? atoi(ln) : 8;
     const int v = ip ? atoi(ip) : 0;
     t.ipsm = v > 0 ? (v > CI_SMALL_IPSM_MAX ? CI_SMALL_IPSM_MAX : v) : 48;
     return t;
@@ -698,7 +701,7 @@ unsigned ci_classes_possible(int l, int maxdeg)
     const int top = std::max(CI_DFS_DMAX, std::max(dsmall, dmid)) + 1;  // every larger degree is class 0
     if (maxdeg > top) mask |= 1u;
     for (int d = l + 1; d <= std::min(maxdeg, top); d++) {
-        const int c = ci_row_class(d, l, dsmall, dmid, dt.span, dt.dmin);
+        const int c = ci_row_class(d, l, dsmall, dmid, dt.span, dt.dmin, dt.lnarrow);
         mask |= 1u << c;
         if (c == 2 && l > CI_MID_LMAX && d >= 32) mask |= 1u << 8;
     }
@@ -715,7 +718,7 @@ void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, in
     degree_plan_kernel<<<(n + 31) / 32, 1024, 0, st>>>(bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl, prev,
                                                        th_level, th_het, n_uniform, work_counter,
                                                        work_counter_small, work_counter_mid, world, k.ipsm_shallow,
-                                                       k.ipsm_deep, k.ipsm_small, k.ipsm_mid, dt.span, dt.dmin, dt.ipsm,
+                                                       k.ipsm_deep, k.ipsm_small, k.ipsm_mid, dt.span, dt.dmin, dt.lnarrow, dt.ipsm,
                                                        sm_count > 0 ? sm_count : 148);
 }
 

@@ -362,42 +362,72 @@ MxpRows load_mxp(const std::string &corr_path, const std::string &se_path, bool 
         fail("marker-trait summary stat file has bad header");
     MxpRows out;
     out.num_phen = header.size() - 3;
+    // pass 1 (sequential, memchr speed): the lines to take.  pass 2 (all host threads): their numbers -- a
+    // whole-genome table is 10^6 rows x 17 traits of text, and `cuskss-all` reads it once for all blocks.
+    struct Span {
+        const char *b, *e, *sb, *se;
+    };
+    std::vector<Span> take;
     size_t line = 0;
     while (Lc.next(&b, &e)) {
         if (het) Ls.next(&sb, &se);
-        bool take;
+        bool t;
         if (by_block) {
             if (line > last_global) break;
-            take = line >= first_global;
+            t = line >= first_global;
         } else {
-            if (out.num_markers >= marker_ixs.size()) break;
-            take = line == (size_t)marker_ixs[out.num_markers];
+            if (take.size() >= marker_ixs.size()) break;
+            t = line == (size_t)marker_ixs[take.size()];
         }
-        if (take) {
-            const char *p = b, *tb, *te, *ps = sb, *tsb = nullptr, *tse = nullptr;
-            for (size_t j = 0; j < out.num_phen + 3; j++) {
-                if (!next_tok(&p, e, &tb, &te)) fail("short line in " + corr_path);
-                if (het && !next_tok(&ps, se, &tsb, &tse)) fail("short line in " + se_path);
-                if (j < 3) continue;
-                bool na = tok_is(tb, te, "NA") || tok_is(tb, te, "NaN") || tok_is(tb, te, "nan");
-                if (het) na = na || tok_is(tb, te, "NAN");
-                if (na) {
-                    out.corr.push_back(0.0f);
-                    if (het) out.ess.push_back(std::nanf(""));
-                } else {
-                    const float rho = tok_stof(tb, te);
-                    out.corr.push_back(rho);
-                    if (het) {
-                        const float sev = tok_stof(tsb, tse);
-                        const float ss_sqrt = (float)((1.0 - (double)(rho * rho)) / (double)sev);
-                        out.ess.push_back(ss_sqrt * ss_sqrt);
-                    }
-                }
-            }
-            out.num_markers++;
-        }
+        if (t) take.push_back({b, e, sb, se});
         line++;
     }
+    const size_t p = out.num_phen, nrows = take.size();
+    out.num_markers = nrows;
+    out.corr.assign(nrows * p, 0.0f);
+    if (het) out.ess.assign(nrows * p, 0.0f);
+    int bad = 0;  // 1: short corr line, 2: short se line, 3: unparsable number
+#pragma omp parallel for schedule(static) if (nrows > 4096)
+    for (long long r = 0; r < (long long)nrows; r++) {
+        const Span &sp = take[(size_t)r];
+        const char *q = sp.b, *tb, *te, *qs = sp.sb, *tsb = nullptr, *tse = nullptr;
+        for (size_t j = 0; j < p + 3; j++) {
+            if (!next_tok(&q, sp.e, &tb, &te)) {
+                bad = 1;
+                break;
+            }
+            if (het && !next_tok(&qs, sp.se, &tsb, &tse)) {
+                bad = 2;
+                break;
+            }
+            if (j < 3) continue;
+            bool na = tok_is(tb, te, "NA") || tok_is(tb, te, "NaN") || tok_is(tb, te, "nan");
+            if (het) na = na || tok_is(tb, te, "NAN");
+            float rho = 0.0f, nn = std::nanf("");
+            if (!na) {
+                char buf[64], *endp = nullptr;
+                size_t n = (size_t)(te - tb) < sizeof(buf) - 1 ? (size_t)(te - tb) : sizeof(buf) - 1;
+                memcpy(buf, tb, n);
+                buf[n] = 0;
+                rho = strtof(buf, &endp);
+                if (endp == buf) bad = 3;
+                if (het) {
+                    n = (size_t)(tse - tsb) < sizeof(buf) - 1 ? (size_t)(tse - tsb) : sizeof(buf) - 1;
+                    memcpy(buf, tsb, n);
+                    buf[n] = 0;
+                    const float sev = strtof(buf, &endp);
+                    if (endp == buf) bad = 3;
+                    const float ss_sqrt = (float)((1.0 - (double)(rho * rho)) / (double)sev);
+                    nn = ss_sqrt * ss_sqrt;
+                }
+            }
+            out.corr[(size_t)r * p + (j - 3)] = rho;
+            if (het) out.ess[(size_t)r * p + (j - 3)] = nn;
+        }
+    }
+    if (bad == 1) fail("short line in " + corr_path);
+    if (bad == 2) fail("short line in " + se_path);
+    if (bad == 3) fail("cannot parse a number in " + corr_path + (het ? " / " + se_path : std::string()));
     return out;
 }
 

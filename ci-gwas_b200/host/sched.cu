@@ -56,8 +56,21 @@ struct Tally {
     std::mutex mu;
     size_t done = 0, skipped_existing = 0, skipped_nosig = 0, failed = 0;
     int64_t tests = 0;
+    double load_s = 0, device_s = 0, write_s = 0;  // summed over blocks (host threads overlap them)
+    std::vector<double> device_s_of;               // per device: seconds its blocks spent in the device phase
+    std::vector<size_t> blocks_of;
     std::string first_error;
 };
+
+// Host threads per GPU (CUSK_SLOTS_PER_GPU, default 2), each with its own context (stream, arenas): while one
+// block is in its device phase the other slot of the GPU reads, assembles, uploads or writes the next one, and the
+// kernels of two small blocks can share the GPU (overlap file IO / H2D with compute).
+int slots_per_gpu()
+{
+    const char *e = getenv("CUSK_SLOTS_PER_GPU");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? (v > 8 ? 8 : v) : 2;
+}
 
 int64_t tests_of(const RunReport &r)
 {
@@ -78,10 +91,15 @@ int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, c
     const std::vector<size_t> order = lpt_order(blocks);
     std::atomic<size_t> next{0};
     Tally tally;
+    tally.device_s_of.assign(devices.size(), 0.0);
+    tally.blocks_of.assign(devices.size(), 0);
+    const int slots = slots_per_gpu();
     const auto t0 = std::chrono::steady_clock::now();
     std::vector<std::thread> workers;
-    for (int dev : devices) {
-        workers.emplace_back([&, dev]() {
+    for (size_t di = 0; di < devices.size() * (size_t)slots; di++) {
+        const int dev = devices[di / (size_t)slots];
+        const size_t dslot = di / (size_t)slots;
+        workers.emplace_back([&, dev, dslot]() {
             cusk_ctx *ctx = nullptr;
             if (cusk_ctx_create(dev, &ctx) != CUSK_OK) {
                 std::lock_guard<std::mutex> lk(tally.mu);
@@ -119,6 +137,11 @@ int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, c
                     tally.done++;
                     tally.tests += tests_of(rep);
                 }
+                tally.load_s += rep.load_s;
+                tally.device_s += rep.device_s;
+                tally.write_s += rep.write_s;
+                tally.device_s_of[dslot] += rep.device_s;
+                tally.blocks_of[dslot]++;
                 printf("{\"block\": \"%s\", \"device\": %d, \"rc\": %d, \"skipped\": %s, \"n_var\": %zu, \"n_out\": %zu, "
                        "\"load_s\": %.4f, \"device_s\": %.4f, \"write_s\": %.4f, \"tests\": %lld}\n",
                        blocks[bid].stem().c_str(), dev, rc, rep.skipped ? "true" : "false", rep.num_var_in,
@@ -129,10 +152,20 @@ int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, c
     }
     for (auto &w : workers) w.join();
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::string per_gpu = "[";
+    for (size_t i = 0; i < devices.size(); i++) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "%s{\"device\": %d, \"blocks\": %zu, \"device_phase_s\": %.4f, \"busy\": %.3f}", i ? ", " : "",
+                 devices[i], tally.blocks_of[i], tally.device_s_of[i], secs > 0 ? tally.device_s_of[i] / secs : 0.0);
+        per_gpu += buf;
+    }
+    per_gpu += "]";
     printf("{\"summary\": true, \"blocks\": %zu, \"done\": %zu, \"skipped_existing\": %zu, \"skipped_no_signal\": %zu, "
-           "\"failed\": %zu, \"gpus\": %zu, \"seconds\": %.3f, \"ci_tests\": %lld, \"ci_tests_per_s\": %.4g}\n",
-           blocks.size(), tally.done, tally.skipped_existing, tally.skipped_nosig, tally.failed, devices.size(), secs,
-           (long long)tally.tests, secs > 0 ? (double)tally.tests / secs : 0.0);
+           "\"failed\": %zu, \"gpus\": %zu, \"slots_per_gpu\": %d, \"seconds\": %.3f, \"ci_tests\": %lld, "
+           "\"ci_tests_per_s\": %.4g, \"sum_load_s\": %.3f, \"sum_device_s\": %.3f, \"sum_write_s\": %.3f, \"per_gpu\": %s}\n",
+           blocks.size(), tally.done, tally.skipped_existing, tally.skipped_nosig, tally.failed, devices.size(), slots, secs,
+           (long long)tally.tests, secs > 0 ? (double)tally.tests / secs : 0.0, tally.load_s, tally.device_s, tally.write_s,
+           per_gpu.c_str());
     if (tally.failed) {
         std::cerr << tally.first_error << std::endl;
         return 1;

@@ -3,6 +3,8 @@
 All generators are numpy-only and seeded (PCG64, master seed 20261104 + stream id) so that the
 parity tests, the bench and the reference arm see bit-identical inputs.
 """
+import os
+
 import numpy as np
 
 MASTER_SEED = 20261104
@@ -298,3 +300,132 @@ def simulate_dag(n=10000, snp=1600, tr=10, n_latent=2, deg=3, prob_pleio=0.2, lo
     np.fill_diagonal(C, 1.0)
     truth = G[np.ix_(keep, keep)]
     return C, truth | truth.T
+
+
+# ---- BASELINE.json configs[3] (C4): a whole genome of LD blocks as cuskss input files ---------------------------------
+def c4_block_sizes(nblocks=1700, stream=4, median=600, sigma=0.6, lo=50, hi=3000):
+    """sizes clip(round(LogNormal(ln 600, 0.6)), 50, 3 000)"""
+    rng = rng_for(stream)
+    return np.clip(np.rint(rng.lognormal(np.log(median), sigma, size=nblocks)), lo, hi).astype(np.int64)
+
+
+def _c4_marker_factor(m, stream, sub_block=50, window=12, max_parents=4, wlo=0.6, whi=0.95):
+    """marker part of sem_correlation (the bench's C2 generator): x = A e with unit variances"""
+    rng = rng_for(stream)
+    A = np.zeros((m, m), np.float64)
+    for i in range(m):
+        row = np.zeros(m, np.float64)
+        v = 0.0
+        if i > 0:
+            if (i % sub_block) == 0:
+                row = 0.3 * A[i - 1]
+            else:
+                lo = max(i - window, i - (i % sub_block))
+                k = min(int(rng.integers(1, max_parents + 1)), i - lo)
+                par = rng.choice(np.arange(lo, i), size=k, replace=False)
+                w = rng.uniform(wlo, whi, size=k) * rng.choice([-1.0, 1.0], size=k)
+                row = w @ A[par]
+            v = float(row @ row)
+            if v > 0.9:
+                row = row * np.sqrt(0.9 / v)
+                v = 0.9
+        row[i] = np.sqrt(1.0 - v)
+        A[i] = row
+    return A, rng
+
+
+def _c4_worker_init():
+    """forked generator workers: one BLAS thread each (the pool already uses every core)"""
+    try:
+        from threadpoolctl import threadpool_limits
+
+        threadpool_limits(1)
+    except Exception:  # noqa: BLE001
+        pass
+
+
+def _c4_write_block(args):
+    """worker: one block's mxm file; returns (block, C_b beta [m, p], beta' C_b beta [p, p])"""
+    b, m, stream, beta, outdir, stem, num_samples = args
+    A, rng = _c4_marker_factor(int(m), stream)
+    Cb = A @ A.T
+    E = rng.standard_normal((m, m)) / np.sqrt(float(num_samples))
+    E = np.triu(E, 1)
+    Cs = np.clip(Cb + E + E.T, -0.999999, 0.999999)
+    np.fill_diagonal(Cs, 1.0)
+    Cs.astype(np.float32)[np.tril_indices(m)].tofile(os.path.join(outdir, "mxm", stem + ".bin"))
+    cb = Cb @ beta  # [m, p] population covariance of the block's markers with the traits' genetic parts
+    return b, cb, beta.T @ cb
+
+
+def c4_genome(outdir, nblocks=1700, p=17, stream=4, num_samples=458000, causal_total=300, trait_density=0.3, chromosomes=22,
+              procs=None):
+    """Writes a synthetic whole genome as `mps cuskss-all` / `ci-gwas.py cuskss` input: <outdir>/genome.blocks
+    (chr, first, last per chromosome), <outdir>/mxm/<chr>_<first>_<last>.bin (float32 lower triangle incl. diagonal), one
+    <outdir>/mxp.txt for the whole genome and <outdir>/pxp.txt.  Every block's marker LD comes from the bench's C2
+    generator with its own stream; each of the p traits has `causal_total` causal markers spread over the genome
+    (|beta| ~ U(0.01, 0.05)) and lower-triangular trait-trait effects; marker-trait and trait-trait correlations follow
+    analytically (blocks are independent) plus N(0, 1/num_samples) noise.  Returns dict(sizes, stems, markers)."""
+    import multiprocessing as mp
+
+    os.makedirs(os.path.join(outdir, "mxm"), exist_ok=True)
+    sizes = c4_block_sizes(nblocks, stream)
+    rng = rng_for(stream + 7000)
+    total = int(sizes.sum())
+    starts = np.concatenate([[0], np.cumsum(sizes)[:-1]])
+    # chromosomes: consecutive runs of blocks
+    chr_of = (np.arange(nblocks) * chromosomes // nblocks) + 1
+    stems, first_in_chr = [], {}
+    off = {}
+    for b in range(nblocks):
+        c = int(chr_of[b])
+        f = off.get(c, 0)
+        stems.append(f"{c}_{f}_{f + int(sizes[b]) - 1}")
+        off[c] = f + int(sizes[b])
+    # causal markers and effects, per trait, genome-wide
+    betas = [np.zeros((int(m), p)) for m in sizes]
+    for t in range(p):
+        ix = rng.choice(total, size=min(causal_total, total), replace=False)
+        w = rng.uniform(0.01, 0.05, size=ix.size) * rng.choice([-1.0, 1.0], size=ix.size)
+        bl = np.searchsorted(starts, ix, side="right") - 1
+        for i, wi, b in zip(ix, w, bl):
+            betas[b][i - starts[b], t] += wi
+    jobs = [(b, int(sizes[b]), 100000 * stream + b, betas[b], outdir, stems[b], num_samples) for b in range(nblocks)]
+    procs = procs or min(32, os.cpu_count() or 1)
+    covG = np.zeros((p, p))
+    cbs = [None] * nblocks
+    with mp.get_context("fork").Pool(procs, initializer=_c4_worker_init) as pool:
+        for b, cb, g in pool.imap_unordered(_c4_write_block, jobs, chunksize=4):
+            cbs[b] = cb
+            covG += g
+    # traits: z = G + e (unit variance), y = D M z with M unit lower triangular (trait -> later trait effects)
+    ve = np.clip(1.0 - np.diag(covG), 0.05, None)
+    covZ = covG + np.diag(ve)
+    M = np.eye(p)
+    for t in range(p):
+        for u in range(t):
+            if rng.random() < trait_density:
+                M[t] += rng.uniform(-0.3, 0.3) * M[u]
+    covY = M @ covZ @ M.T
+    dinv = 1.0 / np.sqrt(np.diag(covY))
+    pxp = covY * dinv[:, None] * dinv[None, :]
+    Ep = rng.standard_normal((p, p)) / np.sqrt(float(num_samples))
+    Ep = np.triu(Ep, 1)
+    pxp = np.clip(pxp + Ep + Ep.T, -0.999999, 0.999999)
+    np.fill_diagonal(pxp, 1.0)
+    names = [f"T{t + 1}" for t in range(p)]
+    with open(os.path.join(outdir, "pxp.txt"), "w") as fh:
+        fh.write(" ".join(names) + "\n")
+        for a in range(p):
+            fh.write(names[a] + " " + " ".join("%.9g" % pxp[a, b] for b in range(p)) + "\n")
+    mix = (M * dinv[:, None]).T  # cov(marker, y) = cov(marker, z) M' D
+    with open(os.path.join(outdir, "mxp.txt"), "w") as fh, open(os.path.join(outdir, "genome.blocks"), "w") as fb:
+        fh.write("chr snp ref " + " ".join(names) + "\n")
+        for b in range(nblocks):
+            c, f, l = stems[b].split("_")
+            fb.write(f"{c}\t{f}\t{l}\n")
+            mt = cbs[b] @ mix + rng.standard_normal((int(sizes[b]), p)) / np.sqrt(float(num_samples))
+            np.clip(mt, -0.999999, 0.999999, out=mt)
+            lines = ["%s rs%d_%d A " % (c, b, i) + " ".join("%.7g" % v for v in mt[i]) for i in range(int(sizes[b]))]
+            fh.write("\n".join(lines) + "\n")
+    return dict(sizes=sizes, stems=stems, markers=total)

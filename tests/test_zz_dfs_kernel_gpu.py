@@ -1,7 +1,8 @@
 """ci_dfs.cu (levels >= 3, lanes over the row's neighbours) against the oracle and against the other CI kernels.
 
-The level plan sends a row to ci_dfs_kernel when CUSK_DFS_MIN_D <= d <= 63 and d - l >= CUSK_DFS_MIN_SPAN (defaults 12
-and 8); the knobs are read on every call, so these tests lower them to put EVERY row with more than l neighbours of a
+The level plan sends a row to ci_dfs_kernel at l >= 3 when it has 33..63 neighbours, and from level
+CUSK_DFS_NARROW_LEVEL (8) on also when CUSK_DFS_MIN_D (20) <= d <= 32 and d - l >= CUSK_DFS_MIN_SPAN (8); the knobs are
+read on every call, so these tests lower them to put EVERY row with more than l neighbours of a
 small case on the kernel (all levels 3..14, one and two columns per lane, all three modes: individual-level engine,
 uniform N, per-pair N with NaN and a time index), and switch the kernel off (CUSK_DFS=0) to compare routes on the same
 input: PC-stable results do not depend on which kernel ran a row.
@@ -41,7 +42,7 @@ class dfs_knobs:
                 os.environ[k] = v
 
 
-ALL_ROWS = dict(CUSK_DFS="1", CUSK_DFS_MIN_SPAN=1, CUSK_DFS_MIN_D=1)
+ALL_ROWS = dict(CUSK_DFS="1", CUSK_DFS_MIN_SPAN=1, CUSK_DFS_MIN_D=1, CUSK_DFS_NARROW_LEVEL=3)
 
 
 def test_dfs_all_levels_individual_level_engine(ctx, oracle):
