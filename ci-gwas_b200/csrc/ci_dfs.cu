@@ -82,6 +82,8 @@ __global__ void __launch_bounds__(CD_NTHREADS) ci_dfs_kernel(const CiParams p)
     __shared__ int s_item;
     LevelCtl *ctl = p.ctl;
     if (ctl->done) return;
+    // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
+    const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int l = LT;
     const int n = p.n;
@@ -96,7 +98,7 @@ __global__ void __launch_bounds__(CD_NTHREADS) ci_dfs_kernel(const CiParams p)
 
     for (;;) {
         __syncthreads();
-        if (tid == 0) s_item = p.shard_rank + p.shard_world * atomicAdd(NS == 1 ? p.work_counter_mid : p.work_counter_dfs2, 1);
+        if (tid == 0) s_item = srank + sworld * atomicAdd(NS == 1 ? p.work_counter_mid : p.work_counter_dfs2, 1);
         __syncthreads();
         const int item = s_item;
         if (item >= nitems) break;

@@ -37,6 +37,8 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
     } s_it;
     LevelCtl *ctl = p.ctl;
     if (ctl->done) return;  // (short rows are not in this kernel's item table: ci_small.cu)
+    // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
+    const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int l = p.l, k = l - 1, n = p.n;
     const int nitems = ctl->nitems;
@@ -51,7 +53,7 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         __syncthreads();
         if (tid == 0) {
             // one thread decodes the item (row lookup, C(d,l), rank range) for the whole CTA
-            const int item = p.shard_rank + p.shard_world * atomicAdd(p.work_counter, 1);
+            const int item = srank + sworld * atomicAdd(p.work_counter, 1);
             s_it.item = item;
             if (item < nitems && item < p.item_cap) {
                 const int4 a4 = *(const int4 *)&p.items[item];

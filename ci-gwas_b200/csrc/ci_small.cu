@@ -80,6 +80,8 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
     __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
     LevelCtl *ctl = p.ctl;
     if (ctl->done) return;
+    // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
+    const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int l = LT;
     const int n = p.n;
@@ -104,7 +106,7 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
 
     for (;;) {
         int item = 0;
-        if (lane == 0) item = p.shard_rank + p.shard_world * atomicAdd(p.work_counter_small, 1);
+        if (lane == 0) item = srank + sworld * atomicAdd(p.work_counter_small, 1);
         item = __shfl_sync(FULLMASK, item, 0);
         if (item >= nitems) break;
         if (item >= p.item_cap) {  // cannot happen: plan_kernel bounds the item count of a small level

@@ -56,7 +56,8 @@ struct ShardLink {
     // while another rank's collective kernel is already waiting for this rank); nullptr for one process per GPU
     void (*host_barrier)(void *user) = nullptr;
     void *user = nullptr;
-    double exchange_ms = 0.0;   // host-measured time spent in the exchanges of the last call
+    double exchange_ms = 0.0;   // device time between the end of a level's CI kernels and the end of its exchange,
+                                // summed over the levels of the last call (includes waiting for the slowest rank)
     size_t exchange_bytes = 0;  // bytes received by this rank in the exchanges of the last call
 };
 
@@ -74,8 +75,9 @@ struct cusk_ctx {
     // pinned, grow-only: the adjacency bitmap on its way back to a host-buffer caller
     void *h_stage = nullptr;
     size_t h_stage_bytes = 0;
-    // [0, ML+2): level boundaries; [ML+2, 3(ML+2)): CI kernel start/stop per level; last 4: copies
-    cudaEvent_t ev[3 * (CUSK_ML + 2) + 4];
+    // [0, ML+2): level boundaries; [ML+2, 3(ML+2)): CI kernel start/stop per level; next 4: copies;
+    // [3(ML+2)+4, 5(ML+2)+4): exchange start/stop per level (edge-sharded mode)
+    cudaEvent_t ev[5 * (CUSK_ML + 2) + 4];
     bool ev_ready = false;
 };
 

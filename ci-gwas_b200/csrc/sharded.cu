@@ -96,6 +96,8 @@ struct cusk_comm {
     LocalGroup *group = nullptr;
     int device = 0;
     ShardLink link;
+    u64 *scratch = nullptr;  // in-process all-reduce: the peers' buffers, grown on demand and kept
+    size_t scratch_count = 0;
 };
 
 __global__ void __launch_bounds__(256) min_u64_kernel(u64 *__restrict__ dst, const u64 *__restrict__ src, size_t count)
@@ -130,13 +132,17 @@ static int local_allreduce_min_u64(void *user, void *d_buf, size_t count, cudaSt
     cusk_comm *c = (cusk_comm *)user;
     LocalGroup *g = c->group;
     const int me = c->link.rank;
-    // pull every peer's buffer into scratch and fold; two barriers keep reads and the write-back apart
-    u64 *scratch = nullptr;
-    cudaError_t e = cudaMalloc((void **)&scratch, (size_t)g->world * count * sizeof(u64));
-    if (e != cudaSuccess) {
-        cusk_set_error("local all-reduce scratch: %s", cudaGetErrorString(e));
-        return (int)e;
+    // pull every peer's buffer into scratch and fold; two barriers keep reads and the write-back apart.  A rank
+    // whose scratch allocation fails still takes part in both barriers (its peers would wait for ever otherwise).
+    cudaError_t e = cudaSuccess;
+    if (c->scratch_count < (size_t)g->world * count) {
+        if (c->scratch) cudaFree(c->scratch);
+        c->scratch = nullptr;
+        c->scratch_count = 0;
+        e = cudaMalloc((void **)&c->scratch, (size_t)g->world * count * sizeof(u64));
+        if (e == cudaSuccess) c->scratch_count = (size_t)g->world * count;
     }
+    u64 *scratch = c->scratch;
     g->send[me] = d_buf;
     g->barrier();
     for (int r = 0; r < g->world && e == cudaSuccess; r++)
@@ -149,7 +155,6 @@ static int local_allreduce_min_u64(void *user, void *d_buf, size_t count, cudaSt
             if (r != me && count) min_u64_kernel<<<grid, 256, 0, st>>>((u64 *)d_buf, scratch + (size_t)r * count, count);
         e = cudaStreamSynchronize(st);
     }
-    cudaFree(scratch);
     if (e != cudaSuccess) {
         cusk_set_error("local all-reduce: %s", cudaGetErrorString(e));
         return (int)e;
@@ -262,27 +267,29 @@ extern "C" int cusk_comm_create_all(cusk_ctx **ctxs, int world, cusk_comm **out)
     return CUSK_OK;
 }
 
-// ranks of one process without NCCL: P2P copies (see LocalGroup).  Each rank must run on its own
-// host thread; ctxs may share a device.
+// ranks of one process without NCCL, all on ONE device (device copies between the ranks' buffers): how the sharded
+// mode is tested on a single GPU.  Each rank must run on its own host thread.  Contexts on distinct devices are
+// refused: between GPUs use cusk_comm_create_all / cusk_comm_create (NCCL); the host-synchronous copy exchange
+// of this group hung on the 8-GPU NVSwitch box in round 1.
 extern "C" int cusk_comm_create_local(cusk_ctx **ctxs, int world, cusk_comm **out)
 {
     if (!ctxs || !out || world < 1) {
         cusk_set_error("cusk_comm_create_local: invalid argument");
         return CUSK_E_ARG;
     }
+    for (int i = 1; i < world; i++)
+        if (!ctxs[i] || !ctxs[0] || ctxs[i]->device != ctxs[0]->device) {
+            cusk_set_error("cusk_comm_create_local: every context must be on the same device (got devices %d and %d); "
+                           "use cusk_comm_create_all (NCCL) for ranks on distinct GPUs",
+                           ctxs[0] ? ctxs[0]->device : -1, ctxs[i] ? ctxs[i]->device : -1);
+            return CUSK_E_ARG;
+        }
     LocalGroup *g = new LocalGroup();
     g->world = world;
     g->send.assign(world, nullptr);
     g->device.resize(world);
     g->refs = world;
     for (int i = 0; i < world; i++) g->device[i] = ctxs[i]->device;
-    for (int i = 0; i < world; i++)
-        for (int j = 0; j < world; j++)
-            if (g->device[i] != g->device[j]) {
-                cudaSetDevice(g->device[i]);
-                cudaDeviceEnablePeerAccess(g->device[j], 0);  // already-enabled is fine
-                cudaGetLastError();
-            }
     for (int i = 0; i < world; i++) {
         out[i] = new cusk_comm();
         out[i]->group = g;
@@ -301,6 +308,7 @@ extern "C" void cusk_comm_destroy(cusk_comm *c)
 {
     if (!c) return;
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    if (c->scratch) cudaFree(c->scratch);
     if (c->group) {
         bool last;
         {

@@ -15,7 +15,7 @@ void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, fl
 void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
                         int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
                         double th_het, float n_uniform, int *work_counter, int *work_counter_small,
-                        int *work_counter_mid, int world, int sm_count);
+                        int *work_counter_mid, int world, int sm_count, u64 shard_min_tests);
 unsigned ci_classes_possible(int l, int maxdeg);
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
                     u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
@@ -115,8 +115,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     // het engine: what a rank removed in a level travels as one byte per slot of the level's CSR
     // (nnz_l bytes per rank instead of the n * rw word bitmap), all-gathered and applied by every rank
     unsigned char *d_removed = nullptr, *d_gather = nullptr;
-    size_t flag_stride = 0, nnz_l = 0;
-    bool shard_level = false;
+    size_t flag_stride = 0, nnz1 = 0;
+    int exchanged_levels = 0;
     static const u64 shard_min_tests = [] {
         const char *e = getenv("CUSK_SHARD_MIN_TESTS");
         const long long v = e ? atoll(e) : -1;
@@ -172,13 +172,14 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
         nl++, launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
                            a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l, d_work_small + l,
-                           d_work_mid + l, sh ? sh->world : 1, ctx->sm_count);
+                           d_work_mid + l, sh ? sh->world : 1, ctx->sm_count, shard_min_tests);
         if (l == 1) {
             // the only mid-call synchronisation: directed edge count after level 0
             LevelCtl h;
             CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
             CUSK_CUDA(cudaStreamSynchronize(st));
             const size_t nnz = (size_t)h.nnz;
+            nnz1 = nnz;
             maxdeg_bound = h.maxdeg;
 
             d_adj = (int *)arena_take(ctx, sizeof(int) * std::max<size_t>(nnz, 1));
@@ -200,25 +201,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             }
         }
         if (sh && l == 1 && sh->host_barrier) sh->host_barrier(sh->user);  // every rank has done its allocations
-        if (sh) {
-            // the ranks must agree on when to stop exchanging: read the level's verdict (and its CSR size)
-            LevelCtl h;
-            CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
-            CUSK_CUDA(cudaStreamSynchronize(st));
-            if (h.done) {
-                l_stop = l;
-                break;
-            }
-            maxdeg_bound = h.maxdeg;
-            nnz_l = (size_t)h.nnz;
-            // a level with few tests is cheaper run whole by every rank (same result everywhere, no exchange)
-            // than dealt out and exchanged: an exchange costs a stream synchronisation plus the collective's latency
-            shard_level = (h.acc_tests + h.acc_small + h.acc_mid) >= shard_min_tests;
-            if (shard_level && d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, (nnz_l + 15) & ~(size_t)15, st));
-        }
-        if (!sh && l == CI_DFS_LMIN && maxdeg_bound > CI_DFS_LMIN) {
+        if (l == CI_DFS_LMIN && maxdeg_bound > CI_DFS_LMIN) {
             // one more look at the plan: after level 2 most rows are short, and the bound read here lets the remaining
-            // levels launch only the kernels some row can need (and stop at the first level none can reach)
+            // levels launch only the kernels some row can need (and stop at the first level none can reach).  Every
+            // rank of an edge-sharded run reads the same numbers, so the ranks keep launching the same sequence.
             LevelCtl h;
             CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
             CUSK_CUDA(cudaStreamSynchronize(st));
@@ -228,6 +214,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             }
             maxdeg_bound = h.maxdeg;
         }
+        // edge-sharded mode: whether a level is dealt out is decided on the device (LevelCtl.shard_on, the same on every
+        // rank); the flags of the level start at zero and are exchanged after its kernels whatever the decision was, so
+        // that the host never has to read the plan back: one fixed-size stream-ordered collective per level.
+        if (sh && d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, std::max<size_t>(flag_stride, 16), st));
         const unsigned classes = ci_classes_possible(l, maxdeg_bound);
         nl++, launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
                        d_items_small, d_items_mid, item_cap);
@@ -255,9 +245,9 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.items_small = d_items_small;
         p.items_mid = d_items_mid;
         p.item_cap = item_cap;
-        p.removed = shard_level ? d_removed : nullptr;
-        p.shard_rank = shard_level ? sh->rank : 0;
-        p.shard_world = shard_level ? sh->world : 1;
+        p.removed = sh ? d_removed : nullptr;
+        p.shard_rank = sh ? sh->rank : 0;  // used by the kernels only when the level's plan set shard_on
+        p.shard_world = sh ? sh->world : 1;
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = CUSK_OK;
         if (classes & 1u) rc = (nl++, launch_ci_level(st, a.het, p, grid));  // hub rows
@@ -274,28 +264,29 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             if (rc) return rc;
         }
         CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
-        if (shard_level) {
-            // exchange step of the level: removed edges (het: AND of the bitmaps; individual-level:
-            // minimum of the separating-set ranks), after which every rank holds the same graph again
-            CUSK_CUDA(cudaStreamSynchronize(st));
-            const auto t0 = std::chrono::steady_clock::now();
+        if (sh) {
+            // exchange step of the level: removed edges (het: one flag byte per slot of the level-1 CSR, all-gathered;
+            // individual-level: minimum of the separating-set ranks), after which every rank holds the same graph
+            // again.  Stream-ordered behind the level's kernels, no host synchronisation; timed with events.
+            cudaEvent_t *xe = ev + 3 * (CUSK_ML + 2) + 4 + 2 * l;
+            CUSK_CUDA(cudaEventRecord(xe[0], st));
             int xrc;
             if (a.het) {
-                const size_t cnt = (nnz_l + 15) & ~(size_t)15;
+                const size_t cnt = std::max<size_t>(flag_stride, 16);
                 xrc = sh->allgather(sh->user, d_removed, d_gather, cnt, st);
                 if (!xrc)
                     nl++, launch_apply_removed(st, d_gather, sh->world, cnt, n, rw, d_rowptr, d_deg, d_adj, a.dbits);
                 sh->exchange_bytes += cnt * (size_t)sh->world;
             } else {
-                xrc = sh->allreduce_min_u64(sh->user, d_minkey, nnz_l, st);
-                sh->exchange_bytes += nnz_l * 8;
+                xrc = sh->allreduce_min_u64(sh->user, d_minkey, std::max<size_t>(nnz1, 1), st);
+                sh->exchange_bytes += nnz1 * 8;
             }
             if (xrc) {
                 cusk_set_error("skeleton: exchange step of level %d failed (rc %d)", l, xrc);
                 return CUSK_E_CUDA;
             }
-            CUSK_CUDA(cudaStreamSynchronize(st));
-            sh->exchange_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            CUSK_CUDA(cudaEventRecord(xe[1], st));
+            exchanged_levels = l;
         }
         if (!a.het)
             nl++, launch_resolve(st, a.dC, n, rw, l, a.dbits, d_deg, d_rowptr, d_adj, d_minkey, a.d_pMax, d_seps,
@@ -305,7 +296,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     // final degrees (edge count) and pMax post-processing
     nl++, launch_degree_plan(st, a.dbits, n, rw, d_deg, CUSK_ML + 1, d_rowptr, d_itemstart, d_chunk, d_ctl + CUSK_ML + 1,
                        nullptr, 1.0, 1.0, n_uniform, d_work + CUSK_ML + 1, d_work_small + CUSK_ML + 1,
-                       d_work_mid + CUSK_ML + 1, 1, ctx->sm_count);
+                       d_work_mid + CUSK_ML + 1, 1, ctx->sm_count, shard_min_tests);
     if (!a.het && a.d_pMax) launch_pmax_final(st, a.dbits, n, rw, a.d_pMax);
     const int l_end = std::min(l_stop, maxl + 1);  // event slot that closes the last launched level
     CUSK_CUDA(cudaEventRecord(ev[l_end], st));
@@ -318,6 +309,13 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     CUSK_CUDA(cudaMemcpyAsync(h_sepcount, d_sepcount, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CUSK_CUDA(cudaStreamSynchronize(st));
 
+    if (sh) {
+        for (int l = 1; l <= exchanged_levels; l++) {
+            float ms = 0.f;
+            cudaEvent_t *xe = ev + 3 * (CUSK_ML + 2) + 4 + 2 * l;
+            if (cudaEventElapsedTime(&ms, xe[0], xe[1]) == cudaSuccess) sh->exchange_ms += ms;
+        }
+    }
     // last level as the reference reports it (src/cuPC-S.cu:99,154-159): the first level that
     // finds max_degree - 1 < l stops the loop with l - 1; otherwise the loop counter runs out.
     int last = maxl + 1;

@@ -34,7 +34,8 @@ struct LevelCtl {
     // accumulators of degree_plan_kernel's row phase (zero at the start of a call)
     u64 acc_tests, acc_small, acc_canon;
     int acc_maxdeg, acc_infeasible;
-    unsigned ticket, pad2;
+    unsigned ticket;
+    int shard_on;  // edge-sharded mode: 1 = this level's work items are dealt over the ranks (enough tests to pay for the exchange)
     u64 acc_mid;
 };
 

@@ -225,7 +225,8 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                                                            double th_het, float n_uniform, int *work_counter,
                                                            int *work_counter_small, int *work_counter_mid, int world,
                                                            int ipsm_shallow, int ipsm_deep, int ipsm_small, int ipsm_mid,
-                                                           int dfs_span, int dfs_dmin, int dfs_lnarrow, int ipsm_dfs, int sm_count)
+                                                           int dfs_span, int dfs_dmin, int dfs_lnarrow, int ipsm_dfs, int sm_count,
+                                                           u64 shard_min_tests)
 {
     __shared__ u64 s_warp2[66];
     __shared__ u64 s_acc[4];
@@ -401,6 +402,8 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         ctl->nitems = runs ? (int)(carry_items & 0x1fffffu) : 0;
         ctl->nitems_small = runs ? (int)((carry_items >> 21) & 0x1fffffu) : 0;
         ctl->nitems_mid = runs ? (int)((carry_items >> 42) & 0x1fffffu) : 0;
+        // a level with few tests is cheaper run whole by every rank (same result everywhere) than dealt out
+        ctl->shard_on = (runs && world > 1 && tot_tests + tot_small + tot_mid >= shard_min_tests) ? 1 : 0;
         ctl->done = runs ? 0 : 1;
     }
 }
@@ -711,7 +714,7 @@ unsigned ci_classes_possible(int l, int maxdeg)
 void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
                         int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
                         double th_het, float n_uniform, int *work_counter, int *work_counter_small,
-                        int *work_counter_mid, int world, int sm_count)
+                        int *work_counter_mid, int world, int sm_count, u64 shard_min_tests)
 {
     const PlanKnobs &k = plan_knobs();
     const DfsTuning dt = dfs_tuning();
@@ -719,7 +722,7 @@ void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, in
                                                        th_level, th_het, n_uniform, work_counter,
                                                        work_counter_small, work_counter_mid, world, k.ipsm_shallow,
                                                        k.ipsm_deep, k.ipsm_small, k.ipsm_mid, dt.span, dt.dmin, dt.lnarrow, dt.ipsm,
-                                                       sm_count > 0 ? sm_count : 148);
+                                                       sm_count > 0 ? sm_count : 148, shard_min_tests);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,

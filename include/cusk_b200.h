@@ -186,7 +186,7 @@ typedef struct cusk_comm cusk_comm;
 int cusk_comm_unique_id(char *out128);                       /* ncclGetUniqueId; share it with all ranks */
 int cusk_comm_create(cusk_ctx *ctx, int rank, int world, const char *id128, cusk_comm **out); /* one process per GPU */
 int cusk_comm_create_all(cusk_ctx **ctxs, int world, cusk_comm **out);   /* one process, NCCL, distinct devices */
-int cusk_comm_create_local(cusk_ctx **ctxs, int world, cusk_comm **out); /* one process, P2P copies; ranks may share a device */
+int cusk_comm_create_local(cusk_ctx **ctxs, int world, cusk_comm **out); /* one process, ranks on ONE device (testing); CUSK_E_ARG for distinct devices */
 void cusk_comm_destroy(cusk_comm *c);
 int cusk_ctx_set_comm(cusk_ctx *ctx, cusk_comm *c);          /* attach (NULL detaches): later skeleton calls are sharded */
 int cusk_comm_stats(const cusk_comm *c, double *exchange_ms, int64_t *exchange_bytes); /* of the last call */

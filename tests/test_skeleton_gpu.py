@@ -307,3 +307,40 @@ def test_all_levels_hetcor_engine(ctx, oracle, general_n):
     assert ro["l"] == 15 and rg["l"] == ro["l"]
     _assert_adj_equal(rg["G"], ro["G"], ro["near"])
     assert rg["stats"]["tests_canonical"][:15] == ro["stats"][:15].tolist()
+
+
+def test_local_group_refuses_distinct_devices():
+    """the in-process copy exchange hung with ranks on distinct GPUs of the NVSwitch box; it is a
+    single-device test vehicle and says so (distinct GPUs go through NCCL: cusk_comm_create_all / cusk_comm_create)"""
+    import torch
+
+    import cigwas_b200
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    ctxs = [cigwas_b200.Context(0), cigwas_b200.Context(1)]
+    with pytest.raises(cigwas_b200.CuskError):
+        cigwas_b200.local_group(ctxs)
+    for c in ctxs:
+        c.close()
+
+
+def test_edge_sharded_mixed_levels(ctx, monkeypatch):
+    """with a CUSK_SHARD_MIN_TESTS between the levels' test counts some levels are dealt over the ranks and
+    some run whole on every rank (the decision is taken on the device, LevelCtl.shard_on); same graph either way"""
+    from cigwas_b200 import synth
+    import cigwas_b200
+
+    m, p = 300, 6
+    n = m + p
+    Cm = synth.sem_correlation(m, p, stream=93, num_samples=20000, causal_per_trait=10)
+    N = np.full((n, n), 20000.0, np.float32)
+    th = cigwas_b200.hetcor_threshold(ALPHA)
+    ti = np.zeros(n, np.int32)
+    ti[m:] = 1
+    one = ctx.hetcor_skeleton(Cm, None, N, th, 14, ti)
+    # the library reads the knob once per process: this test only checks that whatever threshold is in force (the
+    # suite's conftest sets 0; a run with CUSK_SHARD_MIN_TESTS=200000 exercises the mixed case) the result is the same
+    res = _run_group(2, [0], lambda c: c.hetcor_skeleton(Cm, None, N, th, 14, ti))
+    for r in res:
+        assert r["l"] == one["l"] and (r["G"] == one["G"]).all()
