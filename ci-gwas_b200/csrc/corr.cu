@@ -37,6 +37,33 @@ __global__ void scatter_mxp_kernel(const float *__restrict__ mxp, int m, int p, 
     Csq[(size_t)(m + t) * ldc + i] = r;
 }
 
+// level 0 of the pairs the Gram epilogue does not see: marker x trait and trait x trait (the strip of C right of /
+// below the markers); same expression and the same upper-triangle entry as level0_kernel
+__global__ void __launch_bounds__(256) level0_strip_kernel(const float *__restrict__ Csq, int nvar, int m, int p, double th,
+                                                           uint32_t *bits, int rw)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int r, c;
+    if (idx < m * p) {
+        r = idx / p;
+        c = m + (idx - r * p);
+    } else {
+        int k = idx - m * p;  // trait pairs a < b, row-major
+        if (k >= p * (p - 1) / 2) return;
+        int a = 0;
+        while (k >= p - 1 - a) {
+            k -= p - 1 - a;
+            a++;
+        }
+        r = m + a;
+        c = m + a + 1 + k;
+    }
+    if (!(corr_fisher_z((double)Csq[(size_t)r * nvar + c]) < th)) {
+        atomicOr(&bits[(size_t)r * rw + (c >> 5)], 1u << (c & 31));
+        atomicOr(&bits[(size_t)c * rw + (r >> 5)], 1u << (r & 31));
+    }
+}
+
 struct EvTimer {
     cudaEvent_t a, b;
     cudaStream_t st;
@@ -66,9 +93,15 @@ struct EvTimer {
 // them; the reference runs that kernel twice, corr_host.cu:1070,1164).
 int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_phen, size_t m, size_t n, size_t p,
                       const float *d_mean, const float *d_std, int mode, float *d_Csq, float *d_mxp_out,
-                      float *d_pxp_out, long long *d_tables, bool want_mxm, cusk_corr_stats *st, bool mxp_ready)
+                      float *d_pxp_out, long long *d_tables, bool want_mxm, cusk_corr_stats *st, bool mxp_ready,
+                      const Level0Fuse *l0)
 {
     cudaStream_t s = ctx->stream;
+    if (l0 && (!d_Csq || !want_mxm || mode != 0)) {
+        cusk_set_error("corr: the fused level 0 needs the dense matrix of the npn correlations");
+        return CUSK_E_ARG;
+    }
+    if (l0) CUSK_CUDA(cudaMemsetAsync(l0->bits, 0, sizeof(uint32_t) * (size_t)(m + p) * (size_t)l0->rw, s));
     const size_t col_bytes = (n + 3) / 4;
     const int nvar = (int)(m + p);
     EvTimer t_counts(ctx, 0), t_decode(ctx, 1), t_gram(ctx, 2), t_mxp(ctx, 3), t_pxp(ctx, 4);
@@ -200,6 +233,11 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         gp.Ty = d_Ty;
         gp.cnty = d_cnty;
         gp.mxp = d_mxp;
+        if (l0) {
+            gp.l0_bits = l0->bits;
+            gp.l0_rw = l0->rw;
+            gp.l0_th = l0->th;
+        }
         t_gram.start();
         rc = launch_gram(s, map_a, map_b, gp, std::min<int>(ctx->sm_count, (int)tiles.size()));
         if (rc) return rc;
@@ -217,6 +255,11 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
     if (tc_mxp && d_Csq)
         scatter_mxp_kernel<<<(unsigned)((m * p + 255) / 256), 256, 0, s>>>(d_mxp, (int)m, (int)p, d_Csq, nvar);
     if (d_Csq) launch_set_diag(s, d_Csq, nvar, nvar);
+    if (l0 && p > 0) {
+        const size_t pairs = m * p + p * (p - 1) / 2;
+        level0_strip_kernel<<<(unsigned)((pairs + 255) / 256), 256, 0, s>>>(d_Csq, nvar, (int)m, (int)p, l0->th, l0->bits,
+                                                                           l0->rw);
+    }
     CUSK_CUDA(cudaGetLastError());
     if (st) {
         CUSK_CUDA(cudaStreamSynchronize(s));
@@ -243,7 +286,7 @@ extern "C" int cusk_corr_block_dev(cusk_ctx *ctx, const unsigned char *d_bed, co
     cudaEvent_t e0 = ctx->ev[20], e1 = ctx->ev[21];
     cudaEventRecord(e0, ctx->stream);
     int rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, mode, d_Csq, nullptr, nullptr, nullptr, true,
-                               stats, false);
+                               stats, false, nullptr);
     if (rc) return rc;
     cudaEventRecord(e1, ctx->stream);
     CUSK_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -288,7 +331,7 @@ extern "C" int cusk_corr_block(cusk_ctx *ctx, const unsigned char *bed, const fl
     CUSK_CUDA(cudaMemcpyAsync(d_std, stdv, sizeof(float) * m, cudaMemcpyHostToDevice, s));
     cudaEventRecord(e1, s);
     int rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, mode, d_Csq, d_mxp, d_pxp, d_tables, want_mxm,
-                               st, false);
+                               st, false, nullptr);
     if (rc) return rc;
     cudaEventRecord(e2, s);
     if (d_upper) {

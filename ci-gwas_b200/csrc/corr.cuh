@@ -33,7 +33,23 @@ struct GramParams {
     // i < band_rows go to band[i * band_w + (j - i - 1)] and nothing is written to C
     float *band;
     int band_w, band_rows;
+    // level 0 of the individual-level skeleton fused into the epilogue (north_star item 2; cal_Indepl0,
+    // src/cuPC-S.cu:458-484): when l0_bits != nullptr every marker pair whose |atanh r| is not below l0_th sets its
+    // two bits of the adjacency bitmap (l0_rw words per row, zeroed by the caller), so that the skeleton engine
+    // starts at level 1 without reading the matrix back
+    uint32_t *l0_bits;
+    int l0_rw;
+    double l0_th;
 };
+
+struct Level0Fuse {  // corr_block_device: the level-0 adjacency comes out of the correlation pass
+    uint32_t *bits;  // [nvar][rw], written whole
+    int rw;
+    double th;       // Th[0] of threshold_array
+};
+
+// the level-0 statistic exactly as level0_kernel evaluates it (skeleton_kernels.cu)
+__host__ __device__ inline double corr_fisher_z(double rho) { return fabs(0.5 * log(fabs((1.0 + rho) / (1.0 - rho)))); }
 
 #define CUSK_TC_MXP_MAX_TRAITS 32
 

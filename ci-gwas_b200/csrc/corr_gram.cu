@@ -344,6 +344,10 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         }
                         p.C[(size_t)i * p.ldc + j] = rf;
                         p.C[(size_t)j * p.ldc + i] = rf;
+                        if (p.l0_bits && !(corr_fisher_z((double)rf) < p.l0_th)) {  // level 0: the edge stays
+                            atomicOr(&p.l0_bits[(size_t)i * p.l0_rw + (j >> 5)], 1u << (j & 31));
+                            atomicOr(&p.l0_bits[(size_t)j * p.l0_rw + (i >> 5)], 1u << (i & 31));
+                        }
                         if (p.tables) {
                             const size_t lin = (size_t)i * (2 * (size_t)p.m - i - 1) / 2 + (size_t)(j - i - 1);
                             for (int k = 0; k < 9; k++) p.tables[lin * 9 + k] = (long long)s[k];

@@ -114,8 +114,11 @@ static int local_allgather(void *user, const void *d_send, void *d_recv, size_t 
     LocalGroup *g = c->group;
     const int me = c->link.rank;
     g->send[me] = d_send;
-    g->barrier();  // every rank's send buffer is complete (callers synchronise their stream first)
-    cudaError_t e = cudaSuccess;
+    // this exchange is host-synchronous (unlike NCCL's, which is ordered on the stream): the level's kernels of this
+    // rank must have finished before a peer copies the buffer
+    cudaError_t e0 = cudaStreamSynchronize(st);
+    g->barrier();  // every rank's send buffer is complete
+    cudaError_t e = e0;
     for (int r = 0; r < g->world && e == cudaSuccess; r++)
         e = cudaMemcpyPeerAsync((char *)d_recv + (size_t)r * bytes, c->device, g->send[r], g->device[r], bytes, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
@@ -144,6 +147,7 @@ static int local_allreduce_min_u64(void *user, void *d_buf, size_t count, cudaSt
     }
     u64 *scratch = c->scratch;
     g->send[me] = d_buf;
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);  // host-synchronous exchange: this rank's level is complete
     g->barrier();
     for (int r = 0; r < g->world && e == cudaSuccess; r++)
         e = cudaMemcpyPeerAsync(scratch + (size_t)r * count, c->device, g->send[r], g->device[r], count * sizeof(u64), st);

@@ -55,6 +55,7 @@ struct EngineArgs {
     const int *d_time;     // het
     float *d_pMax;         // non-het, may be nullptr
     bool want_seps;
+    bool level0_done;      // non-het: dbits already holds the level-0 adjacency (fused into the correlation epilogue)
 };
 
 struct EngineOut {
@@ -146,7 +147,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     } else if (a.het) {
         nl++, launch_level0(st, true, a.dC, dN, n_uniform, a.all_ones ? nullptr : a.dG_in, n, rw, (double)a.th_het,
                       a.dbits, nullptr);
-    } else {
+    } else if (!a.level0_done) {
         nl++, launch_level0(st, false, a.dC, nullptr, 0.f, nullptr, n, rw, (double)a.Th[0], a.dbits, a.d_pMax);
     }
     CUSK_CUDA(cudaGetLastError());
@@ -374,8 +375,12 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
 
 // ---- engine entry points used by api.cu and the correlation -> skeleton pipeline ----------------
 int skeleton_engine(cusk_ctx *ctx, const float *dC, int n, uint32_t *dbits, const float *Th, int maxlevel,
-                    int *l_out, float *d_pMax, std::vector<cusk_sepset> *seps, cusk_stats *stats)
+                    int *l_out, float *d_pMax, std::vector<cusk_sepset> *seps, cusk_stats *stats, bool level0_done)
 {
+    if (level0_done && d_pMax) {
+        cusk_set_error("skeleton: a fused level 0 does not produce pMax");
+        return CUSK_E_ARG;
+    }
     arena_reset(ctx);
     EngineArgs a = {};
     a.het = false;
@@ -386,6 +391,7 @@ int skeleton_engine(cusk_ctx *ctx, const float *dC, int n, uint32_t *dbits, cons
     a.maxlevel = maxlevel;
     a.d_pMax = d_pMax;
     a.want_seps = seps != nullptr;
+    a.level0_done = level0_done;
     EngineOut eo;
     int rc = run_engine(ctx, a, &eo, stats);
     if (rc) return rc;
@@ -441,7 +447,7 @@ extern "C" int cusk_skeleton_dev(cusk_ctx *ctx, const float *dC, int n, uint32_t
     CUSK_CUDA(cudaSetDevice(ctx->device));
     std::vector<cusk_sepset> seps;
     const bool want = sep != nullptr || sep_n != nullptr;
-    int rc = skeleton_engine(ctx, dC, n, dG_bits, Th, maxlevel, l_out, d_pMax, want ? &seps : nullptr, stats);
+    int rc = skeleton_engine(ctx, dC, n, dG_bits, Th, maxlevel, l_out, d_pMax, want ? &seps : nullptr, stats, false);
     if (rc) return rc;
     if (sep_n) *sep_n = (int64_t)seps.size();
     if (sep && sep_cap > 0)

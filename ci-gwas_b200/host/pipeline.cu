@@ -14,6 +14,7 @@
 #include <thread>
 #include <unordered_map>
 
+#include "../csrc/corr.cuh"
 #include "../csrc/engine.h"
 #include "host.hpp"
 
@@ -44,6 +45,39 @@ __global__ void __launch_bounds__(256) gather_square_kernel(const float *__restr
     const int i = blockIdx.y;
     if (j >= ns) return;
     out[(size_t)i * ns + j] = in[(size_t)sel[i] * n + sel[j]];
+}
+
+// Square-matrix assembly on the device (make_square_cuskss_inputs, cli.cpp:89-173, for a block): C = [mxm, mxp; mxp',
+// pxp] from the block's lower-triangular mxm file (NaN -> 0, diagonal as stored), its rows of the marker x trait table
+// and the trait x trait table; N likewise when standard errors were given (marker x marker pairs get the sample size).
+__global__ void __launch_bounds__(256) assemble_square_kernel(const float *__restrict__ tril, int m,
+                                                              const float *__restrict__ mxp, const float *__restrict__ pxp,
+                                                              int p, float *__restrict__ C,
+                                                              const float *__restrict__ mxp_ess,
+                                                              const float *__restrict__ pxp_ess, float sample_size,
+                                                              float *__restrict__ N)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    const int nv = m + p;
+    if (j >= nv) return;
+    float c, nn = sample_size;
+    if (i < m && j < m) {
+        const size_t hi = (size_t)max(i, j), lo = (size_t)min(i, j);
+        const float v = tril[hi * (hi + 1) / 2 + lo];
+        c = isnan(v) ? 0.0f : v;
+    } else if (i < m) {
+        c = mxp[(size_t)i * p + (j - m)];
+        if (mxp_ess) nn = mxp_ess[(size_t)i * p + (j - m)];
+    } else if (j < m) {
+        c = mxp[(size_t)j * p + (i - m)];
+        if (mxp_ess) nn = mxp_ess[(size_t)j * p + (i - m)];
+    } else {
+        c = pxp[(size_t)(i - m) * p + (j - m)];
+        if (pxp_ess) nn = pxp_ess[(size_t)(i - m) * p + (j - m)];
+    }
+    C[(size_t)i * nv + j] = c;
+    if (N) N[(size_t)i * nv + j] = nn;
 }
 
 std::vector<int> expand_bits(const std::vector<uint32_t> &bits, size_t nv, size_t rw, const std::vector<int> &sel)
@@ -181,6 +215,99 @@ static int cuskss_stage(cusk_ctx *ctx, Reduced &gc, bool first_stage, float th, 
     return CUSK_OK;
 }
 
+// First stage of a BLOCK run with the square matrix built on the device: the host reads the block's mxm file into
+// page-locked memory and uploads the triangle (half the bytes of the square), its mxp rows and the trait table; the
+// reduced matrices come back gathered (a few hundred variables), the full n_var^2 matrix never exists on the host.
+// Same bytes in the output files as the host-assembled path (cuskss_stage on make_square_cuskss_inputs).
+static int cuskss_block_first_stage(cusk_ctx *ctx, const CuskssArgs &a, const float *mxp_corr, const float *mxp_ess,
+                                    size_t mxp_rows, const Pxp &pxp, const std::vector<int> &time_index_traits, float th,
+                                    Reduced *out, cusk_stats *stats, double *load_s, double *device_s)
+{
+    const double t0 = now_s();
+    static thread_local Pinned tril_stage;
+    FILE *f = fopen(a.mxm_path.c_str(), "rb");
+    if (!f) fail("file or directory not found: " + a.mxm_path);
+    fseeko(f, 0, SEEK_END);
+    const size_t bytes = (size_t)ftello(f);
+    fseeko(f, 0, SEEK_SET);
+    const size_t cnt = bytes / sizeof(float);
+    float *h_tril = (float *)tril_stage.get(std::max<size_t>(bytes, 4));
+    const size_t got = fread(h_tril, 1, cnt * sizeof(float), f);
+    fclose(f);
+    if (got != cnt * sizeof(float)) fail("short read of " + a.mxm_path);
+    const size_t m = (size_t)((std::sqrt((double)(4 * 2 * cnt + 1)) - 1) / 2);  // marker_summary_stats.cpp:8-24
+    const size_t p = pxp.num_phen, nv = m + p;
+    if (m != mxp_rows) {
+        fail("Numbers of markers seem to differ between mxm and mxp\nmxp: " + std::to_string(mxp_rows) + " x " +
+             std::to_string(p) + "\nmxm: " + std::to_string(m) + " x " + std::to_string(m));
+    }
+    *load_s = now_s() - t0;
+    const double t1 = now_s();
+    const bool het = a.hetcor;
+    const size_t rw = cusk_row_words((int)nv);
+    cudaStream_t st = (cudaStream_t)cusk_ctx_stream(ctx);
+    HOST_CUDA(cudaSetDevice(ctx->device));
+    arena_reset(ctx->io);
+    float *d_tril = (float *)arena_take(ctx->io, std::max<size_t>(m * (m + 1) / 2, 1) * 4);
+    float *d_mxp = (float *)arena_take(ctx->io, std::max<size_t>(m * p, 1) * 4);
+    float *d_pxp = (float *)arena_take(ctx->io, std::max<size_t>(p * p, 1) * 4);
+    float *d_mess = het ? (float *)arena_take(ctx->io, std::max<size_t>(m * p, 1) * 4) : nullptr;
+    float *d_pess = het ? (float *)arena_take(ctx->io, std::max<size_t>(p * p, 1) * 4) : nullptr;
+    float *dC = (float *)arena_take(ctx->io, nv * nv * 4);
+    float *dN = het ? (float *)arena_take(ctx->io, nv * nv * 4) : nullptr;
+    uint32_t *dbits = (uint32_t *)arena_take(ctx->io, nv * rw * 4);
+    int *dT = (int *)arena_take(ctx->io, nv * 4);
+    if (!d_tril || !d_mxp || !d_pxp || !dC || !dbits || !dT || (het && (!d_mess || !d_pess || !dN))) return CUSK_E_CUDA;
+    std::vector<int> time_index(nv, 0);  // markers are time 0, traits carry their time index (cli.cpp:37-42)
+    for (size_t i = m, r = 0; i < nv; i++, r++) time_index[i] = time_index_traits[r];
+    bool use_time = false;
+    for (size_t i = 1; i < nv; i++) use_time |= time_index[i] != time_index[0];
+    HOST_CUDA(cudaMemcpyAsync(d_tril, h_tril, m * (m + 1) / 2 * 4, cudaMemcpyHostToDevice, st));
+    HOST_CUDA(cudaMemcpyAsync(d_mxp, mxp_corr, m * p * 4, cudaMemcpyHostToDevice, st));
+    HOST_CUDA(cudaMemcpyAsync(d_pxp, pxp.corr.data(), p * p * 4, cudaMemcpyHostToDevice, st));
+    if (het) {
+        HOST_CUDA(cudaMemcpyAsync(d_mess, mxp_ess, m * p * 4, cudaMemcpyHostToDevice, st));
+        HOST_CUDA(cudaMemcpyAsync(d_pess, pxp.ess.data(), p * p * 4, cudaMemcpyHostToDevice, st));
+    }
+    if (use_time) HOST_CUDA(cudaMemcpyAsync(dT, time_index.data(), nv * 4, cudaMemcpyHostToDevice, st));
+    assemble_square_kernel<<<dim3((unsigned)((nv + 255) / 256), (unsigned)nv), 256, 0, st>>>(
+        d_tril, (int)m, d_mxp, d_pxp, (int)p, dC, d_mess, d_pess, a.pearson_sample_size, dN);
+    HOST_CUDA(cudaGetLastError());
+    int last = 0;
+    int rc = hetcor_engine(ctx, dC, (int)nv, dbits, nullptr, false, dN, a.pearson_sample_size, th, a.max_level_one,
+                           use_time ? dT : nullptr, &last, stats);
+    if (rc) return rc;
+    std::vector<uint32_t> bits(nv * rw);
+    HOST_CUDA(cudaMemcpyAsync(bits.data(), dbits, nv * rw * 4, cudaMemcpyDeviceToHost, st));
+    HOST_CUDA(cudaStreamSynchronize(st));
+    // subset_variables + reduce_gc(G, C, S, P, num_var, num_phen, ML, new_to_old)  (cli.cpp:56-59)
+    const std::vector<int> sel = subset_variables(bits.data(), nv, rw, m, a.depth);
+    const size_t ns = sel.size();
+    out->num_var = ns;
+    out->num_phen = p;
+    out->max_level = CUSK_ML;
+    out->uniform = !het;
+    out->n_uniform = a.pearson_sample_size;
+    out->new_to_old = sel;
+    out->G = expand_bits(bits, nv, rw, sel);
+    out->C.resize(ns * ns);
+    if (het) out->N.resize(ns * ns);
+    int *d_sel = (int *)arena_take(ctx->io, std::max<size_t>(ns, 1) * 4);
+    float *d_Cs = (float *)arena_take(ctx->io, std::max<size_t>(ns * ns, 1) * 4);
+    float *d_Ns = het ? (float *)arena_take(ctx->io, std::max<size_t>(ns * ns, 1) * 4) : nullptr;
+    if (!d_sel || !d_Cs || (het && !d_Ns)) return CUSK_E_CUDA;
+    HOST_CUDA(cudaMemcpyAsync(d_sel, sel.data(), ns * 4, cudaMemcpyHostToDevice, st));
+    const dim3 gg((unsigned)((ns + 255) / 256), (unsigned)ns);
+    gather_square_kernel<<<gg, 256, 0, st>>>(dC, (int)nv, d_sel, (int)ns, d_Cs);
+    if (het) gather_square_kernel<<<gg, 256, 0, st>>>(dN, (int)nv, d_sel, (int)ns, d_Ns);
+    HOST_CUDA(cudaGetLastError());
+    HOST_CUDA(cudaMemcpyAsync(out->C.data(), d_Cs, ns * ns * 4, cudaMemcpyDeviceToHost, st));
+    if (het) HOST_CUDA(cudaMemcpyAsync(out->N.data(), d_Ns, ns * ns * 4, cudaMemcpyDeviceToHost, st));
+    HOST_CUDA(cudaStreamSynchronize(st));
+    *device_s = now_s() - t1;
+    return CUSK_OK;
+}
+
 void load_cuskss_shared(const CuskssArgs &a, CuskssShared *s)
 {
     s->blocks = read_blocks(a.block_path);
@@ -230,6 +357,7 @@ int run_cuskss(cusk_ctx *ctx, const CuskssArgs &a, bool verbose, RunReport *rep,
     const float th = cusk_hetcor_threshold(a.alpha);
     Reduced gc;
     std::string stem;
+    bool stage_one_done = false;
     if (a.trait_only) {
         gc.num_var = num_phen;
         gc.num_phen = num_phen;
@@ -240,57 +368,90 @@ int run_cuskss(cusk_ctx *ctx, const CuskssArgs &a, bool verbose, RunReport *rep,
         if (a.hetcor) gc.N = pxp.ess;
         stem = "trait_only";
     } else {
-        say("Loading mxm");
-        size_t m = 0;
-        const std::vector<float> mxm = load_mxm_square(a.mxm_path, &m);
         say("Loading mxp summary stats");
         MxpRows mxp;
+        const float *mxp_corr = nullptr, *mxp_ess = nullptr;
+        size_t mxp_rows = 0;
         if (shared && !a.merged) {
             // rows [first_global, last_global] of the preloaded table
             const MxpRows &all = shared->mxp_all;
             const size_t f0 = std::min(block.first_global(), all.num_markers);
             const size_t f1 = std::min(block.last_global() + 1, all.num_markers);
-            mxp.num_phen = all.num_phen;
-            mxp.num_markers = f1 - f0;
-            mxp.corr.assign(all.corr.begin() + f0 * all.num_phen, all.corr.begin() + f1 * all.num_phen);
-            if (!all.ess.empty()) mxp.ess.assign(all.ess.begin() + f0 * all.num_phen, all.ess.begin() + f1 * all.num_phen);
+            if (pxp.num_phen != all.num_phen) fail("Numbers of traits seem to differ between pxp and mxp");
+            mxp_rows = f1 - f0;
+            mxp_corr = all.corr.data() + f0 * all.num_phen;
+            mxp_ess = all.ess.empty() ? nullptr : all.ess.data() + f0 * all.num_phen;
         } else {
             mxp = load_mxp(a.mxp_path, a.hetcor ? a.mxp_se_path : std::string(), !a.merged,
                            a.merged ? 0 : block.first_global(), a.merged ? 0 : block.last_global(), marker_ixs);
+            if (pxp.num_phen != mxp.num_phen) fail("Numbers of traits seem to differ between pxp and mxp");
+            mxp_rows = mxp.num_markers;
+            mxp_corr = mxp.corr.data();
+            mxp_ess = mxp.ess.empty() ? nullptr : mxp.ess.data();
         }
-        if (pxp.num_phen != mxp.num_phen) fail("Numbers of traits seem to differ between pxp and mxp");
-        if (m != mxp.num_markers) {
-            fail("Numbers of markers seem to differ between mxm and mxp\nmxp: " + std::to_string(mxp.num_markers) + " x " +
-                 std::to_string(mxp.num_phen) + "\nmxm: " + std::to_string(m) + " x " + std::to_string(m));
+        static const bool host_assembly = getenv("CUSK_HOST_ASSEMBLY") != nullptr;
+        if (!a.merged && !(ctx->shard && ctx->shard->world > 1) && !host_assembly) {
+            // a block: square matrix built on the device from the uploaded triangle (cuskss_block_first_stage)
+            say("Loading mxm");
+            say("Merging correlations into single matrix");
+            say("Starting first cusk stage");
+            double load_mxm_s = 0, dev_s = 0;
+            int rc1 = cuskss_block_first_stage(ctx, a, mxp_corr, mxp_ess, mxp_rows, pxp, time_index_traits, th, &gc,
+                                               &rep->stage[0], &load_mxm_s, &dev_s);
+            if (rc1) return rc1;
+            rep->stages = 1;
+            rep->num_var_in = mxp_rows + num_phen;
+            rep->load_s = (now_s() - t0) - dev_s;
+            rep->device_s = dev_s;
+            stage_one_done = true;
+            stem = block.stem();
+        } else {
+            say("Loading mxm");
+            size_t m = 0;
+            const std::vector<float> mxm = load_mxm_square(a.mxm_path, &m);
+            if (m != mxp_rows) {
+                fail("Numbers of markers seem to differ between mxm and mxp\nmxp: " + std::to_string(mxp_rows) + " x " +
+                     std::to_string(pxp.num_phen) + "\nmxm: " + std::to_string(m) + " x " + std::to_string(m));
+            }
+            say("Merging correlations into single matrix");
+            MxpRows view;
+            view.num_markers = mxp_rows;
+            view.num_phen = pxp.num_phen;
+            view.corr.assign(mxp_corr, mxp_corr + mxp_rows * pxp.num_phen);
+            if (mxp_ess) view.ess.assign(mxp_ess, mxp_ess + mxp_rows * pxp.num_phen);
+            SquareInputs si = make_square_cuskss_inputs(mxm, m, view, pxp, a.pearson_sample_size, a.hetcor);
+            gc.num_var = m + num_phen;
+            gc.num_phen = num_phen;
+            gc.max_level = a.max_level_one;
+            gc.C = std::move(si.C);
+            gc.N = std::move(si.N);
+            gc.uniform = si.uniform;
+            gc.n_uniform = si.n_uniform;
+            stem = a.merged ? std::string("cuskss_merged") : block.stem();
         }
-        say("Merging correlations into single matrix");
-        SquareInputs si = make_square_cuskss_inputs(mxm, m, mxp, pxp, a.pearson_sample_size, a.hetcor);
-        gc.num_var = m + num_phen;
-        gc.num_phen = num_phen;
-        gc.max_level = a.max_level_one;
-        gc.C = std::move(si.C);
-        gc.N = std::move(si.N);
-        gc.uniform = si.uniform;
-        gc.n_uniform = si.n_uniform;
-        stem = a.merged ? std::string("cuskss_merged") : block.stem();
     }
-    gc.new_to_old.resize(gc.num_var);
-    for (size_t i = 0; i < gc.num_var; i++) gc.new_to_old[i] = (int)i;
-    rep->num_var_in = gc.num_var;
-    rep->load_s = now_s() - t0;
+    if (!stage_one_done) {
+        gc.new_to_old.resize(gc.num_var);
+        for (size_t i = 0; i < gc.num_var; i++) gc.new_to_old[i] = (int)i;
+        rep->num_var_in = gc.num_var;
+        rep->load_s = now_s() - t0;
+    }
 
     const double t1 = now_s();
-    say("Starting first cusk stage");
-    int rc = cuskss_stage(ctx, gc, true, th, a.depth, a.max_level_one, time_index_traits, &rep->stage[0]);
-    if (rc) return rc;
-    rep->stages = 1;
+    int rc = CUSK_OK;
+    if (!stage_one_done) {
+        say("Starting first cusk stage");
+        rc = cuskss_stage(ctx, gc, true, th, a.depth, a.max_level_one, time_index_traits, &rep->stage[0]);
+        if (rc) return rc;
+        rep->stages = 1;
+    }
     if (a.two_stage && !a.trait_only) {
         say("Starting second cusk stage");
         rc = cuskss_stage(ctx, gc, false, th, a.depth, a.max_level_two, time_index_traits, &rep->stage[1]);
         if (rc) return rc;
         rep->stages = 2;
     }
-    rep->device_s = now_s() - t1;
+    rep->device_s += now_s() - t1;
     if (verbose) std::cout << "Retained " << gc.num_markers() << " markers" << std::endl;
     const double t2 = now_s();
     if (a.write_output) gc.to_file(make_path(a.outdir, stem, ""));
@@ -405,13 +566,19 @@ int run_cusk_block(cusk_ctx *ctx, const CuskArgs &a, const CuskShared &s, size_t
     uint32_t *d_bits = (uint32_t *)arena_take(ctx->io, nv * rw * 4);
     if (!d_C || !d_bits) return CUSK_E_CUDA;
     arena_reset(ctx);
+    // level 0 comes out of the correlation pass (the Gram epilogue holds r in a register; the trait strip is a
+    // few thousand pairs): the engine below starts at level 1.  CUSK_FUSE_LEVEL0=0 runs level 0 as its own pass.
+    const char *fuse_env = getenv("CUSK_FUSE_LEVEL0");
+    const bool fuse0 = !(fuse_env && atoi(fuse_env) == 0);
+    Level0Fuse l0 = {d_bits, (int)rw, (double)s.Th[0]};
     rc = corr_block_device(ctx, d_bed, d_phen, m, n, p, d_mean, d_std, 0, d_C, d_mxp, nullptr, nullptr, true, &rep->corr,
-                           true);
+                           true, fuse0 ? &l0 : nullptr);
     if (rc) return rc;
     // ---- first skeleton stage (cli.cpp:662-673) -------------------------------------------------------
     if (verbose) std::cout << "Running cuPC" << std::endl;
     int last = 0;
-    rc = skeleton_engine(ctx, d_C, (int)nv, d_bits, s.Th.data(), a.max_level, &last, nullptr, nullptr, &rep->stage[0]);
+    rc = skeleton_engine(ctx, d_C, (int)nv, d_bits, s.Th.data(), a.max_level, &last, nullptr, nullptr, &rep->stage[0],
+                         fuse0);
     if (rc) return rc;
     std::vector<uint32_t> bits(nv * rw);
     HOST_CUDA(cudaMemcpyAsync(bits.data(), d_bits, nv * rw * 4, cudaMemcpyDeviceToHost, st));

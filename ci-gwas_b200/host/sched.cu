@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <iostream>
@@ -80,15 +81,20 @@ int64_t tests_of(const RunReport &r)
     return t;
 }
 
-template <class RunOne>
-int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, const std::vector<int> &devices,
-            bool resume, RunOne run_one)
+// load_shared() runs on the calling thread WHILE the workers create their CUDA contexts (seconds on an 8-GPU box);
+// it fills `blocks` (and whatever run_one reads); the workers start pulling blocks once it has returned.
+template <class LoadShared, class RunOne>
+int run_all(std::vector<MarkerBlock> &blocks, const std::string &outdir, const std::vector<int> &devices, bool resume,
+            LoadShared load_shared, RunOne run_one)
 {
     if (devices.empty()) {
         std::cerr << "no CUDA device available" << std::endl;
         return 1;
     }
-    const std::vector<size_t> order = lpt_order(blocks);
+    std::vector<size_t> order;
+    std::mutex ready_mu;
+    std::condition_variable ready_cv;
+    int ready = 0;  // 1: shared inputs loaded, -1: loading failed
     std::atomic<size_t> next{0};
     Tally tally;
     tally.device_s_of.assign(devices.size(), 0.0);
@@ -106,6 +112,14 @@ int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, c
                 tally.failed++;
                 if (tally.first_error.empty()) tally.first_error = cusk_last_error();
                 return;
+            }
+            {
+                std::unique_lock<std::mutex> lk(ready_mu);
+                ready_cv.wait(lk, [&] { return ready != 0; });
+                if (ready < 0) {
+                    cusk_ctx_destroy(ctx);
+                    return;
+                }
             }
             for (;;) {
                 const size_t k = next.fetch_add(1);
@@ -150,7 +164,23 @@ int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, c
             cusk_ctx_destroy(ctx);
         });
     }
+    std::string load_error;
+    int load_code = 0;
+    try {
+        load_shared();
+        order = lpt_order(blocks);
+    } catch (const HostError &e) {
+        load_error = e.msg;
+        load_code = e.code ? e.code : 1;
+    }
+    const double load_shared_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    {
+        std::lock_guard<std::mutex> lk(ready_mu);
+        ready = load_error.empty() ? 1 : -1;
+    }
+    ready_cv.notify_all();
     for (auto &w : workers) w.join();
+    if (!load_error.empty()) fail(load_error, load_code);
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     std::string per_gpu = "[";
     for (size_t i = 0; i < devices.size(); i++) {
@@ -161,10 +191,10 @@ int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, c
     }
     per_gpu += "]";
     printf("{\"summary\": true, \"blocks\": %zu, \"done\": %zu, \"skipped_existing\": %zu, \"skipped_no_signal\": %zu, "
-           "\"failed\": %zu, \"gpus\": %zu, \"slots_per_gpu\": %d, \"seconds\": %.3f, \"ci_tests\": %lld, "
+           "\"failed\": %zu, \"gpus\": %zu, \"slots_per_gpu\": %d, \"seconds\": %.3f, \"load_shared_s\": %.3f, \"ci_tests\": %lld, "
            "\"ci_tests_per_s\": %.4g, \"sum_load_s\": %.3f, \"sum_device_s\": %.3f, \"sum_write_s\": %.3f, \"per_gpu\": %s}\n",
            blocks.size(), tally.done, tally.skipped_existing, tally.skipped_nosig, tally.failed, devices.size(), slots, secs,
-           (long long)tally.tests, secs > 0 ? (double)tally.tests / secs : 0.0, tally.load_s, tally.device_s, tally.write_s,
+           load_shared_s, (long long)tally.tests, secs > 0 ? (double)tally.tests / secs : 0.0, tally.load_s, tally.device_s, tally.write_s,
            per_gpu.c_str());
     if (tally.failed) {
         std::cerr << tally.first_error << std::endl;
@@ -178,8 +208,7 @@ int run_all(const std::vector<MarkerBlock> &blocks, const std::string &outdir, c
 int run_cusk_all(const CuskArgs &a, const std::vector<int> &devices, bool resume)
 {
     CuskShared shared;
-    load_cusk_shared(a, &shared, true);
-    return run_all(shared.blocks, a.outdir, devices, resume,
+    return run_all(shared.blocks, a.outdir, devices, resume, [&] { load_cusk_shared(a, &shared, true); },
                    [&](cusk_ctx *ctx, size_t bid, RunReport *rep) { return run_cusk_block(ctx, a, shared, bid, false, rep); });
 }
 
@@ -187,8 +216,8 @@ int run_cusk_all(const CuskArgs &a, const std::vector<int> &devices, bool resume
 int run_cuskss_all(const CuskssArgs &a, const std::string &mxm_pattern, const std::vector<int> &devices, bool resume)
 {
     CuskssShared shared;
-    load_cuskss_shared(a, &shared);
-    return run_all(shared.blocks, a.outdir, devices, resume, [&](cusk_ctx *ctx, size_t bid, RunReport *rep) {
+    return run_all(shared.blocks, a.outdir, devices, resume, [&] { load_cuskss_shared(a, &shared); },
+                   [&](cusk_ctx *ctx, size_t bid, RunReport *rep) {
         CuskssArgs b = a;
         b.block_ix = (int)bid;
         b.merged = false;
