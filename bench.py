@@ -383,6 +383,35 @@ def leg_corr(ctx, torch, peaks):
         dram = json.load(open(os.path.join(ROOT, "profiles", "gram_traffic.json")))
     except Exception:
         pass
+    ref = None
+    try:
+        from tests import ref_lib
+
+        if ref_lib.corr_available():
+            # the reference's own correlation front end (unmodified sources, sm_100) on the leading markers of the same
+            # block, host buffers in and out like ours below; both timed by wall clock around the call
+            mr = 2000
+            rc = ref_lib.RefCorr()
+            sub = np.ascontiguousarray(bed[:mr])
+            with quiet_stdout():
+                rc.corr_pearson_npn(sub[:64], ph, 64, n, p, means[:64], stds[:64])  # context + module load
+                t0 = time.perf_counter()
+                rmxm, rmxp, rpxp = rc.corr_pearson_npn(sub, ph, mr, n, p, means[:mr], stds[:mr])
+                ref_ms = 1e3 * (time.perf_counter() - t0)
+            ctx.corr_block(sub[:64], ph, 64, n, p, means[:64], stds[:64])
+            t0 = time.perf_counter()
+            o = ctx.corr_block(sub, ph, mr, n, p, means[:mr], stds[:mr])
+            our_ms = 1e3 * (time.perf_counter() - t0)
+            pairs = mr * (mr - 1) // 2
+            ref = {"what": "the reference's cu_corr_pearson_npn (src/corr_host.cu:1094, unmodified sources, nvcc -arch=sm_100 "
+                           "--use_fast_math) on the leading markers of the same block, host buffers in / out, wall clock",
+                   "markers": mr, "marker_pairs": pairs, "ref_ms": ref_ms, "ours_same_call_ms": our_ms,
+                   "ref_bed_gbps": mr * ((n + 3) // 4) / 1e9 / (ref_ms * 1e-3),
+                   "max_abs_diff_mxm": float(np.nanmax(np.abs(rmxm - o["mxm"]))),
+                   "max_abs_diff_mxp": float(np.nanmax(np.abs(rmxp - o["mxp"]))),
+                   "extrapolated_ref_ms_full_block": ref_ms * (m * (m - 1) / 2) / pairs}
+    except Exception as e:  # noqa: BLE001
+        ref = {"unavailable": repr(e)[:300]}
     return {"workload": f"BED -> correlations of one block: {n} samples x {m} markers + {p} traits (1 % NA in 3), no "
                         "missing calls, uniform random genotypes; device-resident (BASELINE.json configs[2])",
             "bed_gb": res[-1]["bed_bytes"] / 1e9, "ms_per_block": tot,
@@ -393,7 +422,7 @@ def leg_corr(ctx, torch, peaks):
             "tensor_frac_useful_of_nominal_4.5": useful / (gram * 1e-3) / 4.5e15,
             "tensor_frac_useful_of_2x_measured_bf16": useful / (gram * 1e-3) / (2e12 * bf16),
             "tensor_frac_issued_of_nominal_4.5": issued / (gram * 1e-3) / 4.5e15,
-            "dram_bytes_ncu": dram}
+            "dram_bytes_ncu": dram, "ref_gpu": ref}
 
 
 def leg_merged(ctx, torch, dist, rank, world, th):

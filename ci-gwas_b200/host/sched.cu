@@ -95,6 +95,8 @@ int run_all(std::vector<MarkerBlock> &blocks, const std::string &outdir, const s
     std::mutex ready_mu;
     std::condition_variable ready_cv;
     int ready = 0;  // 1: shared inputs loaded, -1: loading failed
+    std::atomic<int> ctx_ready{0};
+    std::atomic<long long> last_ctx_ready_us{0};  // when the last worker had its CUDA context (since t0)
     std::atomic<size_t> next{0};
     Tally tally;
     tally.device_s_of.assign(devices.size(), 0.0);
@@ -114,6 +116,11 @@ int run_all(std::vector<MarkerBlock> &blocks, const std::string &outdir, const s
                 return;
             }
             {
+                const long long us = std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
+                long long prev = last_ctx_ready_us.load();
+                while (us > prev && !last_ctx_ready_us.compare_exchange_weak(prev, us)) {
+                }
+                ctx_ready.fetch_add(1);
                 std::unique_lock<std::mutex> lk(ready_mu);
                 ready_cv.wait(lk, [&] { return ready != 0; });
                 if (ready < 0) {
@@ -182,6 +189,8 @@ int run_all(std::vector<MarkerBlock> &blocks, const std::string &outdir, const s
     for (auto &w : workers) w.join();
     if (!load_error.empty()) fail(load_error, load_code);
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    // startup (CUDA contexts of every worker, shared tables) against the time spent on the blocks themselves
+    const double contexts_ready_s = 1e-6 * (double)last_ctx_ready_us.load();
     std::string per_gpu = "[";
     for (size_t i = 0; i < devices.size(); i++) {
         char buf[160];
@@ -191,10 +200,11 @@ int run_all(std::vector<MarkerBlock> &blocks, const std::string &outdir, const s
     }
     per_gpu += "]";
     printf("{\"summary\": true, \"blocks\": %zu, \"done\": %zu, \"skipped_existing\": %zu, \"skipped_no_signal\": %zu, "
-           "\"failed\": %zu, \"gpus\": %zu, \"slots_per_gpu\": %d, \"seconds\": %.3f, \"load_shared_s\": %.3f, \"ci_tests\": %lld, "
+           "\"failed\": %zu, \"gpus\": %zu, \"slots_per_gpu\": %d, \"seconds\": %.3f, \"load_shared_s\": %.3f, "
+           "\"contexts_ready_s\": %.3f, \"processing_s\": %.3f, \"ci_tests\": %lld, "
            "\"ci_tests_per_s\": %.4g, \"sum_load_s\": %.3f, \"sum_device_s\": %.3f, \"sum_write_s\": %.3f, \"per_gpu\": %s}\n",
            blocks.size(), tally.done, tally.skipped_existing, tally.skipped_nosig, tally.failed, devices.size(), slots, secs,
-           load_shared_s, (long long)tally.tests, secs > 0 ? (double)tally.tests / secs : 0.0, tally.load_s, tally.device_s, tally.write_s,
+           load_shared_s, contexts_ready_s, secs - std::max(load_shared_s, contexts_ready_s), (long long)tally.tests, secs > 0 ? (double)tally.tests / secs : 0.0, tally.load_s, tally.device_s, tally.write_s,
            per_gpu.c_str());
     if (tally.failed) {
         std::cerr << tally.first_error << std::endl;

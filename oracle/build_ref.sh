@@ -10,12 +10,19 @@ REF=/root/reference/cusk
 OUT="$HERE/_ref"
 [ -d "$REF" ] || { echo "build_ref: $REF not present, skipping"; exit 0; }
 mkdir -p "$OUT"
-if [ -f "$OUT/libcusk_ref.so" ] && [ "$OUT/libcusk_ref.so" -nt "$REF/src/cuPC-S.cu" ]; then exit 0; fi
+if [ -f "$OUT/libcusk_ref.so" ] && [ "$OUT/libcusk_ref.so" -nt "$REF/src/cuPC-S.cu" ] && [ -f "$OUT/libcusk_ref_corr.so" ]; then exit 0; fi
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-std=c++17 -arch=sm_100 -O3 --use_fast_math --expt-relaxed-constexpr -Xcompiler -fPIC -I$REF/include -w"
 $NVCC $FLAGS -dc "$REF/src/cuPC-S.cu" -o "$OUT/cuPC-S.o" &
 $NVCC $FLAGS -dc "$REF/src/hetcor-cuPC-S.cu" -o "$OUT/hetcor-cuPC-S.o" &
 wait
 $NVCC -arch=sm_100 -shared -o "$OUT/libcusk_ref.so" "$OUT/cuPC-S.o" "$OUT/hetcor-cuPC-S.o" -lcudart
+# the reference's correlation kernels and their host drivers (src/corr_kernels.cu, src/corr_host.cu: C++ linkage,
+# called through their mangled names by tests/ref_lib.py), same flags as its CMake build except the architecture
+FLAGS20="-std=c++20 -arch=sm_100 -O3 --use_fast_math --expt-relaxed-constexpr -Xcompiler -fPIC -I$REF/include -w"
+$NVCC $FLAGS20 -dc "$REF/src/corr_kernels.cu" -o "$OUT/corr_kernels.o" &
+$NVCC $FLAGS20 -dc "$REF/src/corr_host.cu" -o "$OUT/corr_host.o" &
+wait
+$NVCC -arch=sm_100 -shared -o "$OUT/libcusk_ref_corr.so" "$OUT/corr_kernels.o" "$OUT/corr_host.o" -lcudart
 rm -f "$OUT"/*.o
-echo "build_ref: $OUT/libcusk_ref.so"
+echo "build_ref: $OUT/libcusk_ref.so $OUT/libcusk_ref_corr.so"

@@ -47,13 +47,39 @@ diff = float(np.nanmax(np.abs(sub - full["corrs"][:rows])))
 tail = orc.mcorrk_banded(bed[m - 40:], 40, n, min(w, 39))
 dtail = float(np.nanmax(np.abs(tail[:, : min(w, 39)] - full["corrs"][m - 40:, : min(w, 39)])))
 pairs = st["pairs"]
+ref = None
+try:
+    from tests import ref_lib
+
+    if ref_lib.corr_available() and not os.environ.get("CUSK_BENCH_NO_REF"):
+        # the reference's own banded correlations (cu_marker_corr_pearson_npn_batched_sparse, src/corr_host.cu:1199: one
+        # kernel launch per marker), unmodified sources built for sm_100, host buffers in / out like ours
+        import ctypes as C
+
+        rc = ref_lib.RefCorr()
+        ub, fp = C.POINTER(C.c_ubyte), C.POINTER(C.c_float)
+        flat = np.ascontiguousarray(bed).reshape(-1)
+        out = np.zeros((m, w), np.float32)
+        rc.banded(flat.ctypes.data_as(ub), 256, n, 8, 256, out.ctypes.data_as(fp))  # context + module load
+        devnull, saved = os.open(os.devnull, os.O_WRONLY), os.dup(1)
+        os.dup2(devnull, 1)
+        t0 = time.perf_counter()
+        rc.banded(flat.ctypes.data_as(ub), m, n, w, m, out.ctypes.data_as(fp))
+        ref_s = time.perf_counter() - t0
+        os.dup2(saved, 1)
+        ok = np.isfinite(out) & np.isfinite(full["corrs"])
+        ref = {"what": "the reference's cu_marker_corr_pearson_npn_batched_sparse (unmodified sources, sm_100 build), host "
+                       "buffers in / out, wall clock", "ms": 1e3 * ref_s, "pairs_per_s": pairs / ref_s,
+               "max_abs_diff_vs_ours": float(np.max(np.abs(out[ok] - full["corrs"][ok])))}
+except Exception as e:  # noqa: BLE001
+    ref = {"unavailable": repr(e)[:300]}
 print(json.dumps({
     "metric": "banded_marker_pairs_per_s", "unit": "pairs/s", "m": m, "n": n, "corr_width": w, "missing": missing,
     "e2e_value": pairs / float(np.median(ts)), "e2e_ms": 1e3 * float(np.median(ts)), "kernel_ms": st["kernel_ms"],
     "h2d_ms": st["h2d_ms"], "kernel_pairs_per_s": pairs / (st["kernel_ms"] * 1e-3),
     "sample_pair_rate_G": pairs * n / (st["kernel_ms"] * 1e-3) / 1e9, "pairs": pairs,
     "cpu_pairs_per_s": rows * w / cpu_s, "cpu_cores": orc.num_threads(), "cpu_sample": f"{rows} rows x {w}",
-    "max_abs_diff_head": diff, "max_abs_diff_tail": dtail,
-    "route": "tcgen05 indicator Gram (CUSK_BLOCK_TC=1)" if os.environ.get("CUSK_BLOCK_TC", "0") not in ("", "0")
-    else "AND + POPC bit planes (default)",
+    "max_abs_diff_head": diff, "max_abs_diff_tail": dtail, "ref_gpu": ref,
+    "route": "AND + POPC bit planes (CUSK_BLOCK_TC=0)" if os.environ.get("CUSK_BLOCK_TC", "") == "0"
+    else "tcgen05 indicator Gram (default from 512 markers)",
 }))

@@ -42,3 +42,38 @@ class RefLib:
         self.lib.Skeleton(Cm.ctypes.data_as(fp), C.byref(P), G.ctypes.data_as(ip), Th.ctypes.data_as(fp), C.byref(l),
                           C.byref(ml), pMax.ctypes.data_as(fp), Sep.ctypes.data_as(ip))
         return dict(G=G, l=l.value, pMax=pMax, SepSet=Sep)
+
+
+CORR_PATH = os.path.join(ROOT, "oracle", "_ref", "libcusk_ref_corr.so")
+
+
+def corr_available():
+    return os.path.exists(CORR_PATH)
+
+
+class RefCorr:
+    """the reference's correlation front end (src/corr_host.cu:1094 cu_corr_pearson_npn and :1199
+    cu_marker_corr_pearson_npn_batched_sparse; C++ linkage, hence the mangled names), unmodified sources, sm_100"""
+
+    def __init__(self):
+        self.lib = C.CDLL(CORR_PATH)
+        ub = C.POINTER(C.c_ubyte)
+        self.npn = getattr(self.lib, "_Z19cu_corr_pearson_npnPKhPKfmmmS2_S2_PfS3_S3_")
+        self.npn.argtypes = [ub, fp, C.c_size_t, C.c_size_t, C.c_size_t, fp, fp, fp, fp, fp]
+        self.npn.restype = None
+        self.banded = getattr(self.lib, "_Z41cu_marker_corr_pearson_npn_batched_sparsePKhmmmmPf")
+        self.banded.argtypes = [ub, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, fp]
+        self.banded.restype = None
+
+    def corr_pearson_npn(self, bed, phen, m, n, p, mean, std):
+        bed = np.ascontiguousarray(bed, np.uint8).reshape(-1)
+        phen = np.ascontiguousarray(phen, np.float32).reshape(-1)
+        mean = np.ascontiguousarray(mean, np.float32)
+        std = np.ascontiguousarray(std, np.float32)
+        mxm = np.zeros(m * (m - 1) // 2, np.float32)
+        mxp = np.zeros(m * p, np.float32)
+        pxp = np.zeros(max(1, p * (p - 1) // 2), np.float32)
+        ub = C.POINTER(C.c_ubyte)
+        self.npn(bed.ctypes.data_as(ub), phen.ctypes.data_as(fp), m, n, p, mean.ctypes.data_as(fp), std.ctypes.data_as(fp),
+                 mxm.ctypes.data_as(fp), mxp.ctypes.data_as(fp), pxp.ctypes.data_as(fp))
+        return mxm, mxp, pxp
