@@ -697,6 +697,25 @@ def main():
             line["cpu_baseline"] = {"value": tests / times[0], "unit": "tests/s", "cores": cores, "kind": "port",
                                     "sample": f"leading {SAMPLE_MARKERS} markers + {P_TRAITS} traits of the block "
                                               f"(n_var {ns}), all levels, {times[0]:.1f} s"}
+        if not args.no_cpu_baseline:
+            # what the reference's own kernels would do differently on this block (int32 rank overflow, F10; the
+            # block-level NoEdgeFlag early exit, F9): counted level by level on the oracle's graphs (oracle/cusk_oracle.cpp
+            # orc_ref_quirks); all zero means the reference enumerates exactly the sets counted in `value`
+            try:
+                from tests import oracle_lib
+
+                orc = oracle_lib.load()
+                Gq = orc.hetcor_skeleton(Cm, np.ones((n, n), np.int32), N, th, 0, ti)["G"]
+                per_level = []
+                for lq in range(1, MAXLEVEL + 1):
+                    q = orc.ref_quirks(Gq, ti, lq)
+                    per_level.append([q["rows_int32_rank_overflow"], q["rows_cut_short_by_noedgeflag"], q["rows_not_analysed"]])
+                    if not orc.hetcor_level(Cm, Gq, N, th, lq, ti):
+                        break
+                line["ref_quirks"] = {"per_level_[int32_overflow_rows, noedgeflag_cut_rows, rows_not_analysed]": per_level,
+                                      "any": bool(any(a or b for a, b, _ in per_level))}
+            except Exception as e:  # noqa: BLE001
+                line["ref_quirks"] = {"unavailable": repr(e)[:200]}
         if not args.no_ref_gpu:
             from tests import ref_lib
 

@@ -2,7 +2,9 @@
 // genotype file set, phenotypes, block descriptors and summary statistics; writers for
 // .mdim/.ixs/.adj/.corr/.sep and the prep-bed column files.  Whole files are read in one call and
 // tokenised in memory (the reference parses line by line through std::istringstream).
+#include <fcntl.h>
 #include <sys/stat.h>
+#include <unistd.h>
 
 #include <cmath>
 #include <cstdio>
@@ -295,39 +297,73 @@ Phen load_phen(const std::string &path)
     Lines L(s);
     const char *b, *e;
     Phen ph;
-    std::vector<float> rows;
     if (!L.next(&b, &e)) return ph;  // header
-    bool first = true;
-    while (L.next(&b, &e)) {
-        const char *tb, *te, *p = b;
+    // pass 1: the lines; pass 2 (all host threads): their numbers.  A .phen of 458 000 samples x 17 traits is 80 MB of text.
+    std::vector<std::pair<const char *, const char *>> lines;
+    while (L.next(&b, &e)) lines.emplace_back(b, e);
+    ph.num_samples = lines.size();
+    if (lines.empty()) return ph;
+    {
+        const char *tb, *te, *p = lines[0].first;
+        size_t col = 0;
+        while (next_tok(&p, lines[0].second, &tb, &te)) col++;
+        ph.num_phen = col >= 2 ? col - 2 : 0;
+    }
+    const size_t np = ph.num_phen, ns = ph.num_samples;
+    ph.data.assign(np * ns, 0.0f);
+    long long bad_line = -1;
+#pragma omp parallel for schedule(static) if (ns > 4096)
+    for (long long i = 0; i < (long long)ns; i++) {
+        const char *tb, *te, *p = lines[(size_t)i].first, *le = lines[(size_t)i].second;
         size_t col = 0, nvals = 0;
-        while (next_tok(&p, e, &tb, &te)) {
+        while (next_tok(&p, le, &tb, &te)) {
             if (col >= 2) {
+                float v;
                 if (tok_is(tb, te, "NA"))
-                    rows.push_back(std::nanf(""));
+                    v = std::nanf("");
                 else {
                     char buf[64];
                     const size_t n = (size_t)(te - tb) < sizeof(buf) - 1 ? (size_t)(te - tb) : sizeof(buf) - 1;
                     memcpy(buf, tb, n);
                     buf[n] = 0;
-                    rows.push_back((float)atof(buf));  // phen.cpp:22: (float)atof
+                    v = (float)atof(buf);  // phen.cpp:22: (float)atof
                 }
+                if (nvals < np) ph.data[nvals * ns + (size_t)i] = v;  // column-major [num_phen][num_samples]
                 nvals++;
             }
             col++;
         }
-        if (first) {
-            ph.num_phen = nvals;
-            first = false;
-        } else if (nvals != ph.num_phen) {
-            fail("Inconsistent row width in .phen file\nLine: " + std::string(b, e));
-        }
-        ph.num_samples++;
+        if (nvals != np) bad_line = i;
     }
-    ph.data.resize(ph.num_phen * ph.num_samples);
-    for (size_t t = 0; t < ph.num_phen; t++)
-        for (size_t i = 0; i < ph.num_samples; i++) ph.data[t * ph.num_samples + i] = rows[i * ph.num_phen + t];
+    if (bad_line >= 0)
+        fail("Inconsistent row width in .phen file\nLine: " + std::string(lines[(size_t)bad_line].first, lines[(size_t)bad_line].second));
     return ph;
+}
+
+// reads [offset, offset + bytes) of a file into dst with several threads (pread on the page cache is memcpy-bound:
+// one thread moves ~2 GB/s, a block of C3 is 1.1 GB)
+void read_file_range(const std::string &path, size_t offset, size_t bytes, unsigned char *dst)
+{
+    const int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) fail("file or directory not found: " + path);
+    const size_t chunk = (size_t)8 << 20;
+    const long long nchunks = (long long)((bytes + chunk - 1) / chunk);
+    bool short_read = false;
+#pragma omp parallel for schedule(dynamic, 1) num_threads(8) if (nchunks > 2)
+    for (long long c = 0; c < nchunks; c++) {
+        size_t off = (size_t)c * chunk;
+        const size_t end = std::min(bytes, off + chunk);
+        while (off < end) {
+            const ssize_t got = pread(fd, dst + off, end - off, (off_t)(offset + off));
+            if (got <= 0) {
+                short_read = true;
+                break;
+            }
+            off += (size_t)got;
+        }
+    }
+    close(fd);
+    if (short_read) fail("short read of " + path);
 }
 
 // ---- summary statistics ------------------------------------------------------------------------

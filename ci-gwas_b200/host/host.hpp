@@ -68,6 +68,7 @@ struct Phen {  // src/phen.cpp:27-74: column-major [num_phen][num_samples], NA -
     std::vector<float> data;
 };
 Phen load_phen(const std::string &path);
+void read_file_range(const std::string &path, size_t offset, size_t bytes, unsigned char *dst);  // several threads; fails on a short read
 
 // ---- summary statistics (cuskss inputs) -----------------------------------------------------
 struct SquareInputs {

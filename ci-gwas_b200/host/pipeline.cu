@@ -518,15 +518,8 @@ int run_cusk_block(cusk_ctx *ctx, const CuskArgs &a, const CuskShared &s, size_t
     // ---- load the block (io.cpp:238-250) straight into page-locked memory -----------------------
     static thread_local Pinned bed_stage;
     unsigned char *h_bed = (unsigned char *)bed_stage.get(std::max<size_t>(m * col_bytes, 1));
-    {
-        FILE *f = fopen((a.bfiles + ".bed").c_str(), "rb");
-        if (!f) fail("file or directory not found: " + a.bfiles + ".bed");
-        // a short read must fail: code 00 is a valid genotype, so zero fill would give plausible wrong correlations
-        const bool seek_ok = fseeko(f, (off_t)(3 + g0 * col_bytes), SEEK_SET) == 0;
-        const size_t got = seek_ok ? fread(h_bed, 1, m * col_bytes, f) : 0;
-        fclose(f);
-        if (got < m * col_bytes) fail("short read of " + a.bfiles + ".bed (block " + block.stem() + ")");
-    }
+    // a short read must fail: code 00 is a valid genotype, so zero fill would give plausible wrong correlations
+    read_file_range(a.bfiles + ".bed", 3 + g0 * col_bytes, m * col_bytes, h_bed);
     rep->load_s = now_s() - t0;
     const double t1 = now_s();
     arena_reset(ctx->io);

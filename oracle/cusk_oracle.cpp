@@ -1048,6 +1048,90 @@ void orc_subset_variables(const int *G, int num_var, int num_markers, int max_de
 
 // bench.py's CPU legs ask for all host cores: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
 // otherwise time the CPU baseline on one thread
+// ---- reference-emulation counters (SURVEY 7 step 1 / 8c "--ref-emulation") -----------------------
+// What the REFERENCE's level-l kernels would do differently from the restatement above on the graph G at the start of
+// level l, counted per row, so that a difference against the reference's GPU output can be explained:
+//   F10  int32 ranks: BINOM / IthCombination work in int (src/cuPC-S.cu:6453-6506); a row whose C(d, l) does not fit
+//        an int enumerates garbage.  out[0] = rows with C(d, l) >= 2^31.
+//   F9   NoEdgeFlag (src/hetcor-cuPC-S.cu:550-589, the same in every cal_Indepl*_ess): a row X is served by
+//        NumOfBlockForEachNodeL = 2 CTAs of ParGivenL = 64 threads; in pass d1 thread tx of CTA bx takes the rank
+//        tx + 64 bx + 128 d1; every thread with a rank sets the CTA's flag to 1 before its set and clears it when it
+//        meets a neighbour Y outside S whose edge is still there and whose time allows S (valid_time_conditioning,
+//        :3055-3065); a CTA whose flag is still 1 at the top of the next pass returns.  Statically (edges as at level
+//        start, which is the best case for the reference: removals during the level only add early exits) a pass leaves
+//        the flag at 1 exactly when none of its 64 sets has such a Y.  out[1] = rows where some CTA returns while
+//        later passes of that CTA still hold a set with a valid (Y, S): rows the reference cuts short; out[2] = the
+//        conditioning sets it never evaluates there; out[3] = rows not analysed (more than `cap` sets).
+// The float32 / --use_fast_math arithmetic of the reference is NOT emulated (its GPU intrinsics have no CPU
+// equivalent); oracle/_ref (the reference's own kernels built for sm_100) is the evidence for that side.
+void orc_ref_quirks(const int *G, int n, const int *time_index, int l, long long cap, long long *out4)
+{
+    std::vector<std::vector<int>> adj;
+    compact(G, n, adj);
+    long long rows_f10 = 0, rows_cut = 0, sets_lost = 0, rows_skipped = 0;
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : rows_f10, rows_cut, sets_lost, rows_skipped)
+    for (int X = 0; X < n; X++) {
+        const std::vector<int> &a = adj[X];
+        const int d = (int)a.size();
+        if (d <= l) continue;  // the kernels return at SizeOfArr <= level
+        const uint64_t nc = binom64(d, l);
+        if (nc >= ((uint64_t)1 << 31)) rows_f10++;
+        if ((long long)nc > cap) {
+            rows_skipped++;
+            continue;
+        }
+        const int tX = time_index[X];
+        // per pass and CTA: does any of the 64 sets have a neighbour Y outside S with max(tX, tY) >= max time of S?
+        std::vector<int> pos(l);
+        for (int i = 0; i < l; i++) pos[i] = i;
+        // largest and second largest max(tX, tY) over the neighbours, to answer "some Y outside S" in O(l)
+        const uint64_t npass = (nc + 127) / 128;
+        std::vector<unsigned char> resets(2 * npass, 0), has_valid(2 * npass, 0);
+        std::vector<uint64_t> valid_sets(2 * npass, 0);
+        uint64_t rank = 0;
+        bool more = true;
+        while (more) {
+            int tS = -2147483647 - 1;
+            for (int i = 0; i < l; i++) tS = std::max(tS, time_index[a[pos[i]]]);
+            bool any = false;
+            int pi = 0;
+            for (int y = 0; y < d && !any; y++) {
+                while (pi < l && pos[pi] < y) pi++;
+                if (pi < l && pos[pi] == y) continue;
+                if (std::max(tX, time_index[a[y]]) >= tS) any = true;
+            }
+            const uint64_t pass = rank / 128, cta = (rank % 128) / 64;
+            if (any) {
+                resets[2 * pass + cta] = 1;
+                valid_sets[2 * pass + cta]++;
+            }
+            rank++;
+            more = next_combination(pos.data(), d, l);
+        }
+        bool cut = false;
+        for (int cta = 0; cta < 2; cta++) {
+            bool returned = false;
+            for (uint64_t ps = 0; ps < npass; ps++) {
+                if (returned) {
+                    if (valid_sets[2 * ps + cta]) {
+                        cut = true;
+                        sets_lost += (long long)valid_sets[2 * ps + cta];
+                    }
+                    continue;
+                }
+                // the pass runs; it leaves the flag at 1 when it had ranks but no thread cleared it
+                const uint64_t first = ps * 128 + (uint64_t)cta * 64;
+                if (first < nc && !resets[2 * ps + cta]) returned = true;  // seen at the top of pass ps + 1
+            }
+        }
+        if (cut) rows_cut++;
+    }
+    out4[0] = rows_f10;
+    out4[1] = rows_cut;
+    out4[2] = sets_lost;
+    out4[3] = rows_skipped;
+}
+
 void orc_set_num_threads(int t)
 {
 #ifdef _OPENMP

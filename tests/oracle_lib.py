@@ -94,6 +94,17 @@ class Oracle:
                                         _p(time_index, c_int_p), int(row_rem), int(row_mod))
         return bool(ran)
 
+    def ref_quirks(self, G, time_index, l, cap=20_000_000):
+        """what the reference's level-l kernels would do differently on graph G at the start of level l:
+        dict(rows_int32_rank_overflow, rows_cut_short_by_noedgeflag, sets_never_evaluated, rows_not_analysed)"""
+        G = np.ascontiguousarray(G, np.int32)
+        n = G.shape[0]
+        ti = np.ascontiguousarray(time_index, np.int32)
+        out = np.zeros(4, np.int64)
+        self.lib.orc_ref_quirks(_p(G, c_int_p), n, _p(ti, c_int_p), int(l), C.c_longlong(cap), _p(out, c_ll_p))
+        return dict(rows_int32_rank_overflow=int(out[0]), rows_cut_short_by_noedgeflag=int(out[1]),
+                    sets_never_evaluated=int(out[2]), rows_not_analysed=int(out[3]))
+
     def bed_col_stats(self, bed, m, n):
         bed = np.ascontiguousarray(bed, np.uint8)
         means = np.zeros(m, np.float32)

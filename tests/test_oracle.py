@@ -150,3 +150,29 @@ def test_skeleton_matches_bruteforce_numpy(oracle):
             G[x, y] = G[y, x] = 0
         l += 1
     assert (r["G"] == G).all()
+
+
+def test_ref_quirk_counters(oracle):
+    """orc_ref_quirks on constructed rows: the reference's NoEdgeFlag early exit (hetcor-cuPC-S.cu:550-589) needs a
+    whole 64-rank pass of one CTA without a (Y, S) that the time rule allows while later passes still hold one; with
+    markers at time 0 and traits at time 1 that cannot happen (any trait neighbour outside S makes S admissible), with
+    the FIRST trait as the latest variable every set that contains it is inadmissible and the row is cut short from
+    level 3 on; int32 ranks overflow at C(40, 14)."""
+    n, m = 60, 43
+    G = np.zeros((n, n), np.int32)
+    G[0, 1:] = 1
+    G[1:, 0] = 1
+    ti = np.zeros(n, np.int32)
+    ti[m:] = 1
+    for l in (2, 3, 4):
+        q = oracle.ref_quirks(G, ti, l)
+        assert q["rows_cut_short_by_noedgeflag"] == 0 and q["rows_int32_rank_overflow"] == 0
+    ti[m] = 3
+    assert oracle.ref_quirks(G, ti, 2)["rows_cut_short_by_noedgeflag"] == 0
+    q = oracle.ref_quirks(G, ti, 3)
+    assert q["rows_cut_short_by_noedgeflag"] == 1 and q["sets_never_evaluated"] == 256
+    G2 = np.zeros((45, 45), np.int32)
+    G2[0, 1:41] = 1
+    G2[1:41, 0] = 1
+    q = oracle.ref_quirks(G2, np.zeros(45, np.int32), 14, cap=1000)
+    assert q["rows_int32_rank_overflow"] == 1 and q["rows_not_analysed"] == 1
