@@ -140,6 +140,20 @@ class quiet_stdout:
         os.close(self.saved)
 
 
+class stdout_to_stderr:
+    """NCCL prints its version banner on stdout when its first communicator comes up; the contract is ONE JSON line"""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 def run_reference_arm(args, rank, world):
     """--impl reference: the reference has no CPU implementation of the skeleton; the timed
     code is the FP64 CPU port under oracle/ on all host threads, on a bounded sample of the workload."""
@@ -536,7 +550,9 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        with stdout_to_stderr():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
     ctx = cigwas_b200.Context(local_rank)
     lib = ctx.lib
     import ctypes as C

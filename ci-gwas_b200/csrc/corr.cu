@@ -196,14 +196,56 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         // HBM.  Squarer super-blocks (16 x 9) should cut HBM traffic 4x on paper but measured worse
         // (ncu: 518 GB read vs 374 GB, L2 hit 39 % vs 50 %, profiles/r1_gram_tile_order.txt): the CTAs
         // that share a block drift apart by more k-steps than the L2 window holds.
-        static const int SB_M = [] { const char *e = getenv("CUSK_GRAM_SB_M"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 1 << 20; }();
-        static const int SB_N = [] { const char *e = getenv("CUSK_GRAM_SB_N"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 1; }();
-        for (int sn = ((n_tn - 1) / SB_N) * SB_N; mxm_tiles && sn >= 0; sn -= SB_N)  // long rows of the triangle first
-            for (int sm = 0; sm < n_tm; sm += SB_M)
-                for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
-                    for (int tm = sm; tm < std::min(sm + SB_M, n_tm); tm++)
-                        if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m)
-                            tiles.push_back({tm, tn});
+        static const int SB_M_ENV = [] { const char *e = getenv("CUSK_GRAM_SB_M"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 0; }();
+        static const int SB_N_ENV = [] { const char *e = getenv("CUSK_GRAM_SB_N"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 0; }();
+        // K-panel synchronisation (GramParams.ksync): with it a wave can be a SQUARE super-block of tiles whose A and B
+        // panels are both shared through L2: (16 x 128 + 9 x 256) K bytes from HBM per 144 tiles instead of 128 K per
+        // tile.  CUSK_GRAM_KSYNC = k-steps between meetings (default 128 = 16 KB of K per operand row; 0 = off)
+        static const int KSYNC = [] { const char *e = getenv("CUSK_GRAM_KSYNC"); return e ? atoi(e) : 128; }();
+        const int grid_full = ctx->sm_count;
+        const bool ksync_on = KSYNC > 0 && mxm_tiles && (size_t)n_tm * (size_t)n_tn > (size_t)2 * grid_full;
+        const int SB_M = SB_M_ENV ? SB_M_ENV : (ksync_on ? 16 : 1 << 20);
+        const int SB_N = SB_N_ENV ? SB_N_ENV : (ksync_on ? 9 : 1);
+        std::vector<int> wave_tiles;
+        if (!ksync_on) {
+            for (int sn = ((n_tn - 1) / SB_N) * SB_N; mxm_tiles && sn >= 0; sn -= SB_N)  // long rows of the triangle first
+                for (int sm = 0; sm < n_tm; sm += SB_M)
+                    for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
+                        for (int tm = sm; tm < std::min(sm + SB_M, n_tm); tm++)
+                            if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m)
+                                tiles.push_back({tm, tn});
+        } else {
+            // one wave = `grid_full` consecutive entries = whole super-blocks (small ones share a wave), padded with
+            // {-1, -1}; the trait tiles pushed above form the first wave(s)
+            auto close_wave = [&]() {
+                const size_t fill = tiles.size() % (size_t)grid_full;
+                int real = (int)(fill ? fill : (tiles.empty() ? 0 : (size_t)grid_full));
+                if (fill)
+                    for (size_t k = fill; k < (size_t)grid_full; k++) tiles.push_back({-1, -1});
+                if (real) wave_tiles.push_back(real);
+            };
+            // trait tiles: count waves already filled by them
+            while ((wave_tiles.size() + 1) * (size_t)grid_full <= tiles.size()) wave_tiles.push_back(grid_full);
+            std::vector<int2> sb;
+            for (int sn = ((n_tn - 1) / SB_N) * SB_N; sn >= 0; sn -= SB_N)
+                for (int sm = 0; sm < n_tm; sm += SB_M) {
+                    sb.clear();
+                    for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
+                        for (int tm = sm; tm < std::min(sm + SB_M, n_tm); tm++)
+                            if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m) sb.push_back({tm, tn});
+                    if (sb.empty()) continue;
+                    const size_t fill = tiles.size() % (size_t)grid_full;
+                    if (fill + sb.size() > (size_t)grid_full) close_wave();
+                    for (const int2 &t : sb) {
+                        tiles.push_back(t);
+                        if (tiles.size() % (size_t)grid_full == 0) wave_tiles.push_back(grid_full);
+                    }
+                }
+            {
+                const size_t fill = tiles.size() % (size_t)grid_full;
+                if (fill) wave_tiles.push_back((int)fill);
+            }
+        }
         int2 *d_tiles = (int2 *)arena_take(ctx, sizeof(int2) * std::max<size_t>(tiles.size(), 1));
         if (!d_tiles) return CUSK_E_CUDA;
         CUSK_CUDA(cudaMemcpyAsync(d_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s));
@@ -233,21 +275,35 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         gp.Ty = d_Ty;
         gp.cnty = d_cnty;
         gp.mxp = d_mxp;
+        const int launch_grid = ksync_on ? grid_full : std::min<int>(ctx->sm_count, (int)tiles.size());
+        if (ksync_on) {
+            gp.ksync = KSYNC;
+            gp.ksync_blocks = (gp.num_k + KSYNC - 1) / KSYNC;
+            int *d_wave = (int *)arena_take(ctx, sizeof(int) * std::max<size_t>(wave_tiles.size(), 1));
+            int *d_sync = (int *)arena_take(ctx, sizeof(int) * std::max<size_t>(wave_tiles.size() * (size_t)gp.ksync_blocks, 1));
+            if (!d_wave || !d_sync) return CUSK_E_CUDA;
+            CUSK_CUDA(cudaMemcpyAsync(d_wave, wave_tiles.data(), sizeof(int) * wave_tiles.size(), cudaMemcpyHostToDevice, s));
+            CUSK_CUDA(cudaMemsetAsync(d_sync, 0, sizeof(int) * wave_tiles.size() * (size_t)gp.ksync_blocks, s));
+            gp.wave_tiles = d_wave;
+            gp.sync = d_sync;
+        }
         if (l0) {
             gp.l0_bits = l0->bits;
             gp.l0_rw = l0->rw;
             gp.l0_th = l0->th;
         }
         t_gram.start();
-        rc = launch_gram(s, map_a, map_b, gp, std::min<int>(ctx->sm_count, (int)tiles.size()));
+        rc = launch_gram(s, map_a, map_b, gp, launch_grid);
         if (rc) return rc;
         t_gram.stop();
         CUSK_CUDA(cudaGetLastError());
         CUSK_CUDA(cudaStreamSynchronize(s));  // the host tile list must outlive the copy
         if (st) {
             st->parts = parts;
-            st->gram_tiles = (int)tiles.size();
-            st->gram_int8_ops = (int64_t)tiles.size() * 2 * 128 * 256 * (int64_t)Kp;
+            size_t real_tiles = 0;
+            for (const int2 &t : tiles) real_tiles += t.x >= 0;
+            st->gram_tiles = (int)real_tiles;
+            st->gram_int8_ops = (int64_t)real_tiles * 2 * 128 * 256 * (int64_t)Kp;
         }
     }
     // tensor-core mxp route: d_mxp is valid here whether this call computed it (trait tiles above) or the caller's

@@ -40,6 +40,13 @@ struct GramParams {
     uint32_t *l0_bits;
     int l0_rw;
     double l0_th;
+    // K-panel synchronisation of a wave (the `grid` consecutive tiles that run together): every ksync k-steps the TMA
+    // producers of the wave's CTAs meet at a counter, so that the CTAs sharing A / B panels read them within the same
+    // L2 window.  wave_tiles[w] = real tiles of wave w (entries with tile.x < 0 are padding), sync[w * ksync_blocks +
+    // kb / ksync] the counters (zeroed by the caller); ksync == 0: off
+    int ksync, ksync_blocks;
+    const int *wave_tiles;
+    int *sync;
 };
 
 struct Level0Fuse {  // corr_block_device: the level-0 adjacency comes out of the correlation pass

@@ -171,7 +171,17 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x) {
                 const int2 tile = p.tiles[t];
+                if (tile.x < 0) continue;  // padding entry of a partial wave
+                const int wave = t / (int)gridDim.x;
                 for (int kb = 0; kb < p.num_k; kb++) {
+                    if (p.ksync && (kb % p.ksync) == 0) {
+                        // every producer of the wave is about to start this K panel: keeps the wave's shared operand
+                        // panels inside the L2 window (without it the CTAs drift apart by thousands of k-steps)
+                        int *c = p.sync + (size_t)wave * p.ksync_blocks + kb / p.ksync;
+                        const int need = p.wave_tiles[wave];
+                        atomicAdd(c, 1);
+                        while (*(volatile int *)c < need) __nanosleep(64);
+                    }
                     mbar_wait(&empty[stage], phase ^ 1);
                     unsigned char *sa = stage_base + stage * STAGE_BYTES;
                     mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
@@ -192,6 +202,7 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             int as = 0;
             uint32_t aphase = 0;
             for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x) {
+                if (p.tiles[t].x < 0) continue;
                 mbar_wait(&tempty[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(as * TILE_N);
@@ -229,6 +240,7 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         uint32_t aphase = 0;
         for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x) {
             const int2 tile = p.tiles[t];
+            if (tile.x < 0) continue;
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + (uint32_t)(as * TILE_N) + ((uint32_t)(q * 32) << 16);

@@ -49,7 +49,13 @@ def main():
 
     torch.cuda.set_device(local_rank)
     if world > 1:
+        saved = os.dup(1)  # NCCL prints its version banner on stdout; keep stdout to the one JSON line
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.barrier()
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
     ctx = cigwas_b200.Context(local_rank)
     if world > 1:
         ids = [cigwas_b200.comm_unique_id() if rank == 0 else None]

@@ -16,7 +16,9 @@ import sys
 METRICS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
            "sm__warps_active.avg.pct_of_peak_sustained_active",
            "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active", "lts__t_sector_hit_rate.pct",
-           "smsp__inst_executed.sum", "launch__registers_per_thread", "sm__throughput.avg.pct_of_peak_sustained_elapsed"]
+           "smsp__inst_executed.sum", "launch__registers_per_thread", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+           "smsp__issue_active.avg.pct_of_peak_sustained_active", "lts__t_bytes.sum",
+           "lts__throughput.avg.pct_of_peak_sustained_elapsed"]
 MULT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "us": 1.0, "ns": 1e-3, "ms": 1e3}
 
 
@@ -39,10 +41,24 @@ def main():
                              dram_read_bytes=val(row, METRICS[1]), dram_write_bytes=val(row, METRICS[2]),
                              warps_active_pct=val(row, METRICS[3]), fp64_pipe_pct=val(row, METRICS[4]),
                              l2_hit_pct=val(row, METRICS[5]), warp_instructions=val(row, METRICS[6]),
-                             registers=val(row, METRICS[7]), sm_throughput_pct=val(row, METRICS[8])))
+                             registers=val(row, METRICS[7]), sm_throughput_pct=val(row, METRICS[8]),
+                             issue_active_pct=val(row, METRICS[9]), l2_bytes=val(row, METRICS[10]),
+                             l2_throughput_pct=val(row, METRICS[11])))
     tot = sum(x["dram_read_bytes"] + x["dram_write_bytes"] for x in launches)
+    tt = sum(x["time_us"] for x in launches)
+    # time-weighted roofs of the same launches: issue slots (the roof these kernels are closest to) and L2
+    issue = sum(x["issue_active_pct"] * x["time_us"] for x in launches) / tt if tt else 0.0
+    l2b = sum(x["l2_bytes"] for x in launches)
+    l2pct = sum(x["l2_throughput_pct"] * x["time_us"] for x in launches) / tt if tt else 0.0
+    fp64 = sum(x["fp64_pipe_pct"] * x["time_us"] for x in launches) / tt if tt else 0.0
     json.dump(dict(source=f"ncu --set full --clock-control none, the {count} level-l CI kernel launches of one C2 step "
-                          f"({rep}; cold-cache, serialised)", bytes_per_step=tot, launches=launches),
+                          f"({rep}; cold-cache, serialised)", bytes_per_step=tot,
+                   bound_measured="issue slots (instruction issue / FP64 latency); DRAM and L2 are far from their peaks",
+                   issue_slot={"achieved_pct_of_peak": issue, "unit": "% of issue slots, time-weighted over the launches",
+                               "fp64_pipe_pct": fp64},
+                   l2={"bytes_per_step": l2b, "achieved_gbps": l2b / (tt * 1e-6) / 1e9 if tt else None,
+                       "pct_of_peak": l2pct},
+                   launches=launches),
               open(out, "w"), indent=1)
     print(f"{'kernel':40s} {'us':>8s} {'rd MB':>8s} {'wr KB':>8s} {'warps%':>7s} {'fp64%':>6s} {'L2hit%':>7s} {'Minst':>7s} regs")
     for x in launches:
