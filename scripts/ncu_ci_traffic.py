@@ -35,6 +35,10 @@ def main():
         x = float(row[ix[k]])
         return x * MULT.get(u[ix[k]], 1.0)
 
+    if count <= 0:  # one step = up to the second launch of the first kernel seen (the capture may hold several steps)
+        first = rows[2][ix["Kernel Name"]]
+        again = [k for k, row in enumerate(rows[3:], start=1) if row[ix["Kernel Name"]] == first]
+        count = again[0] if again else len(rows) - 2
     launches = []
     for row in rows[2:2 + count]:
         launches.append(dict(kernel=row[ix["Kernel Name"]].split("(")[0], time_us=val(row, METRICS[0]),
