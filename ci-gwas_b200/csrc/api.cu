@@ -1,6 +1,7 @@
 // api.cu -- host-buffer entry points and the reference's own signatures (drop-in boundary).
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -47,8 +48,8 @@ int host_threads()
         if (v <= 0) {
             const char *lw = getenv("LOCAL_WORLD_SIZE");
             const int ranks = (lw && atoi(lw) > 0) ? atoi(lw) : 1;
-            v = (int)std::thread::hardware_concurrency() / ranks;
-            if (v > 16) v = 16;
+            v = (int)std::thread::hardware_concurrency() / ranks - 1;  // one core per rank stays with the caller's runtime
+            if (v > 12) v = 12;
             if (v < 2) v = 2;
         }
         return v < 1 ? 1 : v;
@@ -78,6 +79,7 @@ public:
             next_.store(0);
             pending_ = (int)workers_.size();
             generation_++;
+            gen_hint_.store(generation_, std::memory_order_release);
         }
         cv_.notify_all();
         work();
@@ -112,6 +114,15 @@ private:
     {
         unsigned long long seen = 0;
         for (;;) {
+            // a call runs three jobs within a couple of milliseconds (two scans, then the expansion after the level
+            // loop): stay awake that long (yielding the core), then sleep.  Waking a sleeping team costs ~1 ms per job.
+            const auto t0 = std::chrono::steady_clock::now();
+            for (unsigned spins = 0; gen_hint_.load(std::memory_order_acquire) == seen; spins++) {
+                if ((spins & 63u) == 63u) {
+                    if (std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(2500)) break;
+                    std::this_thread::yield();
+                }
+            }
             {
                 std::unique_lock<std::mutex> lk(mu_);
                 cv_.wait(lk, [&] { return stop_ || generation_ != seen; });
@@ -133,6 +144,7 @@ private:
     std::atomic<long long> next_{0};
     int pending_ = 0;
     unsigned long long generation_ = 0;
+    std::atomic<unsigned long long> gen_hint_{0};  // generation_ readable without the mutex (spin phase of the workers)
     bool stop_ = false;
 };
 
@@ -142,6 +154,15 @@ void parallel_chunks(size_t total, size_t grain, F fn)
 {
     const long long nchunks = (long long)((total + grain - 1) / grain);
     if (nchunks <= 1 || host_threads() <= 1) {
+        for (long long c = 0; c < nchunks; c++) fn((size_t)c * grain, std::min(total, (size_t)(c + 1) * grain));
+        return;
+    }
+    // CUSK_HOST_POOL=omp: an OpenMP team of the same size instead of the pool (its workers spin between regions: faster
+    // when calls follow each other within a millisecond, wasteful when several ranks share the cores)
+    static const bool use_omp = [] { const char *e = getenv("CUSK_HOST_POOL"); return e && !strcmp(e, "omp"); }();
+    if (use_omp) {
+        const int T = (int)std::min<long long>((long long)host_threads(), nchunks);
+#pragma omp parallel for schedule(dynamic, 1) num_threads(T)
         for (long long c = 0; c < nchunks; c++) fn((size_t)c * grain, std::min(total, (size_t)(c + 1) * grain));
         return;
     }

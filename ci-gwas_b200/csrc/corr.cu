@@ -215,36 +215,17 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
                             if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m)
                                 tiles.push_back({tm, tn});
         } else {
-            // one wave = `grid_full` consecutive entries = whole super-blocks (small ones share a wave), padded with
-            // {-1, -1}; the trait tiles pushed above form the first wave(s)
-            auto close_wave = [&]() {
-                const size_t fill = tiles.size() % (size_t)grid_full;
-                int real = (int)(fill ? fill : (tiles.empty() ? 0 : (size_t)grid_full));
-                if (fill)
-                    for (size_t k = fill; k < (size_t)grid_full; k++) tiles.push_back({-1, -1});
-                if (real) wave_tiles.push_back(real);
-            };
-            // trait tiles: count waves already filled by them
-            while ((wave_tiles.size() + 1) * (size_t)grid_full <= tiles.size()) wave_tiles.push_back(grid_full);
-            std::vector<int2> sb;
+            // tiles in super-block order; a wave is simply `grid_full` consecutive tiles (the tail of one super-block
+            // and the head of the next may share a wave: two super-blocks' panels still fit the L2 window, and no
+            // slot of a wave idles -- padding the waves to whole super-blocks left 14 % of the slots empty)
             for (int sn = ((n_tn - 1) / SB_N) * SB_N; sn >= 0; sn -= SB_N)
-                for (int sm = 0; sm < n_tm; sm += SB_M) {
-                    sb.clear();
+                for (int sm = 0; sm < n_tm; sm += SB_M)
                     for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
                         for (int tm = sm; tm < std::min(sm + SB_M, n_tm); tm++)
-                            if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m) sb.push_back({tm, tn});
-                    if (sb.empty()) continue;
-                    const size_t fill = tiles.size() % (size_t)grid_full;
-                    if (fill + sb.size() > (size_t)grid_full) close_wave();
-                    for (const int2 &t : sb) {
-                        tiles.push_back(t);
-                        if (tiles.size() % (size_t)grid_full == 0) wave_tiles.push_back(grid_full);
-                    }
-                }
-            {
-                const size_t fill = tiles.size() % (size_t)grid_full;
-                if (fill) wave_tiles.push_back((int)fill);
-            }
+                            if ((size_t)(2 * tn + 2) * MI > (size_t)tm * MI + 1 && (size_t)tm * MI < m)
+                                tiles.push_back({tm, tn});
+            for (size_t w = 0; w * (size_t)grid_full < tiles.size(); w++)
+                wave_tiles.push_back((int)std::min<size_t>((size_t)grid_full, tiles.size() - w * (size_t)grid_full));
         }
         int2 *d_tiles = (int2 *)arena_take(ctx, sizeof(int2) * std::max<size_t>(tiles.size(), 1));
         if (!d_tiles) return CUSK_E_CUDA;
