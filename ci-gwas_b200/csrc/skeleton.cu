@@ -12,10 +12,13 @@
 // launch wrappers (skeleton_kernels.cu, ci_level.cu)
 void launch_level0(cudaStream_t st, bool het, const float *C, const float *N, float n_uniform, const int *G_in,
                    int n, int rw, double th, uint32_t *bits, float *pMax);
-void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
-                        int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
-                        double th_het, float n_uniform, int *work_counter, int *work_counter_small,
-                        int *work_counter_mid, int world, int sm_count, u64 shard_min_tests);
+cudaError_t launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
+                               int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
+                               double th_het, float n_uniform, int *work_counter, int *work_counter_small,
+                               int *work_counter_mid, int world, int sm_count, u64 shard_min_tests, bool fused = false,
+                               int *adj = nullptr, u64 *minkey = nullptr, CiItem *items = nullptr,
+                               CiItem *items_small = nullptr, CiItem *items_mid = nullptr, int item_cap = 0);
+bool plan_compact_fusable(int n, int sm_count);
 unsigned ci_classes_possible(int l, int maxdeg);
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,
                     u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
@@ -163,6 +166,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     // level can need at all, and ends the loop at the first level no row can reach (src/cuPC-S.cu:154-159).
     int maxdeg_bound = 2147483647;
     int l_stop = maxl + 1;  // first level whose kernels were not launched
+    const bool fusable = plan_compact_fusable(n, ctx->sm_count);
     for (int l = 1; l <= maxl; l++) {
         if (maxdeg_bound - 1 < l) {
             l_stop = l;
@@ -171,9 +175,13 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         CUSK_CUDA(cudaEventRecord(ev[l], st));
         LevelCtl *ctl = d_ctl + l;
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
-        nl++, launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
-                           a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l, d_work_small + l,
-                           d_work_mid + l, sh ? sh->world : 1, ctx->sm_count, shard_min_tests);
+        // from level 2 on (the CSR arrays exist) the plan and the compaction are one launch when the grid fits the device
+        const bool fused = l >= 2 && fusable;
+        nl++;
+        CUSK_CUDA(launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
+                                     a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l,
+                                     d_work_small + l, d_work_mid + l, sh ? sh->world : 1, ctx->sm_count, shard_min_tests,
+                                     fused, d_adj, d_minkey, d_items, d_items_small, d_items_mid, item_cap));
         if (l == 1) {
             // the only mid-call synchronisation: directed edge count after level 0
             LevelCtl h;
@@ -220,8 +228,9 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         // that the host never has to read the plan back: one fixed-size stream-ordered collective per level.
         if (sh && d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, std::max<size_t>(flag_stride, 16), st));
         const unsigned classes = ci_classes_possible(l, maxdeg_bound);
-        nl++, launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
-                       d_items_small, d_items_mid, item_cap);
+        if (!fused)
+            nl++, launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
+                                 d_items_small, d_items_mid, item_cap);
         CiParams p;
         p.C = a.dC;
         p.N = a.het ? dN : nullptr;

@@ -37,6 +37,8 @@ struct LevelCtl {
     unsigned ticket;
     int shard_on;  // edge-sharded mode: 1 = this level's work items are dealt over the ranks (enough tests to pay for the exchange)
     u64 acc_mid;
+    int plan_ready;  // fused plan + compaction: set by the planning CTA once the level's plan is in memory
+    int pad3;
 };
 
 // One work item of the CI kernel, decoded once per level by items_kernel (the CI kernel's CTAs then

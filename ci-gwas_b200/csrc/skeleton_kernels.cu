@@ -214,6 +214,62 @@ __device__ __forceinline__ u64 ceil_div_u64(u64 a, u64 b)
     return (a - 1) / b + 1;
 }
 
+// One row of the compaction and its work items (a warp): shared by compact_kernel and the fused tail of
+// degree_plan_kernel.  The plan's arrays are read through L2 (another CTA wrote them in the fused kernel).
+__device__ __forceinline__ void compact_row(int r, int lane, const uint32_t *__restrict__ bits, int rw,
+                                            const int *rowptr, int *__restrict__ adj, u64 *__restrict__ minkey,
+                                            const int *deg, const int *itemstart, const u64 *chunk, int l,
+                                            CiItem *__restrict__ items, CiItem *__restrict__ items_small,
+                                            CiItem *__restrict__ items_mid, int item_cap)
+{
+    const int row0 = __ldcg(&rowptr[r]);
+    // the row's work items (row, degree, CSR offset, rank range) into the table of its CI kernel
+    {
+        const u64 chx = __ldcg(&chunk[r]);
+        if (chx != 0) {
+            const int dd = __ldcg(&deg[r]);
+            const u64 nc = binom64(dd, l);
+            const u64 cnt = ceil_div_u64(nc, chx);
+            const int is = __ldcg(&itemstart[r]);
+            const int cls = is >> 24;
+            CiItem *table = (cls == 1) ? items_small : ((cls == 2) ? items_mid : items);
+            const u64 off = (u64)(is & 0xffffff);
+            for (u64 k = lane; k < cnt; k += 32) {
+                if (off + k >= (u64)item_cap) break;
+                const u64 r0 = k * chx;
+                CiItem it;
+                it.X = r;
+                it.d = dd;
+                it.row0 = row0;
+                it.pad = 0;
+                it.R0 = r0;
+                it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
+                table[off + k] = it;
+            }
+        }
+    }
+    int out = row0;
+    for (int w0 = 0; w0 < rw; w0 += 32) {
+        const int w = w0 + lane;
+        uint32_t word = (w < rw) ? bits[(size_t)r * rw + w] : 0u;
+        const int cnt = __popc(word);
+        int inc = cnt;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        int pos = out + inc - cnt;
+        while (word) {
+            const int b = __ffs(word) - 1;
+            word &= word - 1;
+            adj[pos] = w * 32 + b;
+            if (minkey) minkey[pos] = CUSK_KEY_NONE;
+            pos++;
+        }
+        out += __shfl_sync(0xffffffffu, inc, 31);
+    }
+}
+
 // Degrees and level plan in one launch.  Row phase (every CTA, a warp per row): popcount of the bitmap
 // row, C(d, l) and the row's share of the level totals.  The CTA that finishes last then plans the level:
 // CSR offsets, whether the level runs (src/cuPC-S.cu:154-159: iff max_degree - 1 >= l), the work items of
@@ -226,7 +282,10 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                                                            int *work_counter_small, int *work_counter_mid, int world,
                                                            int ipsm_shallow, int ipsm_deep, int ipsm_small, int ipsm_mid,
                                                            int dfs_span, int dfs_dmin, int dfs_lnarrow, int ipsm_dfs, int sm_count,
-                                                           u64 shard_min_tests)
+                                                           u64 shard_min_tests, int fuse_compact, int *__restrict__ adj,
+                                                           u64 *__restrict__ minkey, CiItem *__restrict__ items,
+                                                           CiItem *__restrict__ items_small, CiItem *__restrict__ items_mid,
+                                                           int item_cap)
 {
     __shared__ u64 s_warp2[66];
     __shared__ u64 s_acc[4];
@@ -292,7 +351,22 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         s_last = (atomicAdd(&ctl->ticket, 1u) == gridDim.x - 1) ? 1 : 0;
     }
     __syncthreads();
-    if (!s_last) return;
+    if (!s_last) {
+        if (!fuse_compact) return;
+        // Fused compaction (the host only asks for it when the whole grid is resident at once): wait for the
+        // planning CTA, then compact this CTA's 32 rows -- one launch per level instead of two.
+        if (tid == 0) {
+            while (atomicAdd(&ctl->plan_ready, 0) == 0) __nanosleep(200);
+            __threadfence();
+        }
+        __syncthreads();
+        if (*(volatile int *)&ctl->done) return;
+        const int r = blockIdx.x * 32 + wid;
+        if (r < n)
+            compact_row(r, lane, bits, rw, rowptr, adj, minkey, deg, itemstart, chunk, l, items, items_small, items_mid,
+                        item_cap);
+        return;
+    }
     __threadfence();
     // ---- plan phase (one CTA) ----------------------------------------------------------------------------
     const int maxdeg = *(volatile int *)&ctl->acc_maxdeg;
@@ -406,6 +480,20 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
         ctl->shard_on = (runs && world > 1 && tot_tests + tot_small + tot_mid >= shard_min_tests) ? 1 : 0;
         ctl->done = runs ? 0 : 1;
     }
+    if (!fuse_compact) return;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        atomicExch(&ctl->plan_ready, 1);
+    }
+    if (!runs) return;
+    {
+        const int r = blockIdx.x * 32 + wid;
+        if (r < n)
+            compact_row(r, lane, bits, rw, rowptr, adj, minkey, deg, itemstart, chunk, l, items, items_small, items_mid,
+                        item_cap);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -425,52 +513,7 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint32_t *__restrict
     const int lane = threadIdx.x & 31;
     const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (r >= n) return;
-    // the row's work items (row, degree, CSR offset, rank range) into the table of its CI kernel
-    {
-        const u64 chx = chunk[r];
-        if (chx != 0) {
-            const int dd = deg[r];
-            const u64 nc = binom64(dd, l);
-            const u64 cnt = ceil_div_u64(nc, chx);
-            const int is = itemstart[r];
-            const int cls = is >> 24;
-            CiItem *table = (cls == 1) ? items_small : ((cls == 2) ? items_mid : items);
-            const u64 off = (u64)(is & 0xffffff);
-            const int row0 = rowptr[r];
-            for (u64 k = lane; k < cnt; k += 32) {
-                if (off + k >= (u64)item_cap) break;
-                const u64 r0 = k * chx;
-                CiItem it;
-                it.X = r;
-                it.d = dd;
-                it.row0 = row0;
-                it.pad = 0;
-                it.R0 = r0;
-                it.R1 = (r0 + chx < nc) ? r0 + chx : nc;
-                table[off + k] = it;
-            }
-        }
-    }
-    int out = rowptr[r];
-    for (int w0 = 0; w0 < rw; w0 += 32) {
-        const int w = w0 + lane;
-        uint32_t word = (w < rw) ? bits[(size_t)r * rw + w] : 0u;
-        const int cnt = __popc(word);
-        int inc = cnt;
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        int pos = out + inc - cnt;
-        while (word) {
-            const int b = __ffs(word) - 1;
-            word &= word - 1;
-            adj[pos] = w * 32 + b;
-            if (minkey) minkey[pos] = CUSK_KEY_NONE;
-            pos++;
-        }
-        out += __shfl_sync(0xffffffffu, inc, 31);
-    }
+    compact_row(r, lane, bits, rw, rowptr, adj, minkey, deg, itemstart, chunk, l, items, items_small, items_mid, item_cap);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -711,18 +754,49 @@ unsigned ci_classes_possible(int l, int maxdeg)
     return mask;
 }
 
-void launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
-                        int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
-                        double th_het, float n_uniform, int *work_counter, int *work_counter_small,
-                        int *work_counter_mid, int world, int sm_count, u64 shard_min_tests)
+// The level's degrees + plan, and (fused = true) its compaction too, as one launch.  The fused form makes CTAs wait
+// for the planning CTA, so it is a cooperative launch (the driver only starts it when the whole grid is resident: two
+// host slots driving the same GPU cannot wedge each other) and only offered when the grid fits the device at once.
+bool plan_compact_fusable(int n, int sm_count)
+{
+    static int occ = -1;
+    static int coop = -1;
+    if (occ < 0) {
+        const char *e = getenv("CUSK_FUSE_PLAN");
+        int dev = 0, o = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        if (e && atoi(e) == 0) coop = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, degree_plan_kernel, 1024, 0);
+        occ = o;
+    }
+    return coop > 0 && occ > 0 && (n + 31) / 32 <= occ * (sm_count > 0 ? sm_count : 148);
+}
+
+cudaError_t launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int rw, int *deg, int l, int *rowptr,
+                               int *itemstart, u64 *chunk, LevelCtl *ctl, const LevelCtl *prev, double th_level,
+                               double th_het, float n_uniform, int *work_counter, int *work_counter_small,
+                               int *work_counter_mid, int world, int sm_count, u64 shard_min_tests, bool fused, int *adj,
+                               u64 *minkey, CiItem *items, CiItem *items_small, CiItem *items_mid, int item_cap)
 {
     const PlanKnobs &k = plan_knobs();
     const DfsTuning dt = dfs_tuning();
-    degree_plan_kernel<<<(n + 31) / 32, 1024, 0, st>>>(bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl, prev,
-                                                       th_level, th_het, n_uniform, work_counter,
-                                                       work_counter_small, work_counter_mid, world, k.ipsm_shallow,
-                                                       k.ipsm_deep, k.ipsm_small, k.ipsm_mid, dt.span, dt.dmin, dt.lnarrow, dt.ipsm,
-                                                       sm_count > 0 ? sm_count : 148, shard_min_tests);
+    int ipsm_shallow = k.ipsm_shallow, ipsm_deep = k.ipsm_deep, ipsm_small = k.ipsm_small, ipsm_mid = k.ipsm_mid;
+    int span = dt.span, dmin = dt.dmin, lnarrow = dt.lnarrow, ipsm_dfs = dt.ipsm;
+    int smc = sm_count > 0 ? sm_count : 148, fuse = fused ? 1 : 0;
+    if (!fused) {
+        degree_plan_kernel<<<(n + 31) / 32, 1024, 0, st>>>(bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl, prev, th_level,
+                                                           th_het, n_uniform, work_counter, work_counter_small,
+                                                           work_counter_mid, world, ipsm_shallow, ipsm_deep, ipsm_small,
+                                                           ipsm_mid, span, dmin, lnarrow, ipsm_dfs, smc, shard_min_tests, 0,
+                                                           nullptr, nullptr, nullptr, nullptr, nullptr, 0);
+        return cudaGetLastError();
+    }
+    void *args[] = {&bits, &n, &rw, &deg, &l, &rowptr, &itemstart, &chunk, &ctl, &prev, &th_level, &th_het, &n_uniform,
+                    &work_counter, &work_counter_small, &work_counter_mid, &world, &ipsm_shallow, &ipsm_deep, &ipsm_small,
+                    &ipsm_mid, &span, &dmin, &lnarrow, &ipsm_dfs, &smc, &shard_min_tests, &fuse, &adj, &minkey, &items,
+                    &items_small, &items_mid, &item_cap};
+    return cudaLaunchCooperativeKernel((const void *)degree_plan_kernel, dim3((n + 31) / 32), dim3(1024), args, 0, st);
 }
 
 void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const int *rowptr, int *adj,

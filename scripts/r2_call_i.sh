@@ -16,5 +16,11 @@ for v in pool omp; do
   CUSK_HOST_POOL=$v timeout 300 python bench.py --no-extras --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > "$OUT/bench_host_$v.json" 2>> "$OUT/bench.err"
 done
 CUSK_HOST_THREADS=8 timeout 300 python bench.py --no-extras --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > "$OUT/bench_host_pool8.json" 2>> "$OUT/bench.err"
+CUSK_FUSE_PLAN=0 timeout 300 python bench.py --no-extras --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > "$OUT/bench_nofuseplan.json" 2>> "$OUT/bench.err"
+CUSK_FUSE_PLAN=0 timeout 600 python -m pytest tests/test_skeleton_gpu.py -m gpu -q > "$OUT/tests_skeleton_nofuseplan.log" 2>&1
+echo "skeleton tests, plan and compaction as two launches: exit $?" | tee -a "$OUT/summary.txt"
+timeout 300 python bench.py --steps 1 --warmup 1 --no-extras --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > /dev/null 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file "$OUT/launches_bench_steps1.csv" \
+  python bench.py --steps 1 --warmup 1 --no-extras --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > "$OUT/ncu_bench.log" 2>&1
 echo "bench host variants: done" | tee -a "$OUT/summary.txt"
 cat "$OUT/summary.txt"
