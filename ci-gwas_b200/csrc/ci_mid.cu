@@ -99,62 +99,92 @@ __global__ void __launch_bounds__(CM_NTHREADS) ci_mid_kernel(const CiParams p)
             }
             __syncthreads();
         }
-        if (LT == 1) {
-            // Level 1, a LANE per neighbour y and a loop over the conditioning variable z (round 2; it was a thread per
-            // (z, 32 y)): everything that belongs to y -- its column, C[x,y], its time bound, whether the edge is still
-            // there -- stays in registers, what belongs to z is one broadcast read per warp, and the gather
-            // C[adj z][adj y] (= C[adj y][adj z]: the matrix is symmetric) has adjacent lanes on adjacent columns of
-            // ONE row.  A warp takes (32-neighbour chunk, piece of CM_ZB consecutive z) units; the piece's gathers are
-            // all in flight before the first test.  ~25 instructions per test instead of ~70.
-            constexpr unsigned CM_ZB = 8;
-            const unsigned nranks = R1 - R0;
-            const unsigned nych = (unsigned)(d + 31) >> 5;
-            const unsigned nzp = (nranks + CM_ZB - 1) / CM_ZB;
-            const unsigned units = nych * nzp;
-            unsigned ntests = 0;
-            for (unsigned u = (unsigned)(tid >> 5); u < units; u += CM_NTHREADS / 32) {
-                const unsigned ych = u % nych, zp = u / nych;
-                const int y = (int)ych * 32 + lane;
-                const bool yin = y < d;
-                const int yc = yin ? y : d - 1;
-                const int adjy = s_adj[yc];
-                const double cxy = (double)s_cx[yc];
-                const int tmax = use_time ? max(tX, s_time[yc]) : 2147483647;
-                bool dead = !yin || (HET && s_skip[yc] != 0);
-                unsigned long long mk = HET ? 0ull : s_minkey[yc];
-                const unsigned z0 = R0 + zp * CM_ZB;
-                const unsigned z1 = (z0 + CM_ZB < R1) ? z0 + CM_ZB : R1;
-                float cz[CM_ZB];
+        const unsigned nranks = R1 - R0;
+        const unsigned nych = (unsigned)(d + 31) >> 5;
+        const unsigned units = nranks * nych;
+        for (unsigned u = tid; u < units; u += CM_NTHREADS) {
+            const unsigned ych = u / nranks;
+            const unsigned R = R0 + (u - ych * nranks);
+            const int y0 = (int)ych * 32, y1 = min(d, y0 + 32);
+            // ---- the set and its factor -----------------------------------------------------------
+            int p0, p1 = -1;
+            if (LT == 1) {
+                p0 = (int)R;
+            } else {
+                // lexicographic rank of {p0 < p1}: d - 1 - p0 sets start with p0
+                unsigned rank = R;
+                int x = 0;
+                for (;; x++) {
+                    const unsigned c = (unsigned)(d - 1 - x);
+                    if (rank < c) break;
+                    rank -= c;
+                }
+                p0 = x;
+                p1 = x + 1 + (int)rank;
+            }
+            const double tx0 = (double)s_cx[p0];
+            double h00 = 1.0 - tx0 * tx0;
+            double l10 = 0.0, invD1 = 0.0, txd1 = 0.0;
+            int tS = use_time ? s_time[p0] : 0;
+            if (LT == 2) {
+                l10 = (double)csub[p1 * stride + p0];
+                const double D1 = 1.0 - l10 * l10;
+                invD1 = (fabs(D1) < CI_PIVOT_TOL) ? 0.0 : 1.0 / D1;
+                const double tx1 = (double)s_cx[p1] - l10 * tx0;
+                txd1 = tx1 * invD1;
+                h00 -= tx1 * txd1;
+                if (use_time) tS = max(tS, s_time[p1]);
+            }
+            const double c2 = fabs(h00);
+            double SP = 0.0;
+            if (het_general) {
+                const size_t row0n = (size_t)s_adj[p0] * n;
+                SP = (double)__float2int_rz(p.N[row0n + X]);
+                if (LT == 2) {
+                    const size_t row1n = (size_t)s_adj[p1] * n;
+                    SP += (double)__float2int_rz(p.N[row1n + X]) + (double)__float2int_rz(p.N[row1n + s_adj[p0]]);
+                }
+            }
+            const float *ccol = p.C + s_adj[p0];  // level 1: C[adj(y), adj(z)] read from L2
+            for (int yb = y0; yb < y1; yb += 4) {
+                float cy0[4];
+                bool live[4];
 #pragma unroll
-                for (unsigned q = 0; q < CM_ZB; q++) {
-                    const unsigned z = z0 + q;
-                    cz[q] = (z < z1 && !dead) ? __ldg(&p.C[(size_t)s_adj[z] * n + adjy]) : 0.f;
+                for (int q = 0; q < 4; q++) {
+                    const int y = yb + q;
+                    live[q] = (y < y1) && (y != p0) && (y != p1);
+                    if (live[q]) {
+                        if (HET) {
+                            if (s_skip[y]) live[q] = false;
+                            if (use_time && tS > max(tX, s_time[y])) live[q] = false;
+                        } else {
+                            if (s_minkey[y] < (unsigned long long)R) live[q] = false;
+                        }
+                    }
+                    cy0[q] = 0.f;
+                    if (live[q]) cy0[q] = (LT == 1) ? __ldg(ccol + (size_t)s_adj[y] * n) : csub[y * stride + p0];
                 }
 #pragma unroll
-                for (unsigned q = 0; q < CM_ZB; q++) {
-                    const unsigned z = z0 + q;
-                    if (z >= z1) break;
-                    bool live = !dead && (y != (int)z);
-                    if (HET) {
-                        if (use_time && s_time[z] > tmax) live = false;
-                    } else {
-                        if (mk < (unsigned long long)z) live = false;
+                for (int q = 0; q < 4; q++) {
+                    if (!live[q]) continue;
+                    const int y = yb + q;
+                    my_tests++;
+                    const double ty0 = (double)cy0[q];
+                    double h01 = (double)s_cx[y] - ty0 * tx0;
+                    double h11 = 1.0 - ty0 * ty0;
+                    if (LT == 2) {
+                        const double ty1 = (double)csub[y * stride + p1] - l10 * ty0;
+                        h01 -= ty1 * txd1;
+                        h11 -= ty1 * ty1 * invD1;
                     }
-                    if (!live) continue;
-                    ntests++;
-                    const double tx0 = (double)s_cx[z];
-                    const double c2 = fabs(1.0 - tx0 * tx0);
-                    const double ty0 = (double)cz[q];
-                    const double h01 = cxy - ty0 * tx0;
-                    const double h11 = 1.0 - ty0 * ty0;
                     const double lhs = h01 * h01;
                     const double den = c2 * fabs(h11);
                     double T2 = T2u;
                     if (het_general) {
-                        const int Y = adjy, Z = s_adj[z];
-                        const double sum = (double)__float2int_rz(p.N[(size_t)Z * n + X]) +
-                                           (double)__float2int_rz(p.N[(size_t)Y * n + X]) +
-                                           (double)__float2int_rz(p.N[(size_t)Z * n + Y]);
+                        const int Y = s_adj[y];
+                        double sum = SP + (double)__float2int_rz(p.N[(size_t)Y * n + X]) +
+                                     (double)__float2int_rz(p.N[(size_t)s_adj[p0] * n + Y]);
+                        if (LT == 2) sum += (double)__float2int_rz(p.N[(size_t)s_adj[p1] * n + Y]);
                         const double m = sum / npairs;
                         const double th = p.th_het / sqrt(m - (double)l - 3.0);
                         const double t = tanh(th);
@@ -163,126 +193,15 @@ __global__ void __launch_bounds__(CM_NTHREADS) ci_mid_kernel(const CiParams p)
                     // |rho| < tanh(th)  or, on the |rho| > 1 branch, |rho| > coth(th)
                     const bool rem = (lhs < T2 * den) || (den > 0.0 && lhs * T2 > den);
                     if (rem) {
+                        const int Y = s_adj[y];
                         if (HET) {
-                            atomicAnd(&p.bits[(size_t)X * p.rw + (adjy >> 5)], ~(1u << (adjy & 31)));
-                            atomicAnd(&p.bits[(size_t)adjy * p.rw + (X >> 5)], ~(1u << (X & 31)));
+                            atomicAnd(&p.bits[(size_t)X * p.rw + (Y >> 5)], ~(1u << (Y & 31)));
+                            atomicAnd(&p.bits[(size_t)Y * p.rw + (X >> 5)], ~(1u << (X & 31)));
                             if (p.removed) p.removed[row0 + y] = 1;
                             s_skip[y] = 1;
-                            dead = true;
                         } else {
-                            atomicMin(&p.minkey[row0 + y], (u64)z);
-                            atomicMin(&s_minkey[y], (unsigned long long)z);
-                            mk = (unsigned long long)z < mk ? (unsigned long long)z : mk;
-                        }
-                    }
-                }
-            }
-            my_tests += ntests;
-        } else {
-            const unsigned nranks = R1 - R0;
-            const unsigned nych = (unsigned)(d + 31) >> 5;
-            const unsigned units = nranks * nych;
-            for (unsigned u = tid; u < units; u += CM_NTHREADS) {
-                const unsigned ych = u / nranks;
-                const unsigned R = R0 + (u - ych * nranks);
-                const int y0 = (int)ych * 32, y1 = min(d, y0 + 32);
-                // ---- the set and its factor -----------------------------------------------------------
-                int p0, p1 = -1;
-                if (LT == 1) {
-                    p0 = (int)R;
-                } else {
-                    // lexicographic rank of {p0 < p1}: d - 1 - p0 sets start with p0
-                    unsigned rank = R;
-                    int x = 0;
-                    for (;; x++) {
-                        const unsigned c = (unsigned)(d - 1 - x);
-                        if (rank < c) break;
-                        rank -= c;
-                    }
-                    p0 = x;
-                    p1 = x + 1 + (int)rank;
-                }
-                const double tx0 = (double)s_cx[p0];
-                double h00 = 1.0 - tx0 * tx0;
-                double l10 = 0.0, invD1 = 0.0, txd1 = 0.0;
-                int tS = use_time ? s_time[p0] : 0;
-                if (LT == 2) {
-                    l10 = (double)csub[p1 * stride + p0];
-                    const double D1 = 1.0 - l10 * l10;
-                    invD1 = (fabs(D1) < CI_PIVOT_TOL) ? 0.0 : 1.0 / D1;
-                    const double tx1 = (double)s_cx[p1] - l10 * tx0;
-                    txd1 = tx1 * invD1;
-                    h00 -= tx1 * txd1;
-                    if (use_time) tS = max(tS, s_time[p1]);
-                }
-                const double c2 = fabs(h00);
-                double SP = 0.0;
-                if (het_general) {
-                    const size_t row0n = (size_t)s_adj[p0] * n;
-                    SP = (double)__float2int_rz(p.N[row0n + X]);
-                    if (LT == 2) {
-                        const size_t row1n = (size_t)s_adj[p1] * n;
-                        SP += (double)__float2int_rz(p.N[row1n + X]) + (double)__float2int_rz(p.N[row1n + s_adj[p0]]);
-                    }
-                }
-                const float *ccol = p.C + s_adj[p0];  // level 1: C[adj(y), adj(z)] read from L2
-                for (int yb = y0; yb < y1; yb += 4) {
-                    float cy0[4];
-                    bool live[4];
-    #pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        const int y = yb + q;
-                        live[q] = (y < y1) && (y != p0) && (y != p1);
-                        if (live[q]) {
-                            if (HET) {
-                                if (s_skip[y]) live[q] = false;
-                                if (use_time && tS > max(tX, s_time[y])) live[q] = false;
-                            } else {
-                                if (s_minkey[y] < (unsigned long long)R) live[q] = false;
-                            }
-                        }
-                        cy0[q] = 0.f;
-                        if (live[q]) cy0[q] = (LT == 1) ? __ldg(ccol + (size_t)s_adj[y] * n) : csub[y * stride + p0];
-                    }
-    #pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        if (!live[q]) continue;
-                        const int y = yb + q;
-                        my_tests++;
-                        const double ty0 = (double)cy0[q];
-                        double h01 = (double)s_cx[y] - ty0 * tx0;
-                        double h11 = 1.0 - ty0 * ty0;
-                        if (LT == 2) {
-                            const double ty1 = (double)csub[y * stride + p1] - l10 * ty0;
-                            h01 -= ty1 * txd1;
-                            h11 -= ty1 * ty1 * invD1;
-                        }
-                        const double lhs = h01 * h01;
-                        const double den = c2 * fabs(h11);
-                        double T2 = T2u;
-                        if (het_general) {
-                            const int Y = s_adj[y];
-                            double sum = SP + (double)__float2int_rz(p.N[(size_t)Y * n + X]) +
-                                         (double)__float2int_rz(p.N[(size_t)s_adj[p0] * n + Y]);
-                            if (LT == 2) sum += (double)__float2int_rz(p.N[(size_t)s_adj[p1] * n + Y]);
-                            const double m = sum / npairs;
-                            const double th = p.th_het / sqrt(m - (double)l - 3.0);
-                            const double t = tanh(th);
-                            T2 = t * t;
-                        }
-                        // |rho| < tanh(th)  or, on the |rho| > 1 branch, |rho| > coth(th)
-                        const bool rem = (lhs < T2 * den) || (den > 0.0 && lhs * T2 > den);
-                        if (rem) {
-                            const int Y = s_adj[y];
-                            if (HET) {
-                                atomicAnd(&p.bits[(size_t)X * p.rw + (Y >> 5)], ~(1u << (Y & 31)));
-                                atomicAnd(&p.bits[(size_t)Y * p.rw + (X >> 5)], ~(1u << (X & 31)));
-                                if (p.removed) p.removed[row0 + y] = 1;
-                                s_skip[y] = 1;
-                            } else {
-                                atomicMin(&p.minkey[row0 + y], (u64)R);
-                                atomicMin(&s_minkey[y], (unsigned long long)R);
-                            }
+                            atomicMin(&p.minkey[row0 + y], (u64)R);
+                            atomicMin(&s_minkey[y], (unsigned long long)R);
                         }
                     }
                 }
