@@ -2,7 +2,7 @@
 """bench.py -- CI tests/s of the skeleton hot path on BASELINE.json configs[1] (cuskss single LD block:
 3 000 markers + 17 traits, max level 14, alpha 1e-4, 458 000 samples), one block per GPU per step.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c4|merged] [--same-block]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c4|merged] [--distinct-blocks]
 
 Contract (see the task statement): ONE JSON line on stdout from rank 0.  `value` = CI tests executed per second with
 inputs resident in HBM; `e2e` = the same metric through the reference-facing C-ABI call (`cusk_hetcor_skeleton`: host
@@ -168,7 +168,7 @@ def run_reference_arm(args, rank, world):
     line = {"impl": "reference", "metric": "ci_tests_per_s", "value": val, "unit": "tests/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "generator": dict(C2_KW, seed_stream="2+rank"), "sample": sample},
+            "config": {"workload": WORKLOAD, "generator": dict(C2_KW, seed_stream="2"), "sample": sample},
             "cpu_baseline": {"value": val, "unit": "tests/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "tests/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -515,8 +515,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c4", "merged"])
-    ap.add_argument("--same-block", action="store_true", help="every rank times the SAME block (separates host contention "
-                    "from data variance in the multi-GPU runs)")
+    ap.add_argument("--same-block", action="store_true", default=True,
+                    help="every rank times the SAME block, the one the N=1 run times (default): weak scaling then measures "
+                    "contention, not which blocks the extra ranks happened to draw")
+    ap.add_argument("--distinct-blocks", dest="same_block", action="store_false",
+                    help="rank r times its own block (generator stream 2+r), as rounds 1 and early 2 did")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
     ap.add_argument("--no-pipelined-probe", action="store_true")

@@ -173,14 +173,39 @@ void parallel_chunks(size_t total, size_t grain, F fn)
     HostPool::get().run(nchunks, job);
 }
 
+// OR of (word ^ ref) over cnt 32-bit words, eight bytes at a time
+static inline uint64_t xor_or_u32(const uint32_t *p, size_t cnt, uint32_t ref)
+{
+    uint64_t d = 0;
+    size_t i = 0;
+    if (cnt && ((uintptr_t)p & 4)) {
+        d |= (uint64_t)(p[0] ^ ref);
+        i = 1;
+    }
+    const uint64_t r2 = ((uint64_t)ref << 32) | ref;
+    const uint64_t *q = (const uint64_t *)(p + i);
+    const size_t m = (cnt - i) / 2;
+    uint64_t d0 = 0, d1 = 0, d2 = 0, d3 = 0;
+    size_t k = 0;
+    for (; k + 4 <= m; k += 4) {
+        d0 |= q[k] ^ r2;
+        d1 |= q[k + 1] ^ r2;
+        d2 |= q[k + 2] ^ r2;
+        d3 |= q[k + 3] ^ r2;
+    }
+    for (; k < m; k++) d0 |= q[k] ^ r2;
+    d |= d0 | d1 | d2 | d3;
+    i += 2 * m;
+    if (i < cnt) d |= (uint64_t)(p[i] ^ ref);
+    return d;
+}
+
 bool host_all_ones(const int *G, size_t nn)
 {
     std::atomic<bool> ok{true};
     parallel_chunks(nn, (size_t)1 << 18, [&](size_t a, size_t b) {
         if (!ok.load(std::memory_order_relaxed)) return;
-        int acc = 1;
-        for (size_t i = a; i < b; i++) acc &= (G[i] == 1);
-        if (!acc) ok.store(false, std::memory_order_relaxed);
+        if (xor_or_u32((const uint32_t *)G + a, b - a, 1u)) ok.store(false, std::memory_order_relaxed);
     });
     return ok.load();
 }
@@ -195,18 +220,28 @@ bool host_constant_offdiag(const float *N, int n, float *value)
     std::atomic<bool> ok{true};
     parallel_chunks((size_t)n, 64, [&](size_t r0, size_t r1) {
         if (!ok.load(std::memory_order_relaxed)) return;
+        uint64_t diff = 0;
         for (size_t r = r0; r < r1; r++) {
             const uint32_t *row = (const uint32_t *)(N + r * (size_t)n);
-            uint32_t diff = 0;
-            for (size_t c = 0; c < (size_t)n; c++) diff |= (c == r) ? 0u : (row[c] ^ ref);
-            if (diff) {
-                ok.store(false, std::memory_order_relaxed);
-                return;
-            }
+            diff |= xor_or_u32(row, r, ref) | xor_or_u32(row + r + 1, (size_t)n - r - 1, ref);
         }
+        if (diff) ok.store(false, std::memory_order_relaxed);
     });
     if (ok.load()) *value = N[1];
     return ok.load();
+}
+
+// Scan the caller's G / N on the host (and skip their upload when they are trivial), or upload them and let the device
+// look?  The scan needs host threads: with many ranks on one host each has two or three and the PCIe link of its own GPU is
+// the better tool (measured at 8 ranks on 24 cores: 9.1 ms per call scanning, 2.6 ms at one rank).  CUSK_HOST_SCAN=0/1.
+bool host_scan_enabled()
+{
+    static const bool on = [] {
+        const char *e = getenv("CUSK_HOST_SCAN");
+        if (e) return atoi(e) != 0;
+        return host_threads() >= 6;
+    }();
+    return on;
 }
 
 void host_expand_bits(const uint32_t *bits, int n, int rw, int *G)
@@ -224,15 +259,44 @@ void host_expand_bits(const uint32_t *bits, int n, int rw, int *G)
     });
 }
 
-// device bitmap -> the caller's dense int matrix (pinned staging, host expansion)
-int fetch_adjacency(cusk_ctx *ctx, const uint32_t *dbits, int n, int rw, int *G, int64_t *bytes)
+void host_zero_fill(int *G, size_t nn)
+{
+    parallel_chunks(nn, (size_t)1 << 18, [&](size_t a, size_t b) { memset(G + a, 0, (b - a) * sizeof(int)); });
+}
+
+// the set bits into a matrix that is already zero
+void host_scatter_bits(const uint32_t *bits, int n, int rw, int *G)
+{
+    parallel_chunks((size_t)n, 64, [&](size_t r0, size_t r1) {
+        for (size_t r = r0; r < r1; r++) {
+            const uint32_t *row = bits + r * (size_t)rw;
+            int *out = G + r * (size_t)n;
+            for (int w = 0; w < rw; w++) {
+                uint32_t word = row[w];
+                while (word) {
+                    const int b = __builtin_ctz(word);
+                    word &= word - 1;
+                    const int c = w * 32 + b;
+                    if (c < n) out[c] = 1;
+                }
+            }
+        }
+    });
+}
+
+// device bitmap -> the caller's dense int matrix (pinned staging).  `zeroed`: the matrix was zero-filled while the device
+// worked (ctx->idle_job), only the surviving edges are written; otherwise the host team expands every word.
+int fetch_adjacency(cusk_ctx *ctx, const uint32_t *dbits, int n, int rw, int *G, int64_t *bytes, bool zeroed)
 {
     const size_t nb = (size_t)n * rw * 4;
     uint32_t *h = (uint32_t *)host_stage(ctx, nb);
     if (!h) return CUSK_E_CUDA;
     CUSK_CUDA(cudaMemcpyAsync(h, dbits, nb, cudaMemcpyDeviceToHost, ctx->stream));
     CUSK_CUDA(cudaStreamSynchronize(ctx->stream));
-    host_expand_bits(h, n, rw, G);
+    if (zeroed)
+        host_scatter_bits(h, n, rw, G);
+    else
+        host_expand_bits(h, n, rw, G);
     *bytes += (int64_t)nb;
     return CUSK_OK;
 }
@@ -264,7 +328,14 @@ extern "C" int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const
     cusk_stats *sp = stats ? stats : &local;
     std::vector<cusk_sepset> seps;
     const bool want_seps = SepSet || sep || sep_n;
+    // G is output only (src/cuPC-S.cu:61: the input is ignored): zero it while the device works
+    bool zeroed = false;
+    ctx->idle_job = [&] {
+        host_zero_fill(G, nn);
+        zeroed = true;
+    };
     int rc = skeleton_engine(ctx, dC, n, dbits, Th, maxlevel, l_out, dP, want_seps ? &seps : nullptr, sp);
+    ctx->idle_job = nullptr;
     if (rc) return rc;
     int64_t down = (int64_t)(seps.size() * sizeof(cusk_sepset));
     td2h.start();
@@ -272,7 +343,7 @@ extern "C" int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const
         CUSK_CUDA(cudaMemcpyAsync(pMax, dP, nn * 4, cudaMemcpyDeviceToHost, st));
         down += (int64_t)(nn * 4);
     }
-    rc = fetch_adjacency(ctx, dbits, n, rw, G, &down);
+    rc = fetch_adjacency(ctx, dbits, n, rw, G, &down, zeroed);
     if (rc) return rc;
     td2h.stop();
     if (sep_n) *sep_n = (int64_t)seps.size();
@@ -324,12 +395,13 @@ extern "C" int cusk_hetcor_skeleton(cusk_ctx *ctx, const float *C, int n, int *G
         up += (int64_t)n * 4;
     }
     // while C travels (asynchronously when the caller's buffer is page-locked): is G all ones, is N one constant?
-    const bool all_ones = G_in_all_ones || host_all_ones(G, nn);
+    const bool scan = host_scan_enabled();
+    const bool all_ones = G_in_all_ones || (scan && host_all_ones(G, nn));
     float n_uniform = 0.f;
-    const bool uniform = host_constant_offdiag(N, n, &n_uniform);
+    const bool uniform = scan && host_constant_offdiag(N, n, &n_uniform);
     float *dN = nullptr;
     int *dG = nullptr;
-    if (!uniform) {
+    if (!uniform) {  // the engine looks for a constant N on the device (ess_minmax_kernel)
         dN = (float *)arena_take(ctx->io, nn * 4);
         if (!dN) return CUSK_E_CUDA;
         CUSK_CUDA(cudaMemcpyAsync(dN, N, nn * 4, cudaMemcpyHostToDevice, st));
@@ -341,14 +413,24 @@ extern "C" int cusk_hetcor_skeleton(cusk_ctx *ctx, const float *C, int n, int *G
         CUSK_CUDA(cudaMemcpyAsync(dG, G, nn * 4, cudaMemcpyHostToDevice, st));
         up += (int64_t)(nn * 4);
     }
+    CUSK_CUDA(cudaEventRecord(ctx->ev_inputs, st));
     th2d.stop();
     cusk_stats local;
     cusk_stats *sp = stats ? stats : &local;
+    // once the inputs are on the device nothing reads the caller's G any more: zero it while the device works (the engine
+    // calls idle_job before one of its synchronisations), the surviving edges are written afterwards
+    bool zeroed = false;
+    ctx->idle_job = [&] {
+        if (cudaEventSynchronize(ctx->ev_inputs) != cudaSuccess) return;  // an uploaded G has left the caller's buffer
+        host_zero_fill(G, nn);
+        zeroed = true;
+    };
     int rc = hetcor_engine(ctx, dC, n, dbits, dG, false, dN, n_uniform, th, maxlevel, dT, l_out, sp);
+    ctx->idle_job = nullptr;
     if (rc) return rc;
     int64_t down = 0;
     td2h.start();
-    rc = fetch_adjacency(ctx, dbits, n, rw, G, &down);  // bitmap over PCIe, expanded by the host threads
+    rc = fetch_adjacency(ctx, dbits, n, rw, G, &down, zeroed);  // bitmap over PCIe, expanded by the host threads
     if (rc) return rc;
     td2h.stop();
     sp->h2d_ms = th2d.ms();

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -78,8 +79,21 @@ struct cusk_ctx {
     // [0, ML+2): level boundaries; [ML+2, 3(ML+2)): CI kernel start/stop per level; next 4: copies;
     // [3(ML+2)+4, 5(ML+2)+4): exchange start/stop per level (edge-sharded mode)
     cudaEvent_t ev[5 * (CUSK_ML + 2) + 4];
+    cudaEvent_t ev_inputs = nullptr;  // the host-buffer arguments of the current call have reached the device
     bool ev_ready = false;
+    // host work of the calling entry point that does not depend on the device's result (zero-filling the caller's output
+    // matrix): the engine runs it once, just before one of its stream synchronisations, while the device is busy
+    std::function<void()> idle_job;
 };
+
+inline void run_idle_job(cusk_ctx *ctx)
+{
+    if (ctx->idle_job) {
+        std::function<void()> f = std::move(ctx->idle_job);
+        ctx->idle_job = nullptr;
+        f();
+    }
+}
 
 void arena_reset(Arena &a);                // rewind: all earlier takes become invalid
 void *arena_take(Arena &a, size_t bytes);  // 256-byte aligned; grows by whole blocks; nullptr + error on failure

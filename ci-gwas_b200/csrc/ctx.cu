@@ -62,6 +62,7 @@ extern "C" int cusk_ctx_create(int device_id, cusk_ctx **out)
     ctx->h_pinned_bytes = 1 << 16;
     CUSK_CUDA(cudaMallocHost(&ctx->h_pinned, ctx->h_pinned_bytes));
     for (auto &ev : ctx->ev) CUSK_CUDA(cudaEventCreate(&ev));
+    CUSK_CUDA(cudaEventCreateWithFlags(&ctx->ev_inputs, cudaEventDisableTiming));
     ctx->ev_ready = true;
     *out = ctx;
     return CUSK_OK;
@@ -77,7 +78,10 @@ extern "C" void cusk_ctx_destroy(cusk_ctx *ctx)
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->ev_ready)
+    {
         for (auto &ev : ctx->ev) cudaEventDestroy(ev);
+        if (ctx->ev_inputs) cudaEventDestroy(ctx->ev_inputs);
+    }
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -216,6 +216,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             // rank of an edge-sharded run reads the same numbers, so the ranks keep launching the same sequence.
             LevelCtl h;
             CUSK_CUDA(cudaMemcpyAsync(&h, ctl, sizeof(h), cudaMemcpyDeviceToHost, st));
+            run_idle_job(ctx);  // levels 1-2 are in flight: the caller's host work hides behind them
             CUSK_CUDA(cudaStreamSynchronize(st));
             if (h.done) {
                 l_stop = l;
@@ -317,6 +318,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     unsigned long long *h_sepcount = (unsigned long long *)(h_ctl + CUSK_ML + 2);
     CUSK_CUDA(cudaMemcpyAsync(h_ctl, d_ctl, sizeof(LevelCtl) * (CUSK_ML + 2), cudaMemcpyDeviceToHost, st));
     CUSK_CUDA(cudaMemcpyAsync(h_sepcount, d_sepcount, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    run_idle_job(ctx);
     CUSK_CUDA(cudaStreamSynchronize(st));
 
     if (sh) {
