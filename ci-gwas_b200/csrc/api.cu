@@ -389,42 +389,67 @@ extern "C" int cusk_hetcor_skeleton(cusk_ctx *ctx, const float *C, int n, int *G
     Timer th2d(ctx, 0), td2h(ctx, 1);
     int64_t up = (int64_t)(nn * 4);
     th2d.start();
-    CUSK_CUDA(cudaMemcpyAsync(dC, C, nn * 4, cudaMemcpyHostToDevice, st));
-    if (use_time) {
-        CUSK_CUDA(cudaMemcpyAsync(dT, time_index, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-        up += (int64_t)n * 4;
-    }
-    // while C travels (asynchronously when the caller's buffer is page-locked): is G all ones, is N one constant?
     const bool scan = host_scan_enabled();
-    const bool all_ones = G_in_all_ones || (scan && host_all_ones(G, nn));
     float n_uniform = 0.f;
-    const bool uniform = scan && host_constant_offdiag(N, n, &n_uniform);
     float *dN = nullptr;
     int *dG = nullptr;
-    if (!uniform) {  // the engine looks for a constant N on the device (ess_minmax_kernel)
-        dN = (float *)arena_take(ctx->io, nn * 4);
+    bool zeroed = false;
+    cusk_stats local;
+    cusk_stats *sp = stats ? stats : &local;
+    if (!scan) {
+        // Few host threads (several ranks share the host): everything goes over this GPU's own PCIe link, G first, and the
+        // caller's G is zero-filled as soon as it has left while C and N are still travelling.
+        if (!G_in_all_ones) {
+            dG = (int *)arena_take(ctx->io, nn * 4);
+            if (!dG) return CUSK_E_CUDA;
+            CUSK_CUDA(cudaMemcpyAsync(dG, G, nn * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)(nn * 4);
+        }
+        CUSK_CUDA(cudaEventRecord(ctx->ev_inputs, st));
+        CUSK_CUDA(cudaMemcpyAsync(dC, C, nn * 4, cudaMemcpyHostToDevice, st));
+        if (use_time) {
+            CUSK_CUDA(cudaMemcpyAsync(dT, time_index, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)n * 4;
+        }
+        dN = (float *)arena_take(ctx->io, nn * 4);  // the engine looks for a constant N on the device (ess_minmax_kernel)
         if (!dN) return CUSK_E_CUDA;
         CUSK_CUDA(cudaMemcpyAsync(dN, N, nn * 4, cudaMemcpyHostToDevice, st));
         up += (int64_t)(nn * 4);
-    }
-    if (!all_ones) {
-        dG = (int *)arena_take(ctx->io, nn * 4);
-        if (!dG) return CUSK_E_CUDA;
-        CUSK_CUDA(cudaMemcpyAsync(dG, G, nn * 4, cudaMemcpyHostToDevice, st));
-        up += (int64_t)(nn * 4);
-    }
-    CUSK_CUDA(cudaEventRecord(ctx->ev_inputs, st));
-    th2d.stop();
-    cusk_stats local;
-    cusk_stats *sp = stats ? stats : &local;
-    // once the inputs are on the device nothing reads the caller's G any more: zero it while the device works (the engine
-    // calls idle_job before one of its synchronisations), the surviving edges are written afterwards
-    bool zeroed = false;
-    ctx->idle_job = [&] {
-        if (cudaEventSynchronize(ctx->ev_inputs) != cudaSuccess) return;  // an uploaded G has left the caller's buffer
+        th2d.stop();
+        CUSK_CUDA(cudaEventSynchronize(ctx->ev_inputs));
         host_zero_fill(G, nn);
         zeroed = true;
-    };
+    } else {
+        CUSK_CUDA(cudaMemcpyAsync(dC, C, nn * 4, cudaMemcpyHostToDevice, st));
+        if (use_time) {
+            CUSK_CUDA(cudaMemcpyAsync(dT, time_index, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)n * 4;
+        }
+        // while C travels (asynchronously when the caller's buffer is page-locked): is G all ones, is N one constant?
+        const bool all_ones = G_in_all_ones || host_all_ones(G, nn);
+        const bool uniform = host_constant_offdiag(N, n, &n_uniform);
+        if (!uniform) {
+            dN = (float *)arena_take(ctx->io, nn * 4);
+            if (!dN) return CUSK_E_CUDA;
+            CUSK_CUDA(cudaMemcpyAsync(dN, N, nn * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)(nn * 4);
+        }
+        if (!all_ones) {
+            dG = (int *)arena_take(ctx->io, nn * 4);
+            if (!dG) return CUSK_E_CUDA;
+            CUSK_CUDA(cudaMemcpyAsync(dG, G, nn * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)(nn * 4);
+        }
+        CUSK_CUDA(cudaEventRecord(ctx->ev_inputs, st));
+        th2d.stop();
+        // once the inputs are on the device nothing reads the caller's G any more: zero it while the device works (the
+        // engine calls idle_job before one of its synchronisations), the surviving edges are written afterwards
+        ctx->idle_job = [&] {
+            if (cudaEventSynchronize(ctx->ev_inputs) != cudaSuccess) return;  // an uploaded G has left the caller's buffer
+            host_zero_fill(G, nn);
+            zeroed = true;
+        };
+    }
     int rc = hetcor_engine(ctx, dC, n, dbits, dG, false, dN, n_uniform, th, maxlevel, dT, l_out, sp);
     ctx->idle_job = nullptr;
     if (rc) return rc;

@@ -207,6 +207,26 @@ __device__ __forceinline__ void block_scan_excl_2u64(u64 v0, u64 v1, u64 *s_warp
 
 // ceil(a / b) with the 32-bit divider when both operands fit (they nearly always do; a 64-bit division is
 // ~4x the instructions, and the plan phase below is one CTA on the critical path of every level)
+// C(n, k) for n < 64, k < 16 from a table (Pascal's rule at compile time): binom64's chain of 64-bit divisions on one lane
+// per row was a visible part of the per-level planning time; larger arguments fall back to it
+struct BinomTab {
+    u64 v[64 * 16];
+};
+constexpr BinomTab make_binom_tab()
+{
+    BinomTab t{};
+    for (int n = 0; n < 64; n++)
+        for (int k = 0; k < 16; k++)
+            t.v[n * 16 + k] = (k > n) ? 0 : ((k == 0 || k == n) ? 1 : t.v[(n - 1) * 16 + k - 1] + t.v[(n - 1) * 16 + k]);
+    return t;
+}
+__device__ const BinomTab g_binom_tab = make_binom_tab();
+__device__ __forceinline__ u64 binom_dev(int n, int k)
+{
+    if ((unsigned)n < 64u && (unsigned)k < 16u) return g_binom_tab.v[n * 16 + k];
+    return binom64(n, k);
+}
+
 __device__ __forceinline__ u64 ceil_div_u64(u64 a, u64 b)
 {
     if (a == 0) return 0;
@@ -228,7 +248,7 @@ __device__ __forceinline__ void compact_row(int r, int lane, const uint32_t *__r
         const u64 chx = __ldcg(&chunk[r]);
         if (chx != 0) {
             const int dd = __ldcg(&deg[r]);
-            const u64 nc = binom64(dd, l);
+            const u64 nc = binom_dev(dd, l);
             const u64 cnt = ceil_div_u64(nc, chx);
             const int is = __ldcg(&itemstart[r]);
             const int cls = is >> 24;
@@ -323,7 +343,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
                 deg[r] = d;
                 u64 cb = 0;
                 if (d > l) {
-                    cb = binom64(d, l);
+                    cb = binom_dev(d, l);
                     const u64 canon = (cb > ((u64)1 << 40) ? ((u64)1 << 40) : cb) * (u64)(d - l);
                     atomicAdd((unsigned long long *)&s_acc[2], (unsigned long long)canon);
                     if (cb >= CI_MAX_COMB)
