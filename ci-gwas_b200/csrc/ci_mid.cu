@@ -19,6 +19,104 @@
 #define CM_NTHREADS 256
 #define FULLMASK 0xffffffffu
 
+// Level 1 of the het engine with one sample size for all pairs (the cuskss case): the decision
+//   (r_xy - r_yz r_xz)^2 < T2 (1 - r_xz^2)(1 - r_yz^2)
+// is taken in FP32 when it is not close -- every FP32 quantity here is one or two correctly rounded operations away from
+// the exact value (the FMAs round once), so a relative margin of 2e-6 on both sides leaves the FP64 expression of the
+// general loop only the tests within that band (same decisions everywhere, ~40 % fewer instructions per test).  One
+// 16-byte shared-memory entry per neighbour y: {adj(y) n, latest time a conditioning variable may have (INT_MIN: edge
+// gone), r_xy, adj(y)}.
+__device__ __forceinline__ bool level1_exact(float cxy, float cxz, float cyz, double T2u)
+{
+    const double tx0 = (double)cxz, ty0 = (double)cyz;
+    const double h01 = (double)cxy - ty0 * tx0;
+    const double h11 = 1.0 - ty0 * ty0;
+    const double c2 = fabs(1.0 - tx0 * tx0);
+    const double lhs = h01 * h01;
+    const double den = c2 * fabs(h11);
+    return (lhs < T2u * den) || (den > 0.0 && lhs * T2u > den);
+}
+
+__device__ __forceinline__ u64 level1_fast(const CiParams &p, int X, int d, int row0, unsigned R0, unsigned R1, int tX,
+                                           bool use_time, double T2u, unsigned char *smem)
+{
+    constexpr int INT_LOW = -2147483647 - 1;
+    const int tid = threadIdx.x;
+    const int n = p.n;
+    int4 *s_t = (int4 *)smem;                     // CI_MID_DMAX1 entries
+    int *s_tz = (int *)(s_t + CI_MID_DMAX1);      // time of each neighbour (as a conditioning variable)
+    for (int i = tid; i < d; i += CM_NTHREADS) {
+        const int v = p.adj[row0 + i];
+        const uint32_t wbits = __ldcg(&p.bits[(size_t)X * p.rw + (v >> 5)]);
+        const bool gone = !((wbits >> (v & 31)) & 1u);
+        const int tv = use_time ? p.time_index[v] : 0;
+        int4 t;
+        t.x = (int)((unsigned)v * (unsigned)n);
+        t.y = gone ? INT_LOW : (use_time ? max(tX, tv) : 2147483647);
+        t.z = __float_as_int(p.C[(size_t)X * n + v]);
+        t.w = v;
+        s_t[i] = t;
+        s_tz[i] = tv;
+    }
+    __syncthreads();
+    const float T2f = (float)T2u;
+    unsigned tests = 0;
+    const unsigned nranks = R1 - R0;
+    const unsigned nych = (unsigned)(d + 31) >> 5;
+    const unsigned units = nranks * nych;
+    const float *__restrict__ C = p.C;
+    for (unsigned u = tid; u < units; u += CM_NTHREADS) {
+        const unsigned ych = u / nranks;
+        const int z = (int)(R0 + (u - ych * nranks));
+        const int y0 = (int)ych * 32, y1 = min(d, y0 + 32);
+        const int4 tz = s_t[z];
+        const unsigned adjz = (unsigned)tz.w;
+        const float cxz = __int_as_float(tz.z);
+        const int tS = s_tz[z];
+        const float c2 = fabsf(fmaf(-cxz, cxz, 1.0f));
+        const float k = T2f * c2;
+        const float k_lo = k * (1.0f - 2e-6f), k_hi = k * (1.0f + 2e-6f);
+        const float k2 = (c2 / T2f) * (1.0f - 2e-6f);  // lhs T2 > den cannot hold below this multiple of |h11|
+        for (int yb = y0; yb < y1; yb += 4) {
+            int4 ty[4];
+            float cyz[4];
+            bool live[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int y = min(yb + q, y1 - 1);
+                ty[q] = s_t[y];
+                live[q] = (yb + q < y1) && (y != z) && (tS <= ty[q].y);
+                cyz[q] = 0.f;
+                if (live[q]) cyz[q] = __ldg(C + ((unsigned)ty[q].x + adjz));
+            }
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (!live[q]) continue;
+                tests++;
+                const float cxy = __int_as_float(ty[q].z);
+                const float a = fmaf(-cyz[q], cxz, cxy);
+                const float ah = fabsf(fmaf(-cyz[q], cyz[q], 1.0f));
+                const float lhs = a * a;
+                bool rem;
+                if (lhs < k_lo * ah)
+                    rem = true;
+                else if (lhs > k_hi * ah && lhs < k2 * ah)
+                    rem = false;
+                else
+                    rem = level1_exact(cxy, cxz, cyz[q], T2u);
+                if (rem) {
+                    const int Y = ty[q].w;
+                    atomicAnd(&p.bits[(size_t)X * p.rw + (Y >> 5)], ~(1u << (Y & 31)));
+                    atomicAnd(&p.bits[(size_t)Y * p.rw + (X >> 5)], ~(1u << (X & 31)));
+                    if (p.removed) p.removed[row0 + yb + q] = 1;
+                    s_t[yb + q].y = INT_LOW;
+                }
+            }
+        }
+    }
+    return (u64)tests;
+}
+
 template <bool HET, int LT>
 __global__ void __launch_bounds__(CM_NTHREADS) ci_mid_kernel(const CiParams p)
 {
@@ -62,6 +160,12 @@ __global__ void __launch_bounds__(CM_NTHREADS) ci_mid_kernel(const CiParams p)
         const unsigned R0 = (unsigned)r2.x, R1 = (unsigned)r2.y;
         const int tX = use_time ? p.time_index[X] : 0;
         const int stride = d | 1;
+        if constexpr (HET && LT == 1) {
+            if (!het_general && (unsigned)n < 65536u) {
+                my_tests += level1_fast(p, X, d, row0, R0, R1, tX, use_time, T2u, smem);
+                continue;
+            }
+        }
         for (int i = tid; i < d; i += CM_NTHREADS) {
             const int v = p.adj[row0 + i];
             s_adj[i] = v;
