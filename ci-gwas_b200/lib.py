@@ -130,6 +130,9 @@ def load_library():
                                       C.c_void_p, C.c_void_p, C.c_int64, c_i64_p, C.POINTER(Stats)]
     lib.cusk_bed_marker_stats.argtypes = [C.c_void_p, c_ubyte_p, C.c_size_t, C.c_size_t, c_float_p, c_float_p,
                                           c_int_p, c_i64_p]
+    lib.cusk_bed_marker_stats_noalloc.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                  C.c_void_p, C.c_void_p]
+    lib.cusk_bed_marker_stats_noalloc.restype = C.c_int
     lib.cusk_corr_block.argtypes = [C.c_void_p, c_ubyte_p, c_float_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                     c_float_p, c_float_p, C.c_int, c_float_p, c_float_p, c_float_p, c_i64_p,
                                     C.POINTER(CorrStats)]

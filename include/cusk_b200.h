@@ -130,6 +130,19 @@ typedef struct cusk_corr_stats {
 int cusk_bed_marker_stats(cusk_ctx *ctx, const unsigned char *bed, size_t m, size_t n, float *means,
                           float *stds, int *modes, int64_t *counts4);
 
+/* Allocation-free variant of cusk_bed_marker_stats.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * d_bed [m][ceil(n/4)], d_means[m], d_stds[m], d_modes[m] and the optional d_counts4[m][4] (int32: n0, n1, n2, nmissing;
+ * may be NULL) are DEVICE buffers of the caller on the current device; `stream` is a cudaStream_t (NULL = the default
+ * stream).  The work is queued on `stream` and the call returns without synchronising.  The only scratch, the counts
+ * table between the two kernels, is a fixed __device__ array inside the library (1 MiB per GPU, held until exit), so
+ * m <= CUSK_NOALLOC_MAX_MARKERS (CUSK_E_ARG beyond it) and no cudaMalloc / cudaFree / allocating library call is made.
+ * All calls share that array: calls that overlap on the GPU (two streams, concurrent graph replays) race -- serialise
+ * them.  The first call on a device looks the array's address up (cudaGetSymbolAddress); make it outside a capture. */
+#define CUSK_NOALLOC_MAX_MARKERS 65536
+int cusk_bed_marker_stats_noalloc(const unsigned char *d_bed, size_t m, size_t n, float *d_means, float *d_stds,
+                                  int *d_modes, int *d_counts4, void *stream);
+
 /* marker x trait Pearson (replaces cu_marker_phen_corr_pearson, src/corr_host.cu:1023). mxp[m*p] */
 int cusk_marker_phen_corr(cusk_ctx *ctx, const unsigned char *bed, const float *phen, size_t m, size_t n,
                           size_t p, const float *mean, const float *std, float *mxp,
