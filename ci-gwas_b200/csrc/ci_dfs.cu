@@ -81,6 +81,7 @@ __global__ void __launch_bounds__(CD_NTHREADS) ci_dfs_kernel(const CiParams p)
     int *s_time = s_adj + NC;
     __shared__ int s_item;
     LevelCtl *ctl = p.ctl;
+    pdl_enter();
     if (ctl->done) return;
     // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
     const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
@@ -490,7 +491,7 @@ static int cd_launch(cudaStream_t st, const CiParams &p)
         ctas_per_sm = nb;
         ctas_of_device[dev].store(nb, std::memory_order_release);
     }
-    ci_dfs_kernel<MODE, LT, NS><<<(p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm, CD_NTHREADS, dyn, st>>>(p);
+    launch_k(ci_dfs_kernel<MODE, LT, NS>, dim3((p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm), dim3(CD_NTHREADS), dyn, st, p);
     return CUSK_OK;
 }
 

@@ -36,6 +36,7 @@ __global__ void __launch_bounds__(CI_NTHREADS, 1) ci_level_kernel(const CiParams
         u64 R0, R1;
     } s_it;
     LevelCtl *ctl = p.ctl;
+    pdl_enter();
     if (ctl->done) return;  // (short rows are not in this kernel's item table: ci_small.cu)
     // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
     const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
@@ -419,8 +420,8 @@ int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid)
         return CUSK_E_CUDA;
     }
     if (het)
-        ci_level_kernel<true><<<grid, CI_NTHREADS, p.smem_bytes, st>>>(p);
+        launch_k(ci_level_kernel<true>, dim3(grid), dim3(CI_NTHREADS), p.smem_bytes, st, p);
     else
-        ci_level_kernel<false><<<grid, CI_NTHREADS, p.smem_bytes, st>>>(p);
+        launch_k(ci_level_kernel<false>, dim3(grid), dim3(CI_NTHREADS), p.smem_bytes, st, p);
     return CUSK_OK;
 }

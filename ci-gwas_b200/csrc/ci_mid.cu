@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(CM_NTHREADS) ci_mid_kernel(const CiParams p)
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_item;
     LevelCtl *ctl = p.ctl;
+    pdl_enter();
     if (ctl->done) return;
     // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
     const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
@@ -340,7 +341,7 @@ static int cm_launch(cudaStream_t st, const CiParams &p)
         ctas_per_sm = nb;
         ctas_of_device[dev].store(nb, std::memory_order_release);
     }
-    ci_mid_kernel<HET, LT><<<(p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm, CM_NTHREADS, dyn, st>>>(p);
+    launch_k(ci_mid_kernel<HET, LT>, dim3((p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm), dim3(CM_NTHREADS), dyn, st, p);
     return CUSK_OK;
 }
 

@@ -79,6 +79,7 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
     __shared__ CsWarp s_w[CS_NWARPS(LT)];
     __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
     LevelCtl *ctl = p.ctl;
+    pdl_enter();
     if (ctl->done) return;
     // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
     const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
@@ -326,7 +327,7 @@ static int cs_launch(cudaStream_t st, const CiParams &p)
         ctas_per_sm = nb;
         ctas_of_device[dev].store(nb, std::memory_order_release);
     }
-    ci_small_kernel<HET, LT><<<(p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm, NT, dyn, st>>>(p);
+    launch_k(ci_small_kernel<HET, LT>, dim3((p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm), dim3(NT), dyn, st, p);
     return CUSK_OK;
 }
 

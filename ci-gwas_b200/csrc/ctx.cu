@@ -27,6 +27,11 @@ extern "C" int cusk_device_count(void)
     return n;
 }
 
+extern "C" void cusk_ctx_set_level_timing(cusk_ctx *ctx, int on)
+{
+    if (ctx) ctx->level_timing = on != 0;
+}
+
 extern "C" int cusk_ctx_create(int device_id, cusk_ctx **out)
 {
     if (!out) {
@@ -64,6 +69,10 @@ extern "C" int cusk_ctx_create(int device_id, cusk_ctx **out)
     for (auto &ev : ctx->ev) CUSK_CUDA(cudaEventCreate(&ev));
     CUSK_CUDA(cudaEventCreateWithFlags(&ctx->ev_inputs, cudaEventDisableTiming));
     ctx->ev_ready = true;
+    {
+        const char *e = getenv("CUSK_LEVEL_TIMING");
+        ctx->level_timing = !(e && atoi(e) == 0);
+    }
     *out = ctx;
     return CUSK_OK;
 }

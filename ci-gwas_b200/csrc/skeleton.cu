@@ -138,6 +138,9 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     if (!d_items || !d_items_small || !d_items_mid) return CUSK_E_CUDA;
 
     cudaEvent_t *ev = ctx->ev;
+    // per-level and per-kernel-group events are instrumentation (cusk_stats.level_ms / ci_kernel_ms): three records per
+    // level sit between back-to-back launches, so a caller that only wants the result can switch them off
+    const bool timing = ctx->level_timing;
     CUSK_CUDA(cudaEventRecord(ev[0], st));
     // ---- level 0 -----------------------------------------------------------------------------
     if (a.het && a.bits_are_input) {
@@ -172,7 +175,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             l_stop = l;
             break;
         }
-        CUSK_CUDA(cudaEventRecord(ev[l], st));
+        if (timing) CUSK_CUDA(cudaEventRecord(ev[l], st));
         LevelCtl *ctl = d_ctl + l;
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
         // from level 2 on (the CSR arrays exist) the plan and the compaction are one launch when the grid fits the device
@@ -259,7 +262,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.removed = sh ? d_removed : nullptr;
         p.shard_rank = sh ? sh->rank : 0;  // used by the kernels only when the level's plan set shard_on
         p.shard_world = sh ? sh->world : 1;
-        CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
+        if (timing) CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = CUSK_OK;
         if (classes & 1u) rc = (nl++, launch_ci_level(st, a.het, p, grid));  // hub rows
         if (rc) return rc;
@@ -274,7 +277,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             if (!rc && (classes & 256u)) rc = (nl++, launch_ci_dfs(st, a.het, p, true));
             if (rc) return rc;
         }
-        CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
+        if (timing) CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
         if (sh) {
             // exchange step of the level: removed edges (het: one flag byte per slot of the level-1 CSR, all-gathered;
             // individual-level: minimum of the separating-set ranks), after which every rank holds the same graph
@@ -358,7 +361,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             stats->edges_after[l] = (int64_t)(((l + 1 < l_stop && l < maxl) ? h_ctl[l + 1].nnz : h_ctl[CUSK_ML + 1].nnz) / 2);
         }
         if (maxl == 0) stats->edges_after[0] = (int64_t)(h_ctl[CUSK_ML + 1].nnz / 2);
-        for (int l = 0; l < l_end; l++) {
+        for (int l = 0; timing && l < l_end; l++) {
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, ev[l], ev[l + 1]) == cudaSuccess) stats->level_ms[l] = ms;
             if (l >= 1 && !h_ctl[l].done &&

@@ -96,3 +96,32 @@ __host__ __device__ inline int ci_row_class(int d, int l, int dsmall, int dmid, 
     if (l <= CI_MID_LMAX && d <= dmid) return 2;
     return 0;
 }
+
+// ---- programmatic dependent launch (sm_90+) ---------------------------------------------------------------------------
+// The level loop is a chain of short dependent kernels.  With CUSK_PDL=1 they are launched with the programmatic
+// stream-serialisation attribute: a kernel lets its successor's CTAs become resident at once (launch_dependents) and
+// itself waits for its predecessor's completion and memory flush (wait) before it touches anything, so the successor's
+// launch latency hides behind the predecessor instead of following it.  Without the attribute both are no-ops.
+bool pdl_enabled();  // skeleton_kernels.cu
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_enter()
+{
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename K, typename... A>
+inline cudaError_t launch_k(K kern, dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, args...);
+}
+#endif

@@ -312,6 +312,7 @@ __global__ void __launch_bounds__(1024) degree_plan_kernel(const uint32_t *__res
     __shared__ int s_maxdeg, s_infeasible, s_last;
     __shared__ u64 s_target, s_target_small, s_target_mid;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    pdl_enter();
     if (prev && prev->done) {
         if (blockIdx.x == 0 && tid == 0) {
             ctl->done = 1;
@@ -529,6 +530,7 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint32_t *__restrict
                                                       CiItem *__restrict__ items_small, CiItem *__restrict__ items_mid,
                                                       int item_cap)
 {
+    pdl_enter();
     if (ctl->done) return;
     const int lane = threadIdx.x & 31;
     const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -576,6 +578,7 @@ __global__ void __launch_bounds__(128) resolve_kernel(const float *__restrict__ 
                                                       cusk_sepset *seps, unsigned long long *sep_count,
                                                       u64 sep_cap, const LevelCtl *ctl)
 {
+    pdl_enter();
     if (ctl->done) return;
     const int lane = threadIdx.x & 31;
     const int X = blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -777,6 +780,15 @@ unsigned ci_classes_possible(int l, int maxdeg)
 // The level's degrees + plan, and (fused = true) its compaction too, as one launch.  The fused form makes CTAs wait
 // for the planning CTA, so it is a cooperative launch (the driver only starts it when the whole grid is resident: two
 // host slots driving the same GPU cannot wedge each other) and only offered when the grid fits the device at once.
+bool pdl_enabled()
+{
+    static const bool on = [] {
+        const char *e = getenv("CUSK_PDL");
+        return e && atoi(e) != 0;
+    }();
+    return on;
+}
+
 bool plan_compact_fusable(int n, int sm_count)
 {
     static int occ = -1;
@@ -805,12 +817,10 @@ cudaError_t launch_degree_plan(cudaStream_t st, const uint32_t *bits, int n, int
     int span = dt.span, dmin = dt.dmin, lnarrow = dt.lnarrow, ipsm_dfs = dt.ipsm;
     int smc = sm_count > 0 ? sm_count : 148, fuse = fused ? 1 : 0;
     if (!fused) {
-        degree_plan_kernel<<<(n + 31) / 32, 1024, 0, st>>>(bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl, prev, th_level,
-                                                           th_het, n_uniform, work_counter, work_counter_small,
-                                                           work_counter_mid, world, ipsm_shallow, ipsm_deep, ipsm_small,
-                                                           ipsm_mid, span, dmin, lnarrow, ipsm_dfs, smc, shard_min_tests, 0,
-                                                           nullptr, nullptr, nullptr, nullptr, nullptr, 0);
-        return cudaGetLastError();
+        return launch_k(degree_plan_kernel, dim3((n + 31) / 32), dim3(1024), 0, st, bits, n, rw, deg, l, rowptr, itemstart, chunk, ctl,
+                        prev, th_level, th_het, n_uniform, work_counter, work_counter_small, work_counter_mid, world,
+                        ipsm_shallow, ipsm_deep, ipsm_small, ipsm_mid, span, dmin, lnarrow, ipsm_dfs, smc, shard_min_tests, 0,
+                        (int *)nullptr, (u64 *)nullptr, (CiItem *)nullptr, (CiItem *)nullptr, (CiItem *)nullptr, 0);
     }
     void *args[] = {&bits, &n, &rw, &deg, &l, &rowptr, &itemstart, &chunk, &ctl, &prev, &th_level, &th_het, &n_uniform,
                     &work_counter, &work_counter_small, &work_counter_mid, &world, &ipsm_shallow, &ipsm_deep, &ipsm_small,
@@ -823,16 +833,16 @@ void launch_compact(cudaStream_t st, const uint32_t *bits, int n, int rw, const 
                     u64 *minkey, const LevelCtl *ctl, const int *deg, const int *itemstart, const u64 *chunk, int l,
                     CiItem *items, CiItem *items_small, CiItem *items_mid, int item_cap)
 {
-    compact_kernel<<<(n + 7) / 8, 256, 0, st>>>(bits, n, rw, rowptr, adj, minkey, ctl, deg, itemstart, chunk, l, items,
-                                                items_small, items_mid, item_cap);
+    launch_k(compact_kernel, dim3((n + 7) / 8), dim3(256), 0, st, bits, n, rw, rowptr, adj, minkey, ctl, deg, itemstart, chunk, l,
+             items, items_small, items_mid, item_cap);
 }
 
 void launch_resolve(cudaStream_t st, const float *C, int n, int rw, int l, uint32_t *bits, const int *deg,
                     const int *rowptr, const int *adj, const u64 *minkey, float *pMax, cusk_sepset *seps,
                     unsigned long long *sep_count, u64 sep_cap, const LevelCtl *ctl)
 {
-    resolve_kernel<<<(n + 3) / 4, 128, 0, st>>>(C, n, rw, l, bits, deg, rowptr, adj, minkey, pMax, seps,
-                                                sep_count, sep_cap, ctl);
+    launch_k(resolve_kernel, dim3((n + 3) / 4), dim3(128), 0, st, C, n, rw, l, bits, deg, rowptr, adj, minkey, pMax, seps, sep_count,
+             sep_cap, ctl);
 }
 
 void launch_pmax_final(cudaStream_t st, const uint32_t *bits, int n, int rw, float *pMax)

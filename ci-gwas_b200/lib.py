@@ -111,6 +111,8 @@ def load_library():
     lib.cusk_version.restype = C.c_char_p
     lib.cusk_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     lib.cusk_ctx_destroy.argtypes = [C.c_void_p]
+    lib.cusk_ctx_set_level_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.cusk_ctx_set_level_timing.restype = None
     lib.cusk_ctx_stream.restype = C.c_void_p
     lib.cusk_ctx_stream.argtypes = [C.c_void_p]
     lib.cusk_ctx_sync.argtypes = [C.c_void_p]
@@ -250,6 +252,10 @@ class Context:
             raise CuskError(self.lib.cusk_last_error().decode())
         self.h = h
         self.device = device
+
+    def set_level_timing(self, on):
+        """per-level event records (stats level_ms / ci_kernel_ms) on or off; include/cusk_b200.h"""
+        self.lib.cusk_ctx_set_level_timing(self.h, 1 if on else 0)
 
     def close(self):
         self.detach_comm()

@@ -76,6 +76,10 @@ int cusk_device_count(void);
 /* the CUDA stream the context launches on (a cudaStream_t), for callers that time with events */
 void *cusk_ctx_stream(cusk_ctx *ctx);
 int cusk_ctx_sync(cusk_ctx *ctx);
+/* Per-level instrumentation (cusk_stats.level_ms / ci_kernel_ms: three event records per level between the launches).
+ * On by default (CUSK_LEVEL_TIMING=0 turns it off for new contexts); total_ms and the counters are always filled.
+ * The reference's counterpart are its per-level "spent seconds" host timers (src/cuPC-S.cu:139-159). */
+void cusk_ctx_set_level_timing(cusk_ctx *ctx, int on);
 
 /* ---- thresholds  (replaces src/cuPC_call_prep.cpp:13-28) --------------------------------- */
 /* Th[l] = |qnorm(alpha/2)| / sqrt(n-l-3), l = 0..14, same float/double type flow. */
