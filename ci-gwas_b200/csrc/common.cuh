@@ -84,7 +84,7 @@ struct cusk_ctx {
     // host work of the calling entry point that does not depend on the device's result (zero-filling the caller's output
     // matrix): the engine runs it once, just before one of its stream synchronisations, while the device is busy
     std::function<void()> idle_job;
-    bool level_timing = true;  // record the per-level / per-kernel-group events behind cusk_stats.level_ms and ci_kernel_ms
+    bool level_timing = false;  // record the per-level / per-kernel-group events behind cusk_stats.level_ms and ci_kernel_ms
 };
 
 inline void run_idle_job(cusk_ctx *ctx)

@@ -71,7 +71,7 @@ extern "C" int cusk_ctx_create(int device_id, cusk_ctx **out)
     ctx->ev_ready = true;
     {
         const char *e = getenv("CUSK_LEVEL_TIMING");
-        ctx->level_timing = !(e && atoi(e) == 0);
+        ctx->level_timing = e && atoi(e) != 0;  // instrumentation: off unless asked for
     }
     *out = ctx;
     return CUSK_OK;

@@ -98,7 +98,7 @@ __host__ __device__ inline int ci_row_class(int d, int l, int dsmall, int dmid, 
 }
 
 // ---- programmatic dependent launch (sm_90+) ---------------------------------------------------------------------------
-// The level loop is a chain of short dependent kernels.  With CUSK_PDL=1 they are launched with the programmatic
+// The level loop is a chain of short dependent kernels.  Unless CUSK_PDL=0 they are launched with the programmatic
 // stream-serialisation attribute: a kernel lets its successor's CTAs become resident at once (launch_dependents) and
 // itself waits for its predecessor's completion and memory flush (wait) before it touches anything, so the successor's
 // launch latency hides behind the predecessor instead of following it.  Without the attribute both are no-ops.

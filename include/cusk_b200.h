@@ -77,7 +77,8 @@ int cusk_device_count(void);
 void *cusk_ctx_stream(cusk_ctx *ctx);
 int cusk_ctx_sync(cusk_ctx *ctx);
 /* Per-level instrumentation (cusk_stats.level_ms / ci_kernel_ms: three event records per level between the launches).
- * On by default (CUSK_LEVEL_TIMING=0 turns it off for new contexts); total_ms and the counters are always filled.
+ * OFF by default -- the records cost ~4.5 us each, 0.2 ms of the 1.1 ms C2 step -- (CUSK_LEVEL_TIMING=1 turns it on for
+ * new contexts); total_ms and the counters are always filled.
  * The reference's counterpart are its per-level "spent seconds" host timers (src/cuPC-S.cu:139-159). */
 void cusk_ctx_set_level_timing(cusk_ctx *ctx, int on);
 
