@@ -68,7 +68,100 @@ struct CsIdx {
     __device__ __forceinline__ static constexpr int w(int j, int a) { return j * LM - (j * (j + 1)) / 2 + (a - j - 1); }
 };
 
-template <bool HET, int LT>
+// ---- self-planned level (SELF) -------------------------------------------------------------------------------------------
+// Deep levels of a light block run a few hundred thousand tests in ~15 us, and the separate degree / plan / compaction
+// launch in front of them costs as much again.  When every row is known to be short (host: max degree <= CI_SELF_DMAX, het
+// engine, one GPU) the CI kernel does that work itself in a prologue, without prefix sums:
+//   * a warp per row (grid-stride): popcount and expansion of the bitmap row into self_adj[row][0..d) -- the adjacency as
+//     of the level's start, fixed stride, so no CSR offsets are needed;
+//   * the row's conditioning sets are cut into at most CI_SELF_MAXI items of at least CI_SELF_ITEM_TESTS tests, which the
+//     warp appends to the level's item table (one atomicAdd reserves the slots: the order of items is irrelevant);
+//   * level totals (max degree, edges, canonical test count) by atomics; then ONE grid barrier (cooperative launch) and the
+//     kernel goes on as usual, pulling items from the table.  The level runs iff some row has more than l neighbours, i.e.
+//     iff the table is not empty (src/cuPC-S.cu:154-159).
+// Returns the number of items; *T2 = tanh(threshold)^2 of the level.
+__device__ __forceinline__ int cs_self_plan(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int nw = blockDim.x >> 5;
+    const int n = p.n, rw = p.rw;
+    u64 canon = 0, nnz = 0;
+    int maxd = 0, bad = 0;
+    for (int r = blockIdx.x * nw + (tid >> 5); r < n; r += gridDim.x * nw) {
+        int out = 0;
+        int *arow = p.self_adj + (size_t)r * CI_SELF_STRIDE;
+        for (int w0 = 0; w0 < rw; w0 += 32) {
+            const int w = w0 + lane;
+            uint32_t word = (w < rw) ? p.bits[(size_t)r * rw + w] : 0u;
+            const int cnt = __popc(word);
+            int inc = cnt;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(FULLMASK, inc, o);
+                if (lane >= o) inc += t;
+            }
+            int pos = out + inc - cnt;
+            while (word) {
+                const int b = __ffs(word) - 1;
+                word &= word - 1;
+                if (pos < CI_SELF_STRIDE) arow[pos] = w * 32 + b;
+                pos++;
+            }
+            out += __shfl_sync(FULLMASK, inc, 31);
+        }
+        const int d = out;
+        if (lane == 0) p.deg_out[r] = d;
+        maxd = max(maxd, d);
+        nnz += (u64)d;
+        if (d <= l) continue;
+        if (d > CI_SELF_STRIDE) {  // cannot happen: degrees only fall and the host checked the bound
+            bad = 1;
+            continue;
+        }
+        const u64 nsets = (u64)s_binom[d * (CUSK_ML + 1) + l];
+        const u64 tests = nsets * (u64)(d - l);
+        canon += tests;
+        u64 cnt = (tests + CI_SELF_ITEM_TESTS - 1) / CI_SELF_ITEM_TESTS;
+        if (cnt > CI_SELF_MAXI) cnt = CI_SELF_MAXI;
+        if (cnt > nsets) cnt = nsets;
+        const u64 chunk = (nsets + cnt - 1) / cnt;
+        cnt = (nsets + chunk - 1) / chunk;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&ctl->nitems_small, (int)cnt);
+        base = __shfl_sync(FULLMASK, base, 0);
+        for (int k = lane; k < (int)cnt; k += 32) {
+            if (base + k >= p.item_cap) break;  // cannot happen: cap = n * CI_SELF_MAXI
+            CiItem it;
+            it.X = r;
+            it.d = d;
+            it.row0 = r * CI_SELF_STRIDE;
+            it.pad = 0;
+            it.R0 = (u64)k * chunk;
+            it.R1 = (it.R0 + chunk < nsets) ? it.R0 + chunk : nsets;
+            p.self_items[base + k] = it;
+        }
+    }
+    if (lane == 0) {
+        if (maxd) atomicMax(&ctl->maxdeg, maxd);
+        if (nnz) atomicAdd((unsigned long long *)&ctl->nnz, (unsigned long long)nnz);
+        if (canon) atomicAdd((unsigned long long *)&ctl->canon, (unsigned long long)canon);
+        if (bad) atomicExch(&ctl->infeasible, 4);
+    }
+    // grid barrier: every CTA is resident (cooperative launch)
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        atomicAdd(&ctl->ticket, 1u);
+        while (*(volatile unsigned *)&ctl->ticket < gridDim.x) __nanosleep(64);
+        __threadfence();
+    }
+    __syncthreads();
+    int nitems = *(volatile int *)&ctl->nitems_small;
+    if (*(volatile int *)&ctl->infeasible) nitems = 0;
+    if (nitems > p.item_cap) nitems = p.item_cap;
+    return nitems;
+}
+
+template <bool HET, int LT, bool SELF = false>
 __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2 : 1) ci_small_kernel(const CiParams p)
 {
     constexpr int LM = CsIdx<LT>::LM;
@@ -80,14 +173,21 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
     __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
     LevelCtl *ctl = p.ctl;
     pdl_enter();
-    if (ctl->done) return;
+    if constexpr (SELF) {
+        if (p.prev && p.prev->done) {  // an earlier level ended the run (the same for every CTA: that kernel is complete)
+            if (blockIdx.x == 0 && threadIdx.x == 0) ctl->done = 1;
+            return;
+        }
+    } else {
+        if (ctl->done) return;
+    }
     // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
     const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int l = LT;
     const int n = p.n;
-    const int nitems = ctl->nitems_small;
-    const double T2u = ctl->T2;
+    int nitems = SELF ? 0 : ctl->nitems_small;
+    double T2u = SELF ? 0.0 : ctl->T2;
     const bool het_general = HET && p.N != nullptr;
     const bool use_time = HET && p.time_index != nullptr;
     const double npairs = 0.5 * (double)((l + 2) * (l + 1));
@@ -101,6 +201,19 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
         }
     }
     __syncthreads();
+    if constexpr (SELF) {
+        nitems = cs_self_plan(p, l, ctl, s_binom);
+        {
+            const double m = (double)__float2int_rz(p.n_uniform);
+            const double t = tanh(p.th_het / sqrt(m - (double)l - 3.0));
+            T2u = t * t;
+        }
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            ctl->T2 = T2u;
+            ctl->done = (nitems == 0) ? 1 : 0;
+        }
+        if (nitems == 0) return;
+    }
     CsWarp &S = s_w[warp];
     u64 my_tests = 0;
     unsigned my_sing = 0;
@@ -299,6 +412,61 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
     if (lane == 0) {
         if (my_tests) atomicAdd((unsigned long long *)&ctl->executed, (unsigned long long)my_tests);
         if (my_sing) atomicAdd((unsigned long long *)&ctl->singular, (unsigned long long)my_sing);
+    }
+}
+
+// self-planned form: cooperative launch (the prologue ends in a grid barrier)
+template <int LT>
+static int cs_launch_self(cudaStream_t st, const CiParams &p)
+{
+    constexpr int NT = CS_NTHREADS(LT);
+    constexpr int dyn = (LT <= CS_LREG) ? 0 : LT * (LT - 1) / 2 * 8 * NT;
+    static std::atomic<int> ctas_of_device[CUSK_MAX_DEVICES];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = (dev >= 0 && dev < CUSK_MAX_DEVICES) ? dev : 0;
+    int ctas_per_sm = ctas_of_device[dev].load(std::memory_order_acquire);
+    if (!ctas_per_sm) {
+        if (dyn > 0 && cudaFuncSetAttribute(ci_small_kernel<true, LT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            dyn) != cudaSuccess) {
+            cusk_set_error("cudaFuncSetAttribute(ci_small_kernel<%d, self>, %d B): %s", LT, dyn,
+                           cudaGetErrorString(cudaGetLastError()));
+            return CUSK_E_CUDA;
+        }
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ci_small_kernel<true, LT, true>, NT, dyn) != cudaSuccess ||
+            nb < 1)
+            nb = 1;
+        ctas_per_sm = nb;
+        ctas_of_device[dev].store(nb, std::memory_order_release);
+    }
+    CiParams q = p;
+    void *args[] = {&q};
+    const cudaError_t e = cudaLaunchCooperativeKernel((const void *)ci_small_kernel<true, LT, true>,
+                                                      dim3((p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm), dim3(NT), args,
+                                                      dyn, st);
+    if (e != cudaSuccess) {
+        cusk_set_error("cooperative launch of ci_small_kernel<%d, self>: %s", LT, cudaGetErrorString(e));
+        return CUSK_E_CUDA;
+    }
+    return CUSK_OK;
+}
+
+int launch_ci_small_self(cudaStream_t st, const CiParams &p)
+{
+    switch (p.l) {
+        case 4: return cs_launch_self<4>(st, p);
+        case 5: return cs_launch_self<5>(st, p);
+        case 6: return cs_launch_self<6>(st, p);
+        case 7: return cs_launch_self<7>(st, p);
+        case 8: return cs_launch_self<8>(st, p);
+        case 9: return cs_launch_self<9>(st, p);
+        case 10: return cs_launch_self<10>(st, p);
+        case 11: return cs_launch_self<11>(st, p);
+        case 12: return cs_launch_self<12>(st, p);
+        case 13: return cs_launch_self<13>(st, p);
+        case 14: return cs_launch_self<14>(st, p);
+        default: cusk_set_error("launch_ci_small_self: level %d", p.l); return CUSK_E_ARG;
     }
 }
 

@@ -31,6 +31,7 @@ void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, in
 void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits);
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
+int launch_ci_small_self(cudaStream_t st, const CiParams &p);
 int launch_ci_small(cudaStream_t st, bool het, const CiParams &p);
 int launch_ci_mid(cudaStream_t st, bool het, const CiParams &p);
 int launch_ci_dfs(cudaStream_t st, bool het, const CiParams &p, bool wide);
@@ -137,6 +138,21 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     CiItem *d_items_mid = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
     if (!d_items || !d_items_small || !d_items_mid) return CUSK_E_CUDA;
 
+    // self-planned deep levels (ci_small.cu, SELF): het engine on one GPU, skeletons of at most CI_SELF_NMAX variables
+    static const bool self_env = [] {
+        const char *e = getenv("CUSK_SELF_PLAN");
+        return !(e && atoi(e) == 0);
+    }();
+    const bool self_ok = self_env && a.het && !sh && n <= CI_SELF_NMAX && maxl > CI_DFS_LMIN;
+    const int self_cap = n * CI_SELF_MAXI;
+    int *d_self_adj = nullptr;
+    CiItem *d_self_items = nullptr;
+    if (self_ok) {
+        d_self_adj = (int *)arena_take(ctx, sizeof(int) * (size_t)n * CI_SELF_STRIDE);
+        d_self_items = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)self_cap);
+        if (!d_self_adj || !d_self_items) return CUSK_E_CUDA;
+    }
+
     cudaEvent_t *ev = ctx->ev;
     // per-level and per-kernel-group events are instrumentation (cusk_stats.level_ms / ci_kernel_ms): three records per
     // level sit between back-to-back launches, so a caller that only wants the result can switch them off
@@ -179,9 +195,13 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         LevelCtl *ctl = d_ctl + l;
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
         // from level 2 on (the CSR arrays exist) the plan and the compaction are one launch when the grid fits the device
-        const bool fused = l >= 2 && fusable;
-        nl++;
-        CUSK_CUDA(launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
+        // deep levels of a light block: no separate plan / compaction, the CI kernel plans itself (degrees only fall, so the
+        // bound read at level 3 holds for the rest of the call)
+        const bool self_level = self_ok && l > CI_DFS_LMIN && maxdeg_bound <= CI_SELF_DMAX;
+        const bool fused = l >= 2 && fusable && !self_level;
+        if (!self_level) nl++;
+        if (!self_level)
+            CUSK_CUDA(launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
                                      a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l,
                                      d_work_small + l, d_work_mid + l, sh ? sh->world : 1, ctx->sm_count, shard_min_tests,
                                      fused, d_adj, d_minkey, d_items, d_items_small, d_items_mid, item_cap));
@@ -232,7 +252,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         // that the host never has to read the plan back: one fixed-size stream-ordered collective per level.
         if (sh && d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, std::max<size_t>(flag_stride, 16), st));
         const unsigned classes = ci_classes_possible(l, maxdeg_bound);
-        if (!fused)
+        if (!fused && !self_level)
             nl++, launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
                                  d_items_small, d_items_mid, item_cap);
         CiParams p;
@@ -262,8 +282,23 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.removed = sh ? d_removed : nullptr;
         p.shard_rank = sh ? sh->rank : 0;  // used by the kernels only when the level's plan set shard_on
         p.shard_world = sh ? sh->world : 1;
+        p.prev = prev;
+        p.self_adj = d_self_adj;
+        p.self_items = d_self_items;
+        p.deg_out = d_deg;
+        p.n_uniform = n_uniform;
         if (timing) CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = CUSK_OK;
+        if (self_level) {
+            p.adj = d_self_adj;
+            p.items_small = d_self_items;
+            p.item_cap = self_cap;
+            rc = (nl++, launch_ci_small_self(st, p));
+            if (rc) return rc;
+            if (timing) CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
+            CUSK_CUDA(cudaGetLastError());
+            continue;
+        }
         if (classes & 1u) rc = (nl++, launch_ci_level(st, a.het, p, grid));  // hub rows
         if (rc) return rc;
         if (classes & 2u) rc = (nl++, launch_ci_small(st, a.het, p));  // the level's short rows (thread per conditioning set)
