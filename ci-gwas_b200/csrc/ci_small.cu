@@ -68,167 +68,39 @@ struct CsIdx {
     __device__ __forceinline__ static constexpr int w(int j, int a) { return j * LM - (j * (j + 1)) / 2 + (a - j - 1); }
 };
 
-// ---- self-planned level (SELF) -------------------------------------------------------------------------------------------
-// Deep levels of a light block run a few hundred thousand tests in ~15 us, and the separate degree / plan / compaction
-// launch in front of them costs as much again.  When every row is known to be short (host: max degree <= CI_SELF_DMAX, het
-// engine, one GPU) the CI kernel does that work itself in a prologue, without prefix sums:
-//   * a warp per row (grid-stride): popcount and expansion of the bitmap row into self_adj[row][0..d) -- the adjacency as
-//     of the level's start, fixed stride, so no CSR offsets are needed;
-//   * the row's conditioning sets are cut into at most CI_SELF_MAXI items of at least CI_SELF_ITEM_TESTS tests, which the
-//     warp appends to the level's item table (one atomicAdd reserves the slots: the order of items is irrelevant);
-//   * level totals (max degree, edges, canonical test count) by atomics; then ONE grid barrier (cooperative launch) and the
-//     kernel goes on as usual, pulling items from the table.  The level runs iff some row has more than l neighbours, i.e.
-//     iff the table is not empty (src/cuPC-S.cu:154-159).
-// Returns the number of items; *T2 = tanh(threshold)^2 of the level.
-__device__ __forceinline__ int cs_self_plan(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom)
-{
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int nw = blockDim.x >> 5;
-    const int n = p.n, rw = p.rw;
-    u64 canon = 0, nnz = 0;
-    int maxd = 0, bad = 0;
-    for (int r = blockIdx.x * nw + (tid >> 5); r < n; r += gridDim.x * nw) {
-        int out = 0;
-        int *arow = p.self_adj + (size_t)r * CI_SELF_STRIDE;
-        for (int w0 = 0; w0 < rw; w0 += 32) {
-            const int w = w0 + lane;
-            uint32_t word = (w < rw) ? p.bits[(size_t)r * rw + w] : 0u;
-            const int cnt = __popc(word);
-            int inc = cnt;
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(FULLMASK, inc, o);
-                if (lane >= o) inc += t;
-            }
-            int pos = out + inc - cnt;
-            while (word) {
-                const int b = __ffs(word) - 1;
-                word &= word - 1;
-                if (pos < CI_SELF_STRIDE) arow[pos] = w * 32 + b;
-                pos++;
-            }
-            out += __shfl_sync(FULLMASK, inc, 31);
-        }
-        const int d = out;
-        if (lane == 0) p.deg_out[r] = d;
-        maxd = max(maxd, d);
-        nnz += (u64)d;
-        if (d <= l) continue;
-        if (d > CI_SELF_STRIDE) {  // cannot happen: degrees only fall and the host checked the bound
-            bad = 1;
-            continue;
-        }
-        const u64 nsets = (u64)s_binom[d * (CUSK_ML + 1) + l];
-        const u64 tests = nsets * (u64)(d - l);
-        canon += tests;
-        u64 cnt = (tests + CI_SELF_ITEM_TESTS - 1) / CI_SELF_ITEM_TESTS;
-        if (cnt > CI_SELF_MAXI) cnt = CI_SELF_MAXI;
-        if (cnt > nsets) cnt = nsets;
-        const u64 chunk = (nsets + cnt - 1) / cnt;
-        cnt = (nsets + chunk - 1) / chunk;
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&ctl->nitems_small, (int)cnt);
-        base = __shfl_sync(FULLMASK, base, 0);
-        for (int k = lane; k < (int)cnt; k += 32) {
-            if (base + k >= p.item_cap) break;  // cannot happen: cap = n * CI_SELF_MAXI
-            CiItem it;
-            it.X = r;
-            it.d = d;
-            it.row0 = r * CI_SELF_STRIDE;
-            it.pad = 0;
-            it.R0 = (u64)k * chunk;
-            it.R1 = (it.R0 + chunk < nsets) ? it.R0 + chunk : nsets;
-            p.self_items[base + k] = it;
-        }
-    }
-    if (lane == 0) {
-        if (maxd) atomicMax(&ctl->maxdeg, maxd);
-        if (nnz) atomicAdd((unsigned long long *)&ctl->nnz, (unsigned long long)nnz);
-        if (canon) atomicAdd((unsigned long long *)&ctl->canon, (unsigned long long)canon);
-        if (bad) atomicExch(&ctl->infeasible, 4);
-    }
-    // grid barrier: every CTA is resident (cooperative launch)
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        atomicAdd(&ctl->ticket, 1u);
-        while (*(volatile unsigned *)&ctl->ticket < gridDim.x) __nanosleep(64);
-        __threadfence();
-    }
-    __syncthreads();
-    int nitems = *(volatile int *)&ctl->nitems_small;
-    if (*(volatile int *)&ctl->infeasible) nitems = 0;
-    if (nitems > p.item_cap) nitems = p.item_cap;
-    return nitems;
-}
-
-template <bool HET, int LT, bool SELF = false>
-__global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2 : 1) ci_small_kernel(const CiParams p)
+// ---- the level's tests: shared by the one-level kernel and by the self-planned multi-level kernel ---------------------------
+// Everything another CTA may have written during the same launch (the multi-level kernel rebuilds adjacency and items per
+// level) is read with ld.cg: L1 is not coherent across SMs.
+template <bool HET, int LT>
+__device__ __forceinline__ void cs_body(const CiParams &p, LevelCtl *ctl, int *work_counter, const CiItem *items,
+                                        const int *adj, int item_cap, int nitems, double T2u, int srank, int sworld,
+                                        CsWarp *s_w, const unsigned *s_binom, double *s_L)
 {
     constexpr int LM = CsIdx<LT>::LM;
     constexpr int NT = CS_NTHREADS(LT);
     constexpr bool LREG = (LT <= CS_LREG);
     using LS = CsL<LREG, NT>;
-    extern __shared__ double s_L[];  // LT > CS_LREG: LT (LT - 1) / 2 doubles per thread
-    __shared__ CsWarp s_w[CS_NWARPS(LT)];
-    __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
-    LevelCtl *ctl = p.ctl;
-    pdl_enter();
-    if constexpr (SELF) {
-        if (p.prev && p.prev->done) {  // an earlier level ended the run (the same for every CTA: that kernel is complete)
-            if (blockIdx.x == 0 && threadIdx.x == 0) ctl->done = 1;
-            return;
-        }
-    } else {
-        if (ctl->done) return;
-    }
-    // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
-    const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int l = LT;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = p.n;
-    int nitems = SELF ? 0 : ctl->nitems_small;
-    double T2u = SELF ? 0.0 : ctl->T2;
     const bool het_general = HET && p.N != nullptr;
     const bool use_time = HET && p.time_index != nullptr;
     const double npairs = 0.5 * (double)((l + 2) * (l + 1));
-    if (tid < 32) {
-        // Pascal's triangle, one row per step: lane r holds C(m, r)
-        unsigned prev = (lane == 0) ? 1u : 0u;  // row m = 0
-        for (int m = 0; m <= CS_DMAX; m++) {
-            if (lane <= CUSK_ML) s_binom[m * (CUSK_ML + 1) + lane] = prev;
-            const unsigned left = __shfl_up_sync(FULLMASK, prev, 1);
-            prev = (lane == 0) ? 1u : prev + left;  // C(m+1, r) = C(m, r) + C(m, r-1); < 2^32 for m <= 33, r <= 14
-        }
-    }
-    __syncthreads();
-    if constexpr (SELF) {
-        nitems = cs_self_plan(p, l, ctl, s_binom);
-        {
-            const double m = (double)__float2int_rz(p.n_uniform);
-            const double t = tanh(p.th_het / sqrt(m - (double)l - 3.0));
-            T2u = t * t;
-        }
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            ctl->T2 = T2u;
-            ctl->done = (nitems == 0) ? 1 : 0;
-        }
-        if (nitems == 0) return;
-    }
     CsWarp &S = s_w[warp];
     u64 my_tests = 0;
     unsigned my_sing = 0;
 
     for (;;) {
         int item = 0;
-        if (lane == 0) item = srank + sworld * atomicAdd(p.work_counter_small, 1);
+        if (lane == 0) item = srank + sworld * atomicAdd(work_counter, 1);
         item = __shfl_sync(FULLMASK, item, 0);
         if (item >= nitems) break;
-        if (item >= p.item_cap) {  // cannot happen: plan_kernel bounds the item count of a small level
+        if (item >= item_cap) {  // cannot happen: plan_kernel bounds the item count of a small level
             if (lane == 0) ctl->infeasible = 3;
             break;
         }
-        const int4 a4 = *(const int4 *)&p.items_small[item];
-        const ulonglong2 r2 = *(const ulonglong2 *)&p.items_small[item].R0;
+        const int4 a4 = __ldcg((const int4 *)&items[item]);
+        const ulonglong2 r2 = __ldcg((const ulonglong2 *)&items[item].R0);
         const int X = a4.x, d = a4.y, row0 = a4.z;
         const unsigned R0 = (unsigned)r2.x, R1 = (unsigned)r2.y;
         const int tX = use_time ? p.time_index[X] : 0;
@@ -236,7 +108,7 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
         // ---- stage the row (this warp's slice) ------------------------------------------------
         __syncwarp();
         if (lane < d) {
-            const int v = p.adj[row0 + lane];
+            const int v = __ldcg(&adj[row0 + lane]);
             S.adj[lane] = v;
             S.cx[lane] = p.C[(size_t)X * n + v];
             if (use_time) S.time[lane] = p.time_index[v];
@@ -245,7 +117,7 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
         if (HET) {
             bool gone = false;
             if (lane < d) {
-                const int v = p.adj[row0 + lane];
+                const int v = __ldcg(&adj[row0 + lane]);
                 const uint32_t wbits = __ldcg(&p.bits[(size_t)X * p.rw + (v >> 5)]);
                 gone = !((wbits >> (v & 31)) & 1u);
             }
@@ -415,59 +287,271 @@ __global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2
     }
 }
 
-// self-planned form: cooperative launch (the prologue ends in a grid barrier)
-template <int LT>
-static int cs_launch_self(cudaStream_t st, const CiParams &p)
+// Pascal's triangle in shared memory, one row per step: lane r holds C(m, r) (first warp of the CTA; barrier by the caller)
+__device__ __forceinline__ void cs_fill_binom(unsigned *s_binom)
 {
-    constexpr int NT = CS_NTHREADS(LT);
-    constexpr int dyn = (LT <= CS_LREG) ? 0 : LT * (LT - 1) / 2 * 8 * NT;
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) {
+        unsigned prev = (lane == 0) ? 1u : 0u;  // row m = 0
+        for (int m = 0; m <= CS_DMAX; m++) {
+            if (lane <= CUSK_ML) s_binom[m * (CUSK_ML + 1) + lane] = prev;
+            const unsigned left = __shfl_up_sync(FULLMASK, prev, 1);
+            prev = (lane == 0) ? 1u : prev + left;  // C(m+1, r) = C(m, r) + C(m, r-1); < 2^32 for m <= 33, r <= 14
+        }
+    }
+}
+
+template <bool HET, int LT>
+__global__ void __launch_bounds__(CS_NTHREADS(LT), (LT <= 6 || LT > CS_LREG) ? 2 : 1) ci_small_kernel(const CiParams p)
+{
+    extern __shared__ double s_L[];  // LT > CS_LREG: LT (LT - 1) / 2 doubles per thread
+    __shared__ CsWarp s_w[CS_NWARPS(LT)];
+    __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];  // C(m, r), m <= 32, r <= 14
+    LevelCtl *ctl = p.ctl;
+    pdl_enter();
+    if (ctl->done) return;
+    // edge-sharded mode: the level plan decides (identically on every rank) whether this level's items are dealt out
+    const int srank = ctl->shard_on ? p.shard_rank : 0, sworld = ctl->shard_on ? p.shard_world : 1;
+    cs_fill_binom(s_binom);
+    __syncthreads();
+    cs_body<HET, LT>(p, ctl, p.work_counter_small, p.items_small, p.adj, p.item_cap, ctl->nitems_small, ctl->T2, srank,
+                     sworld, s_w, s_binom, s_L);
+}
+
+// ---- self-planned deep levels (multi-level kernel) -------------------------------------------------------------------------
+// Deep levels of a light block run a few hundred thousand tests each, and the degree / plan / compaction launches in front of
+// them plus the launches themselves cost more than the tests (profiles/r2_launches_bench_steps1_call_p.csv: ~17 us of plan and
+// ~20 us of CI kernel per level for ~15 us of work).  When every row is known to be short (host: max degree <= CI_SELF_DMAX at
+// level 3, het engine, one GPU) consecutive levels run inside ONE cooperative launch, each level as
+//   A. a warp per row (grid-stride): popcount and expansion of the bitmap row into self_adj[row][0..d) -- the adjacency as of
+//      the level's start, fixed stride, so no CSR offsets and no prefix sums -- and the level totals (max degree, edges,
+//      canonical tests, conditioning sets) by atomics;                                                       [grid barrier]
+//   B. the rows' conditioning sets are cut into work items of `chunk` sets, chunk chosen from the level's set total so that
+//      the items cover the launch's warps (one atomicAdd per row reserves its slots: item order is irrelevant);  [grid barrier]
+//   C. the tests, exactly as the one-level kernel runs them (cs_body);                                       [grid barrier]
+// and the launch ends at the first level no row can reach (src/cuPC-S.cu:154-159) or at its last level.  Three launches
+// cover levels 4..14 (4-6, 7-10, 11-14: the groups share a block size and a register budget with the one-level kernels).
+__device__ __forceinline__ void cs_grid_barrier(unsigned *bar, unsigned target)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1u);
+        while (*(volatile unsigned *)bar < target) __nanosleep(32);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ unsigned long long cs_globaltimer()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// phase A of a level: degrees, fixed-stride adjacency, level totals
+__device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int nw = blockDim.x >> 5;
+    const int n = p.n, rw = p.rw;
+    u64 canon = 0, nnz = 0, sets = 0;
+    int maxd = 0, bad = 0;
+    for (int r = blockIdx.x * nw + (tid >> 5); r < n; r += gridDim.x * nw) {
+        int out = 0;
+        int *arow = p.self_adj + (size_t)r * CI_SELF_STRIDE;
+        for (int w0 = 0; w0 < rw; w0 += 32) {
+            const int w = w0 + lane;
+            uint32_t word = (w < rw) ? __ldcg(&p.bits[(size_t)r * rw + w]) : 0u;
+            const int cnt = __popc(word);
+            int inc = cnt;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(FULLMASK, inc, o);
+                if (lane >= o) inc += t;
+            }
+            int pos = out + inc - cnt;
+            while (word) {
+                const int b = __ffs(word) - 1;
+                word &= word - 1;
+                if (pos < CI_SELF_STRIDE) __stcg(&arow[pos], w * 32 + b);
+                pos++;
+            }
+            out += __shfl_sync(FULLMASK, inc, 31);
+        }
+        const int d = out;
+        if (lane == 0) __stcg(&p.deg_out[r], d);
+        maxd = max(maxd, d);
+        nnz += (u64)d;
+        if (d <= l) continue;
+        if (d > CI_SELF_STRIDE) {  // cannot happen: degrees only fall and the host checked the bound
+            bad = 1;
+            continue;
+        }
+        const u64 nsets = (u64)s_binom[d * (CUSK_ML + 1) + l];
+        sets += nsets;
+        canon += nsets * (u64)(d - l);
+    }
+    if (lane == 0) {
+        if (maxd) atomicMax(&ctl->maxdeg, maxd);
+        if (nnz) atomicAdd((unsigned long long *)&ctl->nnz, (unsigned long long)nnz);
+        if (canon) atomicAdd((unsigned long long *)&ctl->canon, (unsigned long long)canon);
+        if (sets) atomicAdd((unsigned long long *)&ctl->acc_small, (unsigned long long)sets);
+        if (bad) atomicExch(&ctl->infeasible, 4);
+    }
+}
+
+// phase B: work items of `chunk` conditioning sets
+__device__ __forceinline__ void cs_self_items(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom, u64 chunk)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int nw = blockDim.x >> 5;
+    for (int r = blockIdx.x * nw + (tid >> 5); r < p.n; r += gridDim.x * nw) {
+        const int d = __ldcg(&p.deg_out[r]);
+        if (d <= l || d > CI_SELF_STRIDE) continue;
+        const u64 nsets = (u64)s_binom[d * (CUSK_ML + 1) + l];
+        const int cnt = (int)((nsets + chunk - 1) / chunk);
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&ctl->nitems_small, cnt);
+        base = __shfl_sync(FULLMASK, base, 0);
+        for (int k = lane; k < cnt; k += 32) {
+            if (base + k >= p.item_cap) break;  // cannot happen: at most n + total sets / chunk items (see the host)
+            CiItem it;
+            it.X = r;
+            it.d = d;
+            it.row0 = r * CI_SELF_STRIDE;
+            it.pad = 0;
+            it.R0 = (u64)k * chunk;
+            it.R1 = (it.R0 + chunk < nsets) ? it.R0 + chunk : nsets;
+            int4 *dst = (int4 *)&p.self_items[base + k];
+            __stcg(dst, make_int4(it.X, it.d, it.row0, 0));
+            __stcg((ulonglong2 *)(dst + 1), make_ulonglong2(it.R0, it.R1));
+        }
+    }
+}
+
+template <int L0, int L1>
+__device__ __forceinline__ void cs_multi_dispatch(int l, const CiParams &p, LevelCtl *ctl, int nitems, double T2u, CsWarp *s_w,
+                                                  const unsigned *s_binom, double *s_L)
+{
+    if constexpr (L0 <= L1) {
+        if (l == L0)
+            cs_body<true, L0>(p, ctl, p.work_counter_small + L0, p.self_items, p.self_adj, p.item_cap, nitems, T2u, 0, 1, s_w,
+                              s_binom, s_L);
+        else
+            cs_multi_dispatch<L0 + 1, L1>(l, p, ctl, nitems, T2u, s_w, s_binom, s_L);
+    }
+}
+
+// p.ctl and p.work_counter_small are the BASES of the per-level arrays here; levels l_first..l_last (within L0..L1) run.
+template <int L0, int L1>
+__global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2 : 1)
+    ci_small_multi_kernel(const CiParams p, int l_first, int l_last, int maxl)
+{
+    static_assert(CS_NTHREADS(L0) == CS_NTHREADS(L1), "one block size per launch");
+    extern __shared__ double s_L[];  // levels above CS_LREG: l (l - 1) / 2 doubles per thread
+    __shared__ CsWarp s_w[CS_NWARPS(L0)];
+    __shared__ unsigned s_binom[(CS_DMAX + 1) * (CUSK_ML + 1)];
+    pdl_enter();
+    LevelCtl *base = p.ctl;
+    const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
+    if (base[l_first - 1].done) {  // an earlier launch ended the run (complete before this one started: the same for every CTA)
+        if (lead)
+            for (int k = l_first; k <= maxl; k++) base[k].done = 1;
+        return;
+    }
+    cs_fill_binom(s_binom);
+    __syncthreads();
+    unsigned *bar = &base[l_first].ticket;  // zero at the start of a call; counts arrivals of all barriers of this launch
+    unsigned epoch = 0;
+    const u64 lanes = (u64)gridDim.x * blockDim.x;
+    for (int l = l_first; l <= l_last; l++) {
+        LevelCtl *ctl = base + l;
+        if (lead) ctl->t_begin = cs_globaltimer();
+        cs_self_rows(p, l, ctl, s_binom);
+        cs_grid_barrier(bar, ++epoch * gridDim.x);
+        const u64 sets = *(volatile u64 *)&ctl->acc_small;
+        const bool stop = sets == 0 || *(volatile int *)&ctl->infeasible != 0;
+        double T2u;
+        {
+            const double m = (double)__float2int_rz(p.n_uniform);
+            const double t = tanh(p.th_het / sqrt(m - (double)l - 3.0));
+            T2u = t * t;
+        }
+        if (stop) {  // no row has more than l neighbours: this level and all later ones do not run
+            if (lead) {
+                ctl->T2 = T2u;
+                for (int k = l; k <= maxl; k++) base[k].done = 1;
+            }
+            return;
+        }
+        // one item per warp of the launch while the level is light (fewest row stagings), four per warp when it is not
+        u64 per = (sets + lanes - 1) / lanes;
+        if (sets > 8 * lanes) per = (sets + 4 * lanes - 1) / (4 * lanes);
+        cs_self_items(p, l, ctl, s_binom, 32 * per);
+        cs_grid_barrier(bar, ++epoch * gridDim.x);
+        int nitems = *(volatile int *)&ctl->nitems_small;
+        if (nitems > p.item_cap) nitems = p.item_cap;
+        if (lead) {
+            ctl->T2 = T2u;
+            ctl->done = 0;
+            ctl->t_planned = cs_globaltimer();
+        }
+        cs_multi_dispatch<L0, L1>(l, p, ctl, nitems, T2u, s_w, s_binom, s_L);
+        cs_grid_barrier(bar, ++epoch * gridDim.x);  // the level's removals are in memory
+        if (lead) ctl->t_end = cs_globaltimer();
+    }
+}
+
+template <int L0, int L1>
+static int cs_launch_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl)
+{
+    constexpr int NT = CS_NTHREADS(L0);
+    constexpr int dyn = (L1 <= CS_LREG) ? 0 : L1 * (L1 - 1) / 2 * 8 * NT;
     static std::atomic<int> ctas_of_device[CUSK_MAX_DEVICES];
     int dev = 0;
     cudaGetDevice(&dev);
     dev = (dev >= 0 && dev < CUSK_MAX_DEVICES) ? dev : 0;
     int ctas_per_sm = ctas_of_device[dev].load(std::memory_order_acquire);
     if (!ctas_per_sm) {
-        if (dyn > 0 && cudaFuncSetAttribute(ci_small_kernel<true, LT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            dyn) != cudaSuccess) {
-            cusk_set_error("cudaFuncSetAttribute(ci_small_kernel<%d, self>, %d B): %s", LT, dyn,
+        if (dyn > 0 && cudaFuncSetAttribute(ci_small_multi_kernel<L0, L1>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn) !=
+                           cudaSuccess) {
+            cusk_set_error("cudaFuncSetAttribute(ci_small_multi_kernel<%d, %d>, %d B): %s", L0, L1, dyn,
                            cudaGetErrorString(cudaGetLastError()));
             return CUSK_E_CUDA;
         }
         int nb = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ci_small_kernel<true, LT, true>, NT, dyn) != cudaSuccess ||
-            nb < 1)
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, ci_small_multi_kernel<L0, L1>, NT, dyn) != cudaSuccess || nb < 1)
             nb = 1;
-        ctas_per_sm = nb;
-        ctas_of_device[dev].store(nb, std::memory_order_release);
+        ctas_per_sm = nb > 2 ? 2 : nb;
+        ctas_of_device[dev].store(ctas_per_sm, std::memory_order_release);
     }
     CiParams q = p;
-    void *args[] = {&q};
-    const cudaError_t e = cudaLaunchCooperativeKernel((const void *)ci_small_kernel<true, LT, true>,
+    void *args[] = {&q, &l_first, &l_last, &maxl};
+    const cudaError_t e = cudaLaunchCooperativeKernel((const void *)ci_small_multi_kernel<L0, L1>,
                                                       dim3((p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm), dim3(NT), args,
                                                       dyn, st);
     if (e != cudaSuccess) {
-        cusk_set_error("cooperative launch of ci_small_kernel<%d, self>: %s", LT, cudaGetErrorString(e));
+        cusk_set_error("cooperative launch of ci_small_multi_kernel<%d, %d>: %s", L0, L1, cudaGetErrorString(e));
         return CUSK_E_CUDA;
     }
     return CUSK_OK;
 }
 
-int launch_ci_small_self(cudaStream_t st, const CiParams &p)
+// Levels l_first..l_last (4 <= l_first) of the het engine as up to three cooperative launches; returns the launch count in
+// *launches.  p.ctl / p.work_counter_small: bases of the per-level arrays.
+int launch_ci_small_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl, int *launches)
 {
-    switch (p.l) {
-        case 4: return cs_launch_self<4>(st, p);
-        case 5: return cs_launch_self<5>(st, p);
-        case 6: return cs_launch_self<6>(st, p);
-        case 7: return cs_launch_self<7>(st, p);
-        case 8: return cs_launch_self<8>(st, p);
-        case 9: return cs_launch_self<9>(st, p);
-        case 10: return cs_launch_self<10>(st, p);
-        case 11: return cs_launch_self<11>(st, p);
-        case 12: return cs_launch_self<12>(st, p);
-        case 13: return cs_launch_self<13>(st, p);
-        case 14: return cs_launch_self<14>(st, p);
-        default: cusk_set_error("launch_ci_small_self: level %d", p.l); return CUSK_E_ARG;
-    }
+    int rc = CUSK_OK, nl = 0;
+    auto span = [&](int lo, int hi, auto fn) {
+        const int a = l_first > lo ? l_first : lo, b = l_last < hi ? l_last : hi;
+        if (a <= b && rc == CUSK_OK) rc = (nl++, fn(a, b));
+    };
+    span(CI_DFS_LMIN + 1, 6, [&](int a, int b) { return cs_launch_multi<CI_DFS_LMIN + 1, 6>(st, p, a, b, maxl); });
+    span(7, CS_LREG, [&](int a, int b) { return cs_launch_multi<7, CS_LREG>(st, p, a, b, maxl); });
+    span(CS_LREG + 1, CUSK_ML, [&](int a, int b) { return cs_launch_multi<CS_LREG + 1, CUSK_ML>(st, p, a, b, maxl); });
+    if (launches) *launches = nl;
+    return rc;
 }
 
 template <bool HET, int LT>

@@ -31,7 +31,7 @@ void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, in
 void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits);
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
-int launch_ci_small_self(cudaStream_t st, const CiParams &p);
+int launch_ci_small_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl, int *launches);
 int launch_ci_small(cudaStream_t st, bool het, const CiParams &p);
 int launch_ci_mid(cudaStream_t st, bool het, const CiParams &p);
 int launch_ci_dfs(cudaStream_t st, bool het, const CiParams &p, bool wide);
@@ -138,13 +138,13 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     CiItem *d_items_mid = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)item_cap);
     if (!d_items || !d_items_small || !d_items_mid) return CUSK_E_CUDA;
 
-    // self-planned deep levels (ci_small.cu, SELF): het engine on one GPU, skeletons of at most CI_SELF_NMAX variables
-    static const bool self_env = [] {
-        const char *e = getenv("CUSK_SELF_PLAN");
-        return !(e && atoi(e) == 0);
-    }();
+    // self-planned deep levels (ci_small.cu, multi-level kernel): het engine on one GPU, skeletons of at most CI_SELF_NMAX
+    // variables whose rows are all short by level CI_DFS_LMIN
+    const char *self_e = getenv("CUSK_SELF_PLAN");  // read on every call (tests compare the two routes)
+    const bool self_env = !(self_e && atoi(self_e) == 0);
     const bool self_ok = self_env && a.het && !sh && n <= CI_SELF_NMAX && maxl > CI_DFS_LMIN;
-    const int self_cap = n * CI_SELF_MAXI;
+    // items of a self-planned level: at most one partial item per row plus (sets / chunk) <= lanes / 8 full ones
+    const int self_cap = n + ctx->sm_count * 64 + 64;
     int *d_self_adj = nullptr;
     CiItem *d_self_items = nullptr;
     if (self_ok) {
@@ -152,6 +152,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         d_self_items = (CiItem *)arena_take(ctx, sizeof(CiItem) * (size_t)self_cap);
         if (!d_self_adj || !d_self_items) return CUSK_E_CUDA;
     }
+    int self_first = 0, self_last = -1;  // levels that ran inside the multi-level launches
 
     cudaEvent_t *ev = ctx->ev;
     // per-level and per-kernel-group events are instrumentation (cusk_stats.level_ms / ci_kernel_ms): three records per
@@ -195,13 +196,42 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         LevelCtl *ctl = d_ctl + l;
         const LevelCtl *prev = (l > 1) ? d_ctl + (l - 1) : nullptr;
         // from level 2 on (the CSR arrays exist) the plan and the compaction are one launch when the grid fits the device
-        // deep levels of a light block: no separate plan / compaction, the CI kernel plans itself (degrees only fall, so the
-        // bound read at level 3 holds for the rest of the call)
-        const bool self_level = self_ok && l > CI_DFS_LMIN && maxdeg_bound <= CI_SELF_DMAX;
-        const bool fused = l >= 2 && fusable && !self_level;
-        if (!self_level) nl++;
-        if (!self_level)
-            CUSK_CUDA(launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
+        // deep levels of a light block: no separate plan / compaction / launch per level, the thread-per-set kernel plans
+        // its levels itself (degrees only fall, so the bound read at level 3 holds for the rest of the call)
+        if (self_ok && l > CI_DFS_LMIN && maxdeg_bound <= CI_SELF_DMAX) {
+            const int l_last = std::min(maxl, maxdeg_bound - 1);
+            CiParams p = {};
+            p.C = a.dC;
+            p.N = dN;
+            p.time_index = a.d_time;
+            p.n = n;
+            p.l = l;
+            p.rw = rw;
+            p.bits = a.dbits;
+            p.ctl = d_ctl;                       // bases of the per-level arrays
+            p.work_counter_small = d_work_small;
+            p.th_het = (double)a.th_het;
+            p.smem_bytes = smem_bytes;
+            p.shard_world = 1;
+            p.sm_count = ctx->sm_count;
+            p.self_adj = d_self_adj;
+            p.self_items = d_self_items;
+            p.item_cap = self_cap;
+            p.deg_out = d_deg;
+            p.n_uniform = n_uniform;
+            int launched = 0;
+            const int rc = launch_ci_small_multi(st, p, l, l_last, maxl, &launched);
+            nl += launched;
+            if (rc) return rc;
+            CUSK_CUDA(cudaGetLastError());
+            self_first = l;
+            self_last = l_last;
+            l_stop = l_last + 1;
+            break;
+        }
+        const bool fused = l >= 2 && fusable;
+        nl++;
+        CUSK_CUDA(launch_degree_plan(st, a.dbits, n, rw, d_deg, l, d_rowptr, d_itemstart, d_chunk, ctl, prev,
                                      a.het ? -1.0 : (double)a.Th[l], (double)a.th_het, n_uniform, d_work + l,
                                      d_work_small + l, d_work_mid + l, sh ? sh->world : 1, ctx->sm_count, shard_min_tests,
                                      fused, d_adj, d_minkey, d_items, d_items_small, d_items_mid, item_cap));
@@ -252,10 +282,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         // that the host never has to read the plan back: one fixed-size stream-ordered collective per level.
         if (sh && d_removed) CUSK_CUDA(cudaMemsetAsync(d_removed, 0, std::max<size_t>(flag_stride, 16), st));
         const unsigned classes = ci_classes_possible(l, maxdeg_bound);
-        if (!fused && !self_level)
+        if (!fused)
             nl++, launch_compact(st, a.dbits, n, rw, d_rowptr, d_adj, d_minkey, ctl, d_deg, d_itemstart, d_chunk, l, d_items,
                                  d_items_small, d_items_mid, item_cap);
-        CiParams p;
+        CiParams p = {};
         p.C = a.dC;
         p.N = a.het ? dN : nullptr;
         p.time_index = a.het ? a.d_time : nullptr;
@@ -282,23 +312,8 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.removed = sh ? d_removed : nullptr;
         p.shard_rank = sh ? sh->rank : 0;  // used by the kernels only when the level's plan set shard_on
         p.shard_world = sh ? sh->world : 1;
-        p.prev = prev;
-        p.self_adj = d_self_adj;
-        p.self_items = d_self_items;
-        p.deg_out = d_deg;
-        p.n_uniform = n_uniform;
         if (timing) CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = CUSK_OK;
-        if (self_level) {
-            p.adj = d_self_adj;
-            p.items_small = d_self_items;
-            p.item_cap = self_cap;
-            rc = (nl++, launch_ci_small_self(st, p));
-            if (rc) return rc;
-            if (timing) CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l + 1], st));
-            CUSK_CUDA(cudaGetLastError());
-            continue;
-        }
         if (classes & 1u) rc = (nl++, launch_ci_level(st, a.het, p, grid));  // hub rows
         if (rc) return rc;
         if (classes & 2u) rc = (nl++, launch_ci_small(st, a.het, p));  // the level's short rows (thread per conditioning set)
@@ -398,6 +413,14 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         if (maxl == 0) stats->edges_after[0] = (int64_t)(h_ctl[CUSK_ML + 1].nnz / 2);
         for (int l = 0; timing && l < l_end; l++) {
             float ms = 0.f;
+            if (l >= self_first && l <= self_last) {
+                // levels inside a multi-level launch: %globaltimer stamps of the kernel instead of events
+                if (!h_ctl[l].done && h_ctl[l].t_end > h_ctl[l].t_begin) {
+                    stats->level_ms[l] = (float)((double)(h_ctl[l].t_end - h_ctl[l].t_begin) * 1e-6);
+                    stats->ci_kernel_ms[l] = (float)((double)(h_ctl[l].t_end - h_ctl[l].t_planned) * 1e-6);
+                }
+                continue;
+            }
             if (cudaEventElapsedTime(&ms, ev[l], ev[l + 1]) == cudaSuccess) stats->level_ms[l] = ms;
             if (l >= 1 && !h_ctl[l].done &&
                 cudaEventElapsedTime(&ms, ev[(CUSK_ML + 2) + 2 * l], ev[(CUSK_ML + 2) + 2 * l + 1]) == cudaSuccess)
@@ -411,6 +434,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
     }
     if (infeasible == 1) {
         cusk_set_error("skeleton: a row needs >= 2^48 conditioning sets at some level (degree too large)");
+        return CUSK_E_INFEASIBLE;
+    }
+    if (infeasible > 2) {
+        cusk_set_error("skeleton: internal bound violated at some level (code %d)", infeasible);
         return CUSK_E_INFEASIBLE;
     }
     if (infeasible == 2) {

@@ -39,6 +39,7 @@ struct LevelCtl {
     u64 acc_mid;
     int plan_ready;  // fused plan + compaction: set by the planning CTA once the level's plan is in memory
     int pad3;
+    u64 t_begin, t_planned, t_end;  // levels inside a multi-level launch (ci_small.cu): %globaltimer at start / after the plan / at the end
 };
 
 // One work item of the CI kernel, decoded once per level by items_kernel (the CI kernel's CTAs then
@@ -72,9 +73,8 @@ struct CiParams {
     unsigned char *removed;       // edge-sharded het engine: removed[slot of (X,Y) in the level's CSR] = 1
     int shard_rank, shard_world;  // this launch takes items rank, rank + world, ... (1 GPU: 0, 1)
     int sm_count;                 // persistent grids: CTAs per SM (occupancy) x this
-    // self-planned levels (ci_small.cu, SELF): the level's degrees, fixed-stride adjacency and work items are produced by
-    // the CI kernel's own prologue; adj == self_adj and items_small == self_items then
-    const LevelCtl *prev;  // the previous level's control block (its `done` ends this level too)
+    // self-planned levels (ci_small.cu, multi-level kernel): the level's degrees, fixed-stride adjacency and work items are
+    // produced inside the launch; ctl and work_counter_small are the BASES of the per-level arrays there
     int *self_adj;         // [n][CI_SELF_STRIDE] neighbours at level start, rows of at most CI_SELF_STRIDE neighbours
     CiItem *self_items;    // [item_cap]
     int *deg_out;          // [n]
@@ -83,9 +83,7 @@ struct CiParams {
 
 #define CI_SELF_STRIDE 32    // = CI_SMALL_DMAX: every row of a self-planned level fits the thread-per-set kernel
 #define CI_SELF_DMAX 22      // the host takes the self-planned form when no row has more neighbours than this ...
-#define CI_SELF_NMAX 8192    // ... and the skeleton has at most this many variables (item table: n x CI_SELF_MAXI x 32 B)
-#define CI_SELF_MAXI 64      // work items per row at most
-#define CI_SELF_ITEM_TESTS 128  // ... of at least this many tests each
+#define CI_SELF_NMAX 8192    // ... and the skeleton has at most this many variables
 
 struct DfsTuning {
     int span, dmin, ipsm, lnarrow;
