@@ -127,16 +127,16 @@ __device__ __forceinline__ void cs_body(const CiParams &p, LevelCtl *ctl, int *w
         __syncwarp();
         {
             const int myv = (lane < d) ? S.adj[lane] : 0;
-            for (int i0 = 0; i0 < d; i0 += 8) {  // eight independent gathers in flight per lane
-                float v[8];
+            for (int i0 = 0; i0 < d; i0 += 16) {  // sixteen independent gathers in flight per lane: two round trips per row
+                float v[16];
 #pragma unroll
-                for (int u = 0; u < 8; u++) {
+                for (int u = 0; u < 16; u++) {
                     const int i = i0 + u;
                     v[u] = 1.0f;
                     if (i < d && lane < d && i != lane) v[u] = __ldg(&p.C[(size_t)S.adj[i] * n + myv]);
                 }
 #pragma unroll
-                for (int u = 0; u < 8; u++)
+                for (int u = 0; u < 16; u++)
                     if (i0 + u < d && lane < d) S.csub[(i0 + u) * CS_STRIDE + lane] = v[u];
             }
         }
@@ -337,8 +337,10 @@ __device__ __forceinline__ void cs_grid_barrier(unsigned *bar, unsigned target)
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(bar, 1u);
-        while (*(volatile unsigned *)bar < target) __nanosleep(32);
-        __threadfence();
+        unsigned seen;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(bar) : "memory");
+        } while (seen < target);
     }
     __syncthreads();
 }
@@ -350,20 +352,65 @@ __device__ __forceinline__ unsigned long long cs_globaltimer()
     return t;
 }
 
-// phase A of a level: degrees, fixed-stride adjacency, level totals
-__device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom)
+// conditioning sets per work item of a level with `sets` sets on a launch of `lanes` threads: one item per warp of the
+// launch while the level is light (fewest row stagings), four per warp when it is not
+__device__ __forceinline__ u64 cs_self_chunk(u64 sets, u64 lanes)
 {
+    u64 per = (sets + lanes - 1) / lanes;
+    if (sets > 8 * lanes) per = (sets + 4 * lanes - 1) / (4 * lanes);
+    return 32 * (per ? per : 1);
+}
+
+// the work items of row r (d neighbours, nsets conditioning sets at this level), `chunk` sets each
+__device__ __forceinline__ void cs_self_emit(const CiParams &p, LevelCtl *ctl, int r, int d, u64 nsets, u64 chunk, int lane)
+{
+    const int cnt = (int)((nsets + chunk - 1) / chunk);
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&ctl->nitems_small, cnt);
+    base = __shfl_sync(FULLMASK, base, 0);
+    for (int k = lane; k < cnt; k += 32) {
+        if (base + k >= p.item_cap) break;  // cannot happen: at most n + total sets / chunk items (see the host)
+        const u64 R0 = (u64)k * chunk;
+        const u64 R1 = (R0 + chunk < nsets) ? R0 + chunk : nsets;
+        int4 *dst = (int4 *)&p.self_items[base + k];
+        __stcg(dst, make_int4(r, d, r * CI_SELF_STRIDE, 0));
+        __stcg((ulonglong2 *)(dst + 1), make_ulonglong2(R0, R1));
+    }
+}
+
+// phase A of a level: degrees, fixed-stride adjacency, level totals; the row's bitmap words are fetched in one batch (the
+// next row's while this one is expanded), so a warp pays one L2 round trip per row instead of one per 32 words.
+//   EMIT: the items are cut here, `chunk` sets each (chunk from the bound the previous level left in its acc_mid)
+template <bool EMIT>
+__device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom, u64 chunk)
+{
+    constexpr int KW = (CI_SELF_NMAX / 32 + 31) / 32;  // bitmap words of a row per lane
     const int tid = threadIdx.x, lane = tid & 31;
     const int nw = blockDim.x >> 5;
     const int n = p.n, rw = p.rw;
-    u64 canon = 0, nnz = 0, sets = 0;
+    const int stride = gridDim.x * nw;
+    u64 canon = 0, nnz = 0, sets = 0, next = 0;
     int maxd = 0, bad = 0;
-    for (int r = blockIdx.x * nw + (tid >> 5); r < n; r += gridDim.x * nw) {
+    uint32_t cur[KW], nxt[KW];
+    int r = blockIdx.x * nw + (tid >> 5);
+#pragma unroll
+    for (int k = 0; k < KW; k++) {
+        const int w = k * 32 + lane;
+        nxt[k] = (r < n && w < rw) ? __ldcg(&p.bits[(size_t)r * rw + w]) : 0u;
+    }
+    for (; r < n; r += stride) {
+#pragma unroll
+        for (int k = 0; k < KW; k++) {
+            cur[k] = nxt[k];
+            const int w = k * 32 + lane;
+            nxt[k] = (r + stride < n && w < rw) ? __ldcg(&p.bits[(size_t)(r + stride) * rw + w]) : 0u;
+        }
         int out = 0;
         int *arow = p.self_adj + (size_t)r * CI_SELF_STRIDE;
-        for (int w0 = 0; w0 < rw; w0 += 32) {
-            const int w = w0 + lane;
-            uint32_t word = (w < rw) ? __ldcg(&p.bits[(size_t)r * rw + w]) : 0u;
+#pragma unroll
+        for (int k = 0; k < KW; k++) {
+            if (k * 32 >= rw) break;
+            uint32_t word = cur[k];
             const int cnt = __popc(word);
             int inc = cnt;
             for (int o = 1; o < 32; o <<= 1) {
@@ -374,7 +421,7 @@ __device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl 
             while (word) {
                 const int b = __ffs(word) - 1;
                 word &= word - 1;
-                if (pos < CI_SELF_STRIDE) __stcg(&arow[pos], w * 32 + b);
+                if (pos < CI_SELF_STRIDE) __stcg(&arow[pos], (k * 32 + lane) * 32 + b);
                 pos++;
             }
             out += __shfl_sync(FULLMASK, inc, 31);
@@ -391,17 +438,20 @@ __device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl 
         const u64 nsets = (u64)s_binom[d * (CUSK_ML + 1) + l];
         sets += nsets;
         canon += nsets * (u64)(d - l);
+        if (l < CUSK_ML && d > l + 1) next += (u64)s_binom[d * (CUSK_ML + 1) + l + 1];
+        if (EMIT) cs_self_emit(p, ctl, r, d, nsets, chunk, lane);
     }
     if (lane == 0) {
         if (maxd) atomicMax(&ctl->maxdeg, maxd);
         if (nnz) atomicAdd((unsigned long long *)&ctl->nnz, (unsigned long long)nnz);
         if (canon) atomicAdd((unsigned long long *)&ctl->canon, (unsigned long long)canon);
         if (sets) atomicAdd((unsigned long long *)&ctl->acc_small, (unsigned long long)sets);
+        if (next) atomicAdd((unsigned long long *)&ctl->acc_mid, (unsigned long long)next);  // bound of level l + 1's sets
         if (bad) atomicExch(&ctl->infeasible, 4);
     }
 }
 
-// phase B: work items of `chunk` conditioning sets
+// phase B (first self-planned level of a call only: no bound from a previous level): work items of `chunk` sets
 __device__ __forceinline__ void cs_self_items(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom, u64 chunk)
 {
     const int tid = threadIdx.x, lane = tid & 31;
@@ -409,24 +459,7 @@ __device__ __forceinline__ void cs_self_items(const CiParams &p, int l, LevelCtl
     for (int r = blockIdx.x * nw + (tid >> 5); r < p.n; r += gridDim.x * nw) {
         const int d = __ldcg(&p.deg_out[r]);
         if (d <= l || d > CI_SELF_STRIDE) continue;
-        const u64 nsets = (u64)s_binom[d * (CUSK_ML + 1) + l];
-        const int cnt = (int)((nsets + chunk - 1) / chunk);
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&ctl->nitems_small, cnt);
-        base = __shfl_sync(FULLMASK, base, 0);
-        for (int k = lane; k < cnt; k += 32) {
-            if (base + k >= p.item_cap) break;  // cannot happen: at most n + total sets / chunk items (see the host)
-            CiItem it;
-            it.X = r;
-            it.d = d;
-            it.row0 = r * CI_SELF_STRIDE;
-            it.pad = 0;
-            it.R0 = (u64)k * chunk;
-            it.R1 = (it.R0 + chunk < nsets) ? it.R0 + chunk : nsets;
-            int4 *dst = (int4 *)&p.self_items[base + k];
-            __stcg(dst, make_int4(it.X, it.d, it.row0, 0));
-            __stcg((ulonglong2 *)(dst + 1), make_ulonglong2(it.R0, it.R1));
-        }
+        cs_self_emit(p, ctl, r, d, (u64)s_binom[d * (CUSK_ML + 1) + l], chunk, lane);
     }
 }
 
@@ -468,7 +501,13 @@ __global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2
     for (int l = l_first; l <= l_last; l++) {
         LevelCtl *ctl = base + l;
         if (lead) ctl->t_begin = cs_globaltimer();
-        cs_self_rows(p, l, ctl, s_binom);
+        // every level but the call's first self-planned one (p.l) knows an upper bound of its set total: the level before
+        // it summed C(d, l) over its own rows (degrees only fall), so the items are cut in the row phase itself
+        const bool emit = l > p.l;
+        if (emit)
+            cs_self_rows<true>(p, l, ctl, s_binom, cs_self_chunk(*(volatile u64 *)&base[l - 1].acc_mid, lanes));
+        else
+            cs_self_rows<false>(p, l, ctl, s_binom, 0);
         cs_grid_barrier(bar, ++epoch * gridDim.x);
         const u64 sets = *(volatile u64 *)&ctl->acc_small;
         const bool stop = sets == 0 || *(volatile int *)&ctl->infeasible != 0;
@@ -485,11 +524,10 @@ __global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2
             }
             return;
         }
-        // one item per warp of the launch while the level is light (fewest row stagings), four per warp when it is not
-        u64 per = (sets + lanes - 1) / lanes;
-        if (sets > 8 * lanes) per = (sets + 4 * lanes - 1) / (4 * lanes);
-        cs_self_items(p, l, ctl, s_binom, 32 * per);
-        cs_grid_barrier(bar, ++epoch * gridDim.x);
+        if (!emit) {
+            cs_self_items(p, l, ctl, s_binom, cs_self_chunk(sets, lanes));
+            cs_grid_barrier(bar, ++epoch * gridDim.x);
+        }
         int nitems = *(volatile int *)&ctl->nitems_small;
         if (nitems > p.item_cap) nitems = p.item_cap;
         if (lead) {
@@ -504,7 +542,7 @@ __global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2
 }
 
 template <int L0, int L1>
-static int cs_launch_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl)
+static int cs_launch_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl, bool coop)
 {
     constexpr int NT = CS_NTHREADS(L0);
     constexpr int dyn = (L1 <= CS_LREG) ? 0 : L1 * (L1 - 1) / 2 * 8 * NT;
@@ -526,11 +564,20 @@ static int cs_launch_multi(cudaStream_t st, const CiParams &p, int l_first, int 
         ctas_per_sm = nb > 2 ? 2 : nb;
         ctas_of_device[dev].store(ctas_per_sm, std::memory_order_release);
     }
+    const dim3 grid((p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm);
+    if (!coop) {
+        // plain (programmatic dependent) launch: the grid fits the device, so its CTAs are co-resident unless ANOTHER
+        // barrier-synchronised grid runs beside it -- the caller serialises those (skeleton.cu)
+        const cudaError_t e = launch_k(ci_small_multi_kernel<L0, L1>, grid, dim3(NT), dyn, st, p, l_first, l_last, maxl);
+        if (e != cudaSuccess) {
+            cusk_set_error("launch of ci_small_multi_kernel<%d, %d>: %s", L0, L1, cudaGetErrorString(e));
+            return CUSK_E_CUDA;
+        }
+        return CUSK_OK;
+    }
     CiParams q = p;
     void *args[] = {&q, &l_first, &l_last, &maxl};
-    const cudaError_t e = cudaLaunchCooperativeKernel((const void *)ci_small_multi_kernel<L0, L1>,
-                                                      dim3((p.sm_count > 0 ? p.sm_count : 148) * ctas_per_sm), dim3(NT), args,
-                                                      dyn, st);
+    const cudaError_t e = cudaLaunchCooperativeKernel((const void *)ci_small_multi_kernel<L0, L1>, grid, dim3(NT), args, dyn, st);
     if (e != cudaSuccess) {
         cusk_set_error("cooperative launch of ci_small_multi_kernel<%d, %d>: %s", L0, L1, cudaGetErrorString(e));
         return CUSK_E_CUDA;
@@ -540,16 +587,16 @@ static int cs_launch_multi(cudaStream_t st, const CiParams &p, int l_first, int 
 
 // Levels l_first..l_last (4 <= l_first) of the het engine as up to three cooperative launches; returns the launch count in
 // *launches.  p.ctl / p.work_counter_small: bases of the per-level arrays.
-int launch_ci_small_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl, int *launches)
+int launch_ci_small_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl, bool coop, int *launches)
 {
     int rc = CUSK_OK, nl = 0;
     auto span = [&](int lo, int hi, auto fn) {
         const int a = l_first > lo ? l_first : lo, b = l_last < hi ? l_last : hi;
         if (a <= b && rc == CUSK_OK) rc = (nl++, fn(a, b));
     };
-    span(CI_DFS_LMIN + 1, 6, [&](int a, int b) { return cs_launch_multi<CI_DFS_LMIN + 1, 6>(st, p, a, b, maxl); });
-    span(7, CS_LREG, [&](int a, int b) { return cs_launch_multi<7, CS_LREG>(st, p, a, b, maxl); });
-    span(CS_LREG + 1, CUSK_ML, [&](int a, int b) { return cs_launch_multi<CS_LREG + 1, CUSK_ML>(st, p, a, b, maxl); });
+    span(CI_DFS_LMIN + 1, 6, [&](int a, int b) { return cs_launch_multi<CI_DFS_LMIN + 1, 6>(st, p, a, b, maxl, coop); });
+    span(7, CS_LREG, [&](int a, int b) { return cs_launch_multi<7, CS_LREG>(st, p, a, b, maxl, coop); });
+    span(CS_LREG + 1, CUSK_ML, [&](int a, int b) { return cs_launch_multi<CS_LREG + 1, CUSK_ML>(st, p, a, b, maxl, coop); });
     if (launches) *launches = nl;
     return rc;
 }

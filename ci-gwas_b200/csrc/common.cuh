@@ -80,6 +80,10 @@ struct cusk_ctx {
     // [3(ML+2)+4, 5(ML+2)+4): exchange start/stop per level (edge-sharded mode)
     cudaEvent_t ev[5 * (CUSK_ML + 2) + 4];
     cudaEvent_t ev_inputs = nullptr;  // the host-buffer arguments of the current call have reached the device
+    // side stream of the engine: at level 2 the thread-per-set kernel (short rows) and ci_mid_kernel (medium rows) are
+    // independent and each fills about a third of the warp slots, so they run side by side (fork / join by events)
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool ev_ready = false;
     // host work of the calling entry point that does not depend on the device's result (zero-filling the caller's output
     // matrix): the engine runs it once, just before one of its stream synchronisations, while the device is busy

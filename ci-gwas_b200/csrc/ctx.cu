@@ -68,6 +68,9 @@ extern "C" int cusk_ctx_create(int device_id, cusk_ctx **out)
     CUSK_CUDA(cudaMallocHost(&ctx->h_pinned, ctx->h_pinned_bytes));
     for (auto &ev : ctx->ev) CUSK_CUDA(cudaEventCreate(&ev));
     CUSK_CUDA(cudaEventCreateWithFlags(&ctx->ev_inputs, cudaEventDisableTiming));
+    CUSK_CUDA(cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    CUSK_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    CUSK_CUDA(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
     ctx->ev_ready = true;
     {
         const char *e = getenv("CUSK_LEVEL_TIMING");
@@ -90,7 +93,10 @@ extern "C" void cusk_ctx_destroy(cusk_ctx *ctx)
     {
         for (auto &ev : ctx->ev) cudaEventDestroy(ev);
         if (ctx->ev_inputs) cudaEventDestroy(ctx->ev_inputs);
+        if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+        if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     }
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

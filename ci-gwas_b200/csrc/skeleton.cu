@@ -31,7 +31,7 @@ void launch_expand_bits(cudaStream_t st, const uint32_t *bits, int n, int rw, in
 void launch_pack_bits(cudaStream_t st, const int *G, int n, int rw, uint32_t *bits);
 void launch_ess_minmax(cudaStream_t st, const float *N, int n, int *mn, int *mx, int sm_count);
 int launch_ci_level(cudaStream_t st, bool het, const CiParams &p, int grid);
-int launch_ci_small_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl, int *launches);
+int launch_ci_small_multi(cudaStream_t st, const CiParams &p, int l_first, int l_last, int maxl, bool coop, int *launches);
 int launch_ci_small(cudaStream_t st, bool het, const CiParams &p);
 int launch_ci_mid(cudaStream_t st, bool het, const CiParams &p);
 int launch_ci_dfs(cudaStream_t st, bool het, const CiParams &p, bool wide);
@@ -140,6 +140,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
 
     // self-planned deep levels (ci_small.cu, multi-level kernel): het engine on one GPU, skeletons of at most CI_SELF_NMAX
     // variables whose rows are all short by level CI_DFS_LMIN
+    const char *side_e = getenv("CUSK_SIDE_STREAM");  // level 2: ci_small and ci_mid on two streams (0: one after the other)
+    const bool side_env = !(side_e && atoi(side_e) == 0);
+    const char *coop_e = getenv("CUSK_SELF_COOP");  // 0: the multi-level launches as plain (programmatic dependent) launches
+    const bool self_coop = !(coop_e && atoi(coop_e) == 0);
     const char *self_e = getenv("CUSK_SELF_PLAN");  // read on every call (tests compare the two routes)
     const bool self_env = !(self_e && atoi(self_e) == 0);
     const bool self_ok = self_env && a.het && !sh && n <= CI_SELF_NMAX && maxl > CI_DFS_LMIN;
@@ -220,7 +224,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             p.deg_out = d_deg;
             p.n_uniform = n_uniform;
             int launched = 0;
-            const int rc = launch_ci_small_multi(st, p, l, l_last, maxl, &launched);
+            const int rc = launch_ci_small_multi(st, p, l, l_last, maxl, self_coop, &launched);
             nl += launched;
             if (rc) return rc;
             CUSK_CUDA(cudaGetLastError());
@@ -314,12 +318,23 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         p.shard_world = sh ? sh->world : 1;
         if (timing) CUSK_CUDA(cudaEventRecord(ev[(CUSK_ML + 2) + 2 * l], st));
         int rc = CUSK_OK;
+        // level 2: the short rows' kernel and the medium rows' kernel side by side (each alone keeps a quarter to a third
+        // of the warp slots busy, profiles/r2_ci_kernels_full_summary.txt); the medium rows go first, on the side stream
+        const bool side = side_env && l == CI_MID_LMAX && (classes & 2u) && (classes & 4u) && ctx->stream2;
+        if (side) {
+            CUSK_CUDA(cudaEventRecord(ctx->ev_fork, st));
+            CUSK_CUDA(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+            rc = (nl++, launch_ci_mid(ctx->stream2, a.het, p));
+            if (rc) return rc;
+            CUSK_CUDA(cudaEventRecord(ctx->ev_join, ctx->stream2));
+        }
         if (classes & 1u) rc = (nl++, launch_ci_level(st, a.het, p, grid));  // hub rows
         if (rc) return rc;
         if (classes & 2u) rc = (nl++, launch_ci_small(st, a.het, p));  // the level's short rows (thread per conditioning set)
         if (rc) return rc;
-        if ((classes & 4u) && l <= CI_MID_LMAX) rc = (nl++, launch_ci_mid(st, a.het, p));  // levels 1-2: the medium rows
+        if ((classes & 4u) && l <= CI_MID_LMAX && !side) rc = (nl++, launch_ci_mid(st, a.het, p));  // levels 1-2: the medium rows
         if (rc) return rc;
+        if (side) CUSK_CUDA(cudaStreamWaitEvent(st, ctx->ev_join, 0));
         if ((classes & 4u) && l > CI_MID_LMAX) {
             // deeper levels: rows of up to 63 neighbours whose sets serve many tests (lanes over the neighbours);
             // narrow (<= 31) and wide rows share the item table, each kernel skips the other's

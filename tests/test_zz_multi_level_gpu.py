@@ -61,6 +61,10 @@ def test_multi_level_route_equals_level_per_launch_route(ctx, oracle, general_n,
     with env(CUSK_SELF_PLAN=1):
         r1 = ctx.hetcor_skeleton(Cm, None, N, th, maxlevel, ti)
         r2 = ctx.hetcor_skeleton(Cm, None, N, th, maxlevel, ti)  # a second call: the control blocks start from zero again
+    with env(CUSK_SELF_PLAN=1, CUSK_SELF_COOP=0):  # the same kernels as plain (programmatic dependent) launches
+        r3 = ctx.hetcor_skeleton(Cm, None, N, th, maxlevel, ti)
+    assert r3["l"] == r0["l"] and (r3["G"] == r0["G"]).all()
+    assert r3["stats"]["tests_canonical"] == r0["stats"]["tests_canonical"]
     s0, s1 = r0["stats"], r1["stats"]
     assert s0["max_degree"][3] <= 22, "the case must qualify for the self-planned route"
     assert r1["l"] == r0["l"] == r2["l"]
