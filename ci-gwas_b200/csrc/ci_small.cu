@@ -30,6 +30,8 @@
 #define CS_NTHREADS(LT) (CS_NWARPS(LT) * 32)
 #define CS_STRIDE (CS_DMAX + 1)
 #define FULLMASK 0xffffffffu
+#define CS_WARP_SETS 4  // multi-level kernel: a level with at most this many sets per warp of the launch runs a warp per set
+static_assert(CI_SELF_DMAX < 32, "the warp-per-set form keeps X in lane d");
 
 struct CsWarp {
     float csub[CS_DMAX * CS_STRIDE];
@@ -71,7 +73,9 @@ struct CsIdx {
 // ---- the level's tests: shared by the one-level kernel and by the self-planned multi-level kernel ---------------------------
 // Everything another CTA may have written during the same launch (the multi-level kernel rebuilds adjacency and items per
 // level) is read with ld.cg: L1 is not coherent across SMs.
-template <bool HET, int LT>
+//   STATIC1 (multi-level kernel): warp w of the launch takes item w first and only then pulls from the queue -- a light level
+//   has about one item per warp, and a few thousand fetches of one counter at the same instant cost microseconds
+template <bool HET, int LT, bool STATIC1 = false>
 __device__ __forceinline__ void cs_body(const CiParams &p, LevelCtl *ctl, int *work_counter, const CiItem *items,
                                         const int *adj, int item_cap, int nitems, double T2u, int srank, int sworld,
                                         CsWarp *s_w, const unsigned *s_binom, double *s_L)
@@ -89,11 +93,22 @@ __device__ __forceinline__ void cs_body(const CiParams &p, LevelCtl *ctl, int *w
     CsWarp &S = s_w[warp];
     u64 my_tests = 0;
     unsigned my_sing = 0;
+    __shared__ unsigned long long s_tot[2];  // tests and dropped pivots of the CTA (one global atomic each at the end)
+    if (tid == 0) s_tot[0] = s_tot[1] = 0ull;
+    __syncthreads();
+    const int warps_total = (int)gridDim.x * (NT / 32);
+    bool first = STATIC1;
 
     for (;;) {
         int item = 0;
-        if (lane == 0) item = srank + sworld * atomicAdd(work_counter, 1);
-        item = __shfl_sync(FULLMASK, item, 0);
+        if (STATIC1 && first) {
+            first = false;
+            item = (int)blockIdx.x * (NT / 32) + warp;
+        } else {
+            if (STATIC1 && nitems <= warps_total) break;
+            if (lane == 0) item = (STATIC1 ? warps_total : 0) + srank + sworld * atomicAdd(work_counter, 1);
+            item = __shfl_sync(FULLMASK, item, 0);
+        }
         if (item >= nitems) break;
         if (item >= item_cap) {  // cannot happen: plan_kernel bounds the item count of a small level
             if (lane == 0) ctl->infeasible = 3;
@@ -282,8 +297,13 @@ __device__ __forceinline__ void cs_body(const CiParams &p, LevelCtl *ctl, int *w
         my_sing += __shfl_xor_sync(FULLMASK, my_sing, o);
     }
     if (lane == 0) {
-        if (my_tests) atomicAdd((unsigned long long *)&ctl->executed, (unsigned long long)my_tests);
-        if (my_sing) atomicAdd((unsigned long long *)&ctl->singular, (unsigned long long)my_sing);
+        if (my_tests) atomicAdd(&s_tot[0], (unsigned long long)my_tests);
+        if (my_sing) atomicAdd(&s_tot[1], (unsigned long long)my_sing);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (s_tot[0]) atomicAdd((unsigned long long *)&ctl->executed, s_tot[0]);
+        if (s_tot[1]) atomicAdd((unsigned long long *)&ctl->singular, s_tot[1]);
     }
 }
 
@@ -382,7 +402,8 @@ __device__ __forceinline__ void cs_self_emit(const CiParams &p, LevelCtl *ctl, i
 // next row's while this one is expanded), so a warp pays one L2 round trip per row instead of one per 32 words.
 //   EMIT: the items are cut here, `chunk` sets each (chunk from the bound the previous level left in its acc_mid)
 template <bool EMIT>
-__device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom, u64 chunk)
+__device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl *ctl, const unsigned *s_binom, u64 chunk,
+                                             unsigned long long *s_acc)
 {
     constexpr int KW = (CI_SELF_NMAX / 32 + 31) / 32;  // bitmap words of a row per lane
     const int tid = threadIdx.x, lane = tid & 31;
@@ -441,13 +462,24 @@ __device__ __forceinline__ void cs_self_rows(const CiParams &p, int l, LevelCtl 
         if (l < CUSK_ML && d > l + 1) next += (u64)s_binom[d * (CUSK_ML + 1) + l + 1];
         if (EMIT) cs_self_emit(p, ctl, r, d, nsets, chunk, lane);
     }
+    // level totals: per CTA in shared memory, then one global atomic per CTA and counter (thousands of warps adding to the
+    // same five words would queue up in L2 for microseconds); s_acc is zero at entry (the kernel clears it per level)
     if (lane == 0) {
-        if (maxd) atomicMax(&ctl->maxdeg, maxd);
-        if (nnz) atomicAdd((unsigned long long *)&ctl->nnz, (unsigned long long)nnz);
-        if (canon) atomicAdd((unsigned long long *)&ctl->canon, (unsigned long long)canon);
-        if (sets) atomicAdd((unsigned long long *)&ctl->acc_small, (unsigned long long)sets);
-        if (next) atomicAdd((unsigned long long *)&ctl->acc_mid, (unsigned long long)next);  // bound of level l + 1's sets
+        if (maxd) atomicMax((unsigned long long *)&s_acc[0], (unsigned long long)maxd);
+        if (nnz) atomicAdd(&s_acc[1], (unsigned long long)nnz);
+        if (canon) atomicAdd(&s_acc[2], (unsigned long long)canon);
+        if (sets) atomicAdd(&s_acc[3], (unsigned long long)sets);
+        if (next) atomicAdd(&s_acc[4], (unsigned long long)next);
         if (bad) atomicExch(&ctl->infeasible, 4);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (s_acc[0]) atomicMax(&ctl->maxdeg, (int)s_acc[0]);
+        if (s_acc[1]) atomicAdd((unsigned long long *)&ctl->nnz, s_acc[1]);
+        if (s_acc[2]) atomicAdd((unsigned long long *)&ctl->canon, s_acc[2]);
+        if (s_acc[3]) atomicAdd((unsigned long long *)&ctl->acc_small, s_acc[3]);
+        if (s_acc[4]) atomicAdd((unsigned long long *)&ctl->acc_mid, s_acc[4]);  // bound of level l + 1's sets
+        s_acc[0] = s_acc[1] = s_acc[2] = s_acc[3] = s_acc[4] = 0ull;  // for the next level (a grid barrier follows)
     }
 }
 
@@ -463,16 +495,196 @@ __device__ __forceinline__ void cs_self_items(const CiParams &p, int l, LevelCtl
     }
 }
 
+// ---- a WARP per conditioning set (multi-level kernel, levels that hold fewer sets than a few per warp) ---------------------
+// With one set per lane the level waits for a single thread's chain of l^3/6 + (d - l) l^2/2 dependent FP64 operations
+// (~30 us at l = 14).  Here the lanes are the COLUMNS of a right-looking elimination on M = C[S, {adj(X), X}]: lane c < d
+// holds neighbour c, lane d holds X; after the pivots s_0..s_{j-1}
+//     w_j[c] = M[s_j][c] - sum_{i<j} (w_i[s_j] / D_i) w_i[c],   D_j = w_j[s_j]
+// (w_i[s_j] comes from lane s_j by a shuffle), so w_j[c] = (L^-1 C[S, c])_j -- the forward-substituted column of cs_body,
+// accumulated in the same order: the two forms take the same decisions bit for bit -- and the chain is ~l^2/2 steps.
+// A set costs ~320 warp instructions here against ~19 per set there (32 sets per instruction), so the kernel takes this
+// form only when the level is short of sets (uniform N only: the per-pair form gathers l^2/2 sample sizes per set).
+template <int LT>
+__device__ __forceinline__ void cs_warp_body(const CiParams &p, LevelCtl *ctl, int *work_counter, const CiItem *items,
+                                             const int *adj, int item_cap, int nitems, double T2u, CsWarp *s_w,
+                                             const unsigned *s_binom)
+{
+    constexpr int LM = LT;
+    constexpr int NT = CS_NTHREADS(LT);
+    constexpr int l = LT;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = p.n;
+    const bool use_time = p.time_index != nullptr;
+    CsWarp &S = s_w[warp];
+    unsigned my_tests = 0, my_sing = 0;  // per warp (lane 0's copy is the warp's)
+    __shared__ unsigned long long s_tot[2];
+    if (tid == 0) s_tot[0] = s_tot[1] = 0ull;
+    __syncthreads();
+    const int warps_total = (int)gridDim.x * (NT / 32);
+    bool first = true;
+
+    for (;;) {
+        int item = 0;
+        if (first) {
+            first = false;
+            item = (int)blockIdx.x * (NT / 32) + warp;
+        } else {
+            if (nitems <= warps_total) break;
+            if (lane == 0) item = warps_total + atomicAdd(work_counter, 1);
+            item = __shfl_sync(FULLMASK, item, 0);
+        }
+        if (item >= nitems) break;
+        if (item >= item_cap) {
+            if (lane == 0) ctl->infeasible = 3;
+            break;
+        }
+        const int4 a4 = __ldcg((const int4 *)&items[item]);
+        const ulonglong2 r2 = __ldcg((const ulonglong2 *)&items[item].R0);
+        const int X = a4.x, d = a4.y, row0 = a4.z;
+        const unsigned R0 = (unsigned)r2.x, R1 = (unsigned)r2.y;
+        const int tX = use_time ? p.time_index[X] : 0;
+
+        // ---- stage the row (as cs_body does) ------------------------------------------------------
+        __syncwarp();
+        {
+            bool gone = false;
+            if (lane < d) {
+                const int v = __ldcg(&adj[row0 + lane]);
+                S.adj[lane] = v;
+                S.cx[lane] = p.C[(size_t)X * n + v];
+                if (use_time) S.time[lane] = p.time_index[v];
+                const uint32_t wbits = __ldcg(&p.bits[(size_t)X * p.rw + (v >> 5)]);
+                gone = !((wbits >> (v & 31)) & 1u);
+            }
+            const unsigned m = __ballot_sync(FULLMASK, gone);
+            if (lane == 0) S.skipmask = m;
+        }
+        __syncwarp();
+        {
+            const int myv = (lane < d) ? S.adj[lane] : 0;
+            for (int i0 = 0; i0 < d; i0 += 16) {
+                float v[16];
+#pragma unroll
+                for (int u = 0; u < 16; u++) {
+                    const int i = i0 + u;
+                    v[u] = 1.0f;
+                    if (i < d && lane < d && i != lane) v[u] = __ldg(&p.C[(size_t)S.adj[i] * n + myv]);
+                }
+#pragma unroll
+                for (int u = 0; u < 16; u++)
+                    if (i0 + u < d && lane < d) S.csub[(i0 + u) * CS_STRIDE + lane] = v[u];
+            }
+        }
+        __syncwarp();
+
+        // ---- the item's sets, one after the other; every lane carries the same positions ------------
+        int pos[LM];
+        {
+            unsigned rank = R0;
+            int x = 0;
+#pragma unroll
+            for (int i = 0; i < LM; i++) {
+                for (;; x++) {
+                    const unsigned c = s_binom[(d - 1 - x) * (CUSK_ML + 1) + (l - 1 - i)];
+                    if (rank < c) break;
+                    rank -= c;
+                }
+                pos[i] = x;
+                x++;
+            }
+        }
+        const bool is_nb = lane < d, is_x = lane == d;
+        const double cxy = is_nb ? (double)S.cx[lane] : 0.0;
+        for (unsigned R = R0; R < R1; R++) {
+            double w[LM], invD[LM];
+            int tS = -2147483647 - 1;
+            unsigned inS = 0;
+            bool any_drop = false;
+#pragma unroll
+            for (int j = 0; j < LM; j++) {
+                const int sj = pos[j];
+                double acc = is_nb ? (double)S.csub[sj * CS_STRIDE + lane] : (is_x ? (double)S.cx[sj] : 0.0);
+#pragma unroll
+                for (int i = 0; i < j; i++) {
+                    const double g = __shfl_sync(FULLMASK, w[i], sj);  // w_i[s_j]
+                    const double lji = g * invD[i];
+                    acc -= lji * w[i];
+                }
+                w[j] = acc;
+                const double D = __shfl_sync(FULLMASK, acc, sj);
+                const bool drop = fabs(D) < CI_PIVOT_TOL;
+                invD[j] = drop ? 0.0 : 1.0 / D;
+                if (drop && j < LM - 1) any_drop = true;
+                inS |= 1u << sj;
+                if (use_time) tS = max(tS, S.time[sj]);
+            }
+            if (any_drop) my_sing++;
+            // X's column (lane d) gives t_x; every lane then has its own column's h01 / h11 against it
+            double h00 = 1.0, h01 = cxy, h11 = 1.0;
+#pragma unroll
+            for (int j = 0; j < LM; j++) {
+                const double t = __shfl_sync(FULLMASK, w[j], d);
+                const double txd = t * invD[j];
+                h00 -= t * txd;
+                h01 -= w[j] * txd;
+                h11 -= w[j] * w[j] * invD[j];
+            }
+            const double c2 = fabs(h00);
+            bool todo = is_nb && !((inS >> lane) & 1u) && !((*(volatile unsigned *)&S.skipmask >> lane) & 1u);
+            if (todo && use_time && tS > max(tX, S.time[lane])) todo = false;
+            my_tests += __popc(__ballot_sync(FULLMASK, todo));
+            if (todo) {
+                const double lhs = h01 * h01;
+                const double den = c2 * fabs(h11);
+                const bool rem = (lhs < T2u * den) || (den > 0.0 && lhs * T2u > den);
+                if (rem) {
+                    const int Y = S.adj[lane];
+                    atomicAnd(&p.bits[(size_t)X * p.rw + (Y >> 5)], ~(1u << (Y & 31)));
+                    atomicAnd(&p.bits[(size_t)Y * p.rw + (X >> 5)], ~(1u << (X & 31)));
+                    atomicOr(&S.skipmask, 1u << lane);
+                }
+            }
+            __syncwarp();
+            // ---- successor set ---------------------------------------------------------------------
+            int ii = -1;
+#pragma unroll
+            for (int j = 0; j < LM; j++)
+                if (pos[j] < d - l + j) ii = j;
+#pragma unroll
+            for (int j = 0; j < LM; j++) {
+                if (j == ii)
+                    pos[j]++;
+                else if (j > ii && ii >= 0 && j > 0)
+                    pos[j] = pos[j - 1] + 1;
+            }
+        }
+    }
+    if (lane == 0) {
+        if (my_tests) atomicAdd(&s_tot[0], (unsigned long long)my_tests);
+        if (my_sing) atomicAdd(&s_tot[1], (unsigned long long)my_sing);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (s_tot[0]) atomicAdd((unsigned long long *)&ctl->executed, s_tot[0]);
+        if (s_tot[1]) atomicAdd((unsigned long long *)&ctl->singular, s_tot[1]);
+    }
+}
+
 template <int L0, int L1>
-__device__ __forceinline__ void cs_multi_dispatch(int l, const CiParams &p, LevelCtl *ctl, int nitems, double T2u, CsWarp *s_w,
-                                                  const unsigned *s_binom, double *s_L)
+__device__ __forceinline__ void cs_multi_dispatch(int l, bool warp_mode, const CiParams &p, LevelCtl *ctl, int nitems, double T2u,
+                                                  CsWarp *s_w, const unsigned *s_binom, double *s_L)
 {
     if constexpr (L0 <= L1) {
-        if (l == L0)
-            cs_body<true, L0>(p, ctl, p.work_counter_small + L0, p.self_items, p.self_adj, p.item_cap, nitems, T2u, 0, 1, s_w,
-                              s_binom, s_L);
-        else
-            cs_multi_dispatch<L0 + 1, L1>(l, p, ctl, nitems, T2u, s_w, s_binom, s_L);
+        if (l == L0) {
+            if (warp_mode)
+                cs_warp_body<L0>(p, ctl, p.work_counter_small + L0, p.self_items, p.self_adj, p.item_cap, nitems, T2u, s_w,
+                                 s_binom);
+            else
+                cs_body<true, L0, true>(p, ctl, p.work_counter_small + L0, p.self_items, p.self_adj, p.item_cap, nitems, T2u, 0,
+                                        1, s_w, s_binom, s_L);
+        } else {
+            cs_multi_dispatch<L0 + 1, L1>(l, warp_mode, p, ctl, nitems, T2u, s_w, s_binom, s_L);
+        }
     }
 }
 
@@ -493,22 +705,31 @@ __global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2
             for (int k = l_first; k <= maxl; k++) base[k].done = 1;
         return;
     }
+    __shared__ unsigned long long s_acc[5];
+    if (threadIdx.x < 5) s_acc[threadIdx.x] = 0ull;
     cs_fill_binom(s_binom);
     __syncthreads();
     unsigned *bar = &base[l_first].ticket;  // zero at the start of a call; counts arrivals of all barriers of this launch
     unsigned epoch = 0;
-    const u64 lanes = (u64)gridDim.x * blockDim.x;
+    const u64 lanes = (u64)gridDim.x * blockDim.x, warps = lanes / 32;
+    const bool warp_ok = p.N == nullptr && p.warp_sets;  // uniform N only; CUSK_WARP_SETS=0 keeps a thread per set
     for (int l = l_first; l <= l_last; l++) {
         LevelCtl *ctl = base + l;
         if (lead) ctl->t_begin = cs_globaltimer();
         // every level but the call's first self-planned one (p.l) knows an upper bound of its set total: the level before
         // it summed C(d, l) over its own rows (degrees only fall), so the items are cut in the row phase itself
         const bool emit = l > p.l;
+        // a level short of sets (at most CS_WARP_SETS per warp of the launch, by the same estimate that cuts the items) takes
+        // the warp-per-set form, items of est / warps sets; otherwise a thread per set
+        u64 est = emit ? *(volatile u64 *)&base[l - 1].acc_mid : 0;
+        bool warp_mode = emit && warp_ok && est <= (u64)CS_WARP_SETS * warps;
         if (emit)
-            cs_self_rows<true>(p, l, ctl, s_binom, cs_self_chunk(*(volatile u64 *)&base[l - 1].acc_mid, lanes));
+            cs_self_rows<true>(p, l, ctl, s_binom, warp_mode ? (est + warps - 1) / warps + (est == 0) : cs_self_chunk(est, lanes),
+                               s_acc);
         else
-            cs_self_rows<false>(p, l, ctl, s_binom, 0);
+            cs_self_rows<false>(p, l, ctl, s_binom, 0, s_acc);
         cs_grid_barrier(bar, ++epoch * gridDim.x);
+        if (lead) ctl->t_rows = cs_globaltimer();
         const u64 sets = *(volatile u64 *)&ctl->acc_small;
         const bool stop = sets == 0 || *(volatile int *)&ctl->infeasible != 0;
         double T2u;
@@ -525,7 +746,9 @@ __global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2
             return;
         }
         if (!emit) {
-            cs_self_items(p, l, ctl, s_binom, cs_self_chunk(sets, lanes));
+            est = sets;
+            warp_mode = warp_ok && est <= (u64)CS_WARP_SETS * warps;
+            cs_self_items(p, l, ctl, s_binom, warp_mode ? (est + warps - 1) / warps : cs_self_chunk(est, lanes));
             cs_grid_barrier(bar, ++epoch * gridDim.x);
         }
         int nitems = *(volatile int *)&ctl->nitems_small;
@@ -535,7 +758,8 @@ __global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2
             ctl->done = 0;
             ctl->t_planned = cs_globaltimer();
         }
-        cs_multi_dispatch<L0, L1>(l, p, ctl, nitems, T2u, s_w, s_binom, s_L);
+        cs_multi_dispatch<L0, L1>(l, warp_mode, p, ctl, nitems, T2u, s_w, s_binom, s_L);
+        if (lead) ctl->t_body = cs_globaltimer();
         cs_grid_barrier(bar, ++epoch * gridDim.x);  // the level's removals are in memory
         if (lead) ctl->t_end = cs_globaltimer();
     }

@@ -3,10 +3,21 @@
 #include "corr.cuh"
 
 // ---------------------------------------------------------------------------------------------
-// Genotype counts per marker (exact integers).  One warp per marker; 16 samples per 32-bit word.
-// Replaces the counting pass of compute_bed_col_stats_no_impute (src/prep.cpp:28-50).
-// Bytes: m * ceil(n/4) read once (HBM bound).
+// Genotype counts per marker (exact integers).  One warp per marker.  Replaces the counting pass of
+// compute_bed_col_stats_no_impute (src/prep.cpp:28-50).  Bytes: m * ceil(n/4) read once (HBM bound).
+// Round 2: 16-byte loads (two in flight per lane) after a byte-wise head up to the column's first 16-byte boundary --
+// columns start at mk * ceil(n/4), any alignment -- and three popcounts per 32-bit word instead of four per byte:
+// with lo / hi the low / high bits of the 2-bit codes, #11 = popc(lo & hi), #01 = popc(lo) - #11, #10 = popc(hi) - #11,
+// #00 = samples - popc(lo | hi).  (The byte-per-lane first version ran at 0.8 TB/s, profiles/r2_corr_helpers_full_summary.txt.)
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bed_acc_word(uint32_t w, int &plo, int &phi, int &pand)
+{
+    const uint32_t lo = w & 0x55555555u, hi = (w >> 1) & 0x55555555u;
+    plo += __popc(lo);
+    phi += __popc(hi);
+    pand += __popc(lo & hi);
+}
+
 __global__ void __launch_bounds__(256) bed_counts_kernel(const unsigned char *__restrict__ bed, int m, int n,
                                                          size_t col_bytes, int *__restrict__ counts)
 {
@@ -14,24 +25,51 @@ __global__ void __launch_bounds__(256) bed_counts_kernel(const unsigned char *__
     const int mk = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (mk >= m) return;
     const unsigned char *col = bed + (size_t)mk * col_bytes;
-    int c0 = 0, c1 = 0, c2 = 0, cm = 0;
-    for (size_t b = lane; b < col_bytes; b += 32) {
-        const unsigned v = col[b];
-        const int ns = (int)min((size_t)4, (size_t)n - b * 4);  // samples in this byte
-        const unsigned valid = (1u << (2 * ns)) - 1u;
-        const unsigned lo = v & 0x55u, hi = (v >> 1) & 0x55u, smask = valid & 0x55u;
-        c2 += __popc(~lo & ~hi & smask);  // 00
-        cm += __popc(lo & ~hi & smask);   // 01
-        c1 += __popc(~lo & hi & smask);   // 10
-        c0 += __popc(lo & hi & smask);    // 11
+    const size_t full = (size_t)n / 4;  // bytes whose four samples all exist
+    int plo = 0, phi = 0, pand = 0;
+    size_t head = (size_t)((16u - (unsigned)((uintptr_t)col & 15u)) & 15u);
+    if (head > full) head = full;
+    if ((size_t)lane < head) bed_acc_word(col[lane], plo, phi, pand);
+    const uint4 *v = (const uint4 *)(col + head);
+    const size_t nvec = (full - head) / 16;
+    size_t i = lane;
+    for (; i + 32 < nvec; i += 64) {
+        const uint4 a = __ldg(v + i), b = __ldg(v + i + 32);
+        bed_acc_word(a.x, plo, phi, pand);
+        bed_acc_word(a.y, plo, phi, pand);
+        bed_acc_word(a.z, plo, phi, pand);
+        bed_acc_word(a.w, plo, phi, pand);
+        bed_acc_word(b.x, plo, phi, pand);
+        bed_acc_word(b.y, plo, phi, pand);
+        bed_acc_word(b.z, plo, phi, pand);
+        bed_acc_word(b.w, plo, phi, pand);
     }
+    if (i < nvec) {
+        const uint4 a = __ldg(v + i);
+        bed_acc_word(a.x, plo, phi, pand);
+        bed_acc_word(a.y, plo, phi, pand);
+        bed_acc_word(a.z, plo, phi, pand);
+        bed_acc_word(a.w, plo, phi, pand);
+    }
+    const size_t done = head + nvec * 16;
+    if (done + lane < full) bed_acc_word(col[done + lane], plo, phi, pand);  // fewer than 16 bytes left
     for (int o = 16; o > 0; o >>= 1) {
-        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
-        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
-        c2 += __shfl_xor_sync(0xffffffffu, c2, o);
-        cm += __shfl_xor_sync(0xffffffffu, cm, o);
+        plo += __shfl_xor_sync(0xffffffffu, plo, o);
+        phi += __shfl_xor_sync(0xffffffffu, phi, o);
+        pand += __shfl_xor_sync(0xffffffffu, pand, o);
     }
     if (lane == 0) {
+        int c0 = pand, cm = plo - pand, c1 = phi - pand, c2 = (int)(4 * full) - (plo + phi - pand);
+        const int ns = n - (int)(4 * full);  // samples in the last, partial byte
+        if (ns > 0) {
+            const unsigned v8 = col[full];
+            const unsigned valid = (1u << (2 * ns)) - 1u;
+            const unsigned lo = v8 & 0x55u, hi = (v8 >> 1) & 0x55u, smask = valid & 0x55u;
+            c2 += __popc(~lo & ~hi & smask);  // 00
+            cm += __popc(lo & ~hi & smask);   // 01
+            c1 += __popc(~lo & hi & smask);   // 10
+            c0 += __popc(lo & hi & smask);    // 11
+        }
         counts[4 * mk + 0] = c0;
         counts[4 * mk + 1] = c1;
         counts[4 * mk + 2] = c2;
@@ -80,9 +118,80 @@ __global__ void __launch_bounds__(128) bed_stats_kernel(const unsigned char *__r
     modes[mk] = mode;
 }
 
+// The same statistics with the columns staged through shared memory (round 2).  In the kernel above every thread walks
+// its own column byte by byte: 32 sectors per warp load, 40 GB/s at the C3 shape (28.9 ms for 1.15 GB,
+// profiles/r2_corr_helpers_full_summary.txt).  Here a warp owns 32 markers: it fetches 128 bytes of each column with one
+// coalesced load per column (32 independent loads in flight per lane, the next tile's while this one is summed), parks
+// them in a padded shared tile and every lane then replays its own column's samples IN ORDER from there -- the float
+// sum is the same sequence of additions (a missing call adds +0.0f to a sum that is never -0, which leaves it as it is),
+// so the result is bit-identical; what remains is the chain of dependent float additions itself (~5 cycles per sample).
+// Needs 4-byte aligned columns (ceil(n/4) % 4 == 0); other shapes take the kernel above.
+__global__ void __launch_bounds__(32) bed_stats_tiled_kernel(const unsigned char *__restrict__ bed, int m, int n,
+                                                            size_t col_bytes, const int *__restrict__ counts,
+                                                            float *__restrict__ means, float *__restrict__ stds,
+                                                            int *__restrict__ modes)
+{
+    __shared__ uint32_t s_t[32 * 33];
+    const int lane = threadIdx.x;
+    const int mk0 = blockIdx.x * 32, mk = mk0 + lane;
+    const int rows = min(32, m - mk0);
+    const size_t words = col_bytes / 4;
+    float mean = 0.f, denom = 1.f;
+    int c0 = 0, c1 = 0, c2 = 0;
+    if (mk < m) {
+        const int *c = counts + 4 * mk;
+        c0 = c[0], c1 = c[1], c2 = c[2];
+        const size_t gt_sum = (size_t)c1 + 2 * (size_t)c2;
+        denom = (float)((size_t)n - (size_t)c[3]);
+        mean = (float)gt_sum / denom;  // size_t / float: the sum converts to float first
+    }
+    const float sq_g0 = (0.0f - mean) * (0.0f - mean);  // code 11 -> 0
+    const float sq_g1 = (1.0f - mean) * (1.0f - mean);  // code 10 -> 1
+    const float sq_g2 = (2.0f - mean) * (2.0f - mean);  // code 00 -> 2 (code 01 = missing: adds +0)
+    const uint32_t *base = (const uint32_t *)(bed + (size_t)mk0 * col_bytes);
+    uint32_t nxt[32];
+#pragma unroll
+    for (int r = 0; r < 32; r++) nxt[r] = (r < rows && (size_t)lane < words) ? __ldg(base + (size_t)r * words + lane) : 0x55555555u;
+    float sum_squares = 0.0f;
+    for (size_t t0 = 0; t0 < words; t0 += 32) {
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < 32; r++) s_t[r * 33 + lane] = nxt[r];
+        __syncwarp();
+        const size_t t1 = t0 + 32 + lane;
+#pragma unroll
+        for (int r = 0; r < 32; r++) nxt[r] = (r < rows && t1 < words) ? __ldg(base + (size_t)r * words + t1) : 0x55555555u;
+        for (int j = 0; j < 32; j++) {
+            uint32_t w = s_t[lane * 33 + j];
+            const long long left = (long long)n - (long long)(t0 + j) * 16;  // samples of this word that exist
+            if (left < 16) {
+                const uint32_t keep = left <= 0 ? 0u : ((1u << (2 * (int)left)) - 1u);
+                w = (w & keep) | (0x55555555u & ~keep);  // what does not exist counts as missing
+            }
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                const bool b0 = (w >> (2 * k)) & 1u, b1 = (w >> (2 * k + 1)) & 1u;
+                const float add = b1 ? (b0 ? sq_g0 : sq_g1) : (b0 ? 0.0f : sq_g2);
+                sum_squares = __fadd_rn(sum_squares, add);
+            }
+        }
+    }
+    if (mk < m) {
+        means[mk] = mean;
+        stds[mk] = sqrtf(sum_squares / denom);
+        int mode = 0, best = c0;
+        if (c1 > best) mode = 1, best = c1;
+        if (c2 > best) mode = 2;
+        modes[mk] = mode;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // 2-bit BED -> uint8 indicator rows for the tensor-core Gram.  Thread = 4 packed bytes (16 samples)
 // of one marker -> one 16-byte store per part.  Bytes: m ceil(n/4) read, parts * m * Kp written.
+// Round 2: one 32-bit load per thread where the columns are 4-byte aligned, and the indicators of four samples at a time
+// by byte-parallel logic (the 2-bit codes of a packed byte spread to one byte each, then lo / hi bit planes): the
+// bit-at-a-time first version was issue-bound at 2.5 TB/s of its 10.3 GB (profiles/r2_corr_helpers_full_summary.txt).
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) decode_indicators_kernel(const unsigned char *__restrict__ bed, int m, int n,
                                                                 size_t col_bytes, int parts, int MI, size_t Kp,
@@ -93,21 +202,31 @@ __global__ void __launch_bounds__(256) decode_indicators_kernel(const unsigned c
     if (chunk * 16 >= Kp) return;
     const unsigned char *col = bed + (size_t)mk * col_bytes;
     unsigned v = 0;
+    if ((((uintptr_t)col) & 3u) == 0 && chunk * 4 + 4 <= col_bytes) {
+        v = __ldg((const uint32_t *)(col + chunk * 4));
+    } else {
 #pragma unroll
-    for (int b = 0; b < 4; b++) {
-        const size_t bi = chunk * 4 + b;
-        if (bi < col_bytes) v |= (unsigned)col[bi] << (8 * b);
-    }
-    uint32_t o1[4] = {0, 0, 0, 0}, o2[4] = {0, 0, 0, 0}, ov[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int j = 0; j < 16; j++) {
-        const size_t s = chunk * 16 + j;
-        const unsigned code = (v >> (2 * j)) & 3u;
-        if (s < (size_t)n) {
-            o1[j >> 2] |= (uint32_t)(code == 2u) << (8 * (j & 3));
-            o2[j >> 2] |= (uint32_t)(code == 0u) << (8 * (j & 3));
-            ov[j >> 2] |= (uint32_t)(code != 1u) << (8 * (j & 3));
+        for (int b = 0; b < 4; b++) {
+            const size_t bi = chunk * 4 + b;
+            if (bi < col_bytes) v |= (unsigned)col[bi] << (8 * b);
         }
+    }
+    uint32_t o1[4], o2[4], ov[4];
+    const long long left = (long long)n - (long long)chunk * 16;  // samples of this chunk that exist
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const unsigned byte = (v >> (8 * k)) & 0xffu;
+        const unsigned x = (byte | (byte << 6) | (byte << 12) | (byte << 18)) & 0x03030303u;  // one code per byte
+        const unsigned lo = x & 0x01010101u, hi = (x >> 1) & 0x01010101u;
+        uint32_t is2 = hi & (lo ^ 0x01010101u);          // code 10
+        uint32_t is0 = (hi | lo) ^ 0x01010101u;          // code 00
+        uint32_t ok = (lo & (hi ^ 0x01010101u)) ^ 0x01010101u;  // code != 01
+        if (left < 16) {
+            const long long e = left - 4 * k;  // samples of this byte that exist
+            const uint32_t keep = e >= 4 ? 0xffffffffu : (e <= 0 ? 0u : ((1u << (8 * (int)e)) - 1u));
+            is2 &= keep, is0 &= keep, ok &= keep;
+        }
+        o1[k] = is2, o2[k] = is0, ov[k] = ok;
     }
     const size_t off = chunk * 16;
     if (parts == 2) {
@@ -270,7 +389,10 @@ void launch_bed_counts(cudaStream_t st, const unsigned char *bed, int m, int n, 
 void launch_bed_stats(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, const int *counts,
                       float *means, float *stds, int *modes)
 {
-    bed_stats_kernel<<<(m + 127) / 128, 128, 0, st>>>(bed, m, n, col_bytes, counts, means, stds, modes);
+    if (col_bytes % 4 == 0 && ((uintptr_t)bed & 3u) == 0)
+        bed_stats_tiled_kernel<<<(m + 31) / 32, 32, 0, st>>>(bed, m, n, col_bytes, counts, means, stds, modes);
+    else
+        bed_stats_kernel<<<(m + 127) / 128, 128, 0, st>>>(bed, m, n, col_bytes, counts, means, stds, modes);
 }
 void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int parts, int MI,
                    size_t Kp, unsigned char *ind)

@@ -223,6 +223,10 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             p.item_cap = self_cap;
             p.deg_out = d_deg;
             p.n_uniform = n_uniform;
+            {
+                const char *e = getenv("CUSK_WARP_SETS");
+                p.warp_sets = !(e && atoi(e) == 0);
+            }
             int launched = 0;
             const int rc = launch_ci_small_multi(st, p, l, l_last, maxl, self_coop, &launched);
             nl += launched;
@@ -320,7 +324,7 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
         int rc = CUSK_OK;
         // level 2: the short rows' kernel and the medium rows' kernel side by side (each alone keeps a quarter to a third
         // of the warp slots busy, profiles/r2_ci_kernels_full_summary.txt); the medium rows go first, on the side stream
-        const bool side = side_env && l == CI_MID_LMAX && (classes & 2u) && (classes & 4u) && ctx->stream2;
+        const bool side = side_env && !sh && l == CI_MID_LMAX && (classes & 2u) && (classes & 4u) && ctx->stream2;
         if (side) {
             CUSK_CUDA(cudaEventRecord(ctx->ev_fork, st));
             CUSK_CUDA(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
@@ -394,6 +398,18 @@ int run_engine(cusk_ctx *ctx, const EngineArgs &a, EngineOut *out, cusk_stats *s
             float ms = 0.f;
             cudaEvent_t *xe = ev + 3 * (CUSK_ML + 2) + 4 + 2 * l;
             if (cudaEventElapsedTime(&ms, xe[0], xe[1]) == cudaSuccess) sh->exchange_ms += ms;
+        }
+    }
+    if (self_last >= self_first && getenv("CUSK_SELF_TRACE")) {
+        // phases of the levels inside the multi-level launches, microseconds (CTA 0's view): row phase + barrier, plan,
+        // CTA 0's tests, wait for the other CTAs; and the gap to the next level's start (launch boundaries show up here)
+        for (int l = self_first; l <= self_last && !h_ctl[l].done; l++) {
+            const LevelCtl &c = h_ctl[l];
+            const double gap = (l < self_last && !h_ctl[l + 1].done && h_ctl[l + 1].t_begin > c.t_end)
+                                   ? (double)(h_ctl[l + 1].t_begin - c.t_end) * 1e-3 : 0.0;
+            fprintf(stderr, "cusk self-trace: level %2d rows %6.2f plan %6.2f tests(cta0) %6.2f tail %6.2f | gap %6.2f | items %d\n", l,
+                    (double)(c.t_rows - c.t_begin) * 1e-3, (double)(c.t_planned - c.t_rows) * 1e-3,
+                    (double)(c.t_body - c.t_planned) * 1e-3, (double)(c.t_end - c.t_body) * 1e-3, gap, c.nitems_small);
         }
     }
     // last level as the reference reports it (src/cuPC-S.cu:99,154-159): the first level that

@@ -40,6 +40,7 @@ struct LevelCtl {
     int plan_ready;  // fused plan + compaction: set by the planning CTA once the level's plan is in memory
     int pad3;
     u64 t_begin, t_planned, t_end;  // levels inside a multi-level launch (ci_small.cu): %globaltimer at start / after the plan / at the end
+    u64 t_rows, t_body;             // ... after the row phase's barrier / when CTA 0 has run out of items (CUSK_SELF_TRACE=1 prints them)
 };
 
 // One work item of the CI kernel, decoded once per level by items_kernel (the CI kernel's CTAs then
@@ -79,6 +80,7 @@ struct CiParams {
     CiItem *self_items;    // [item_cap]
     int *deg_out;          // [n]
     float n_uniform;       // het engine, uniform N (threshold of the level)
+    int warp_sets;         // 1: levels short of conditioning sets run a warp per set (ci_small.cu, cs_warp_body)
 };
 
 #define CI_SELF_STRIDE 32    // = CI_SMALL_DMAX: every row of a self-planned level fits the thread-per-set kernel

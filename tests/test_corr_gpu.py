@@ -70,7 +70,10 @@ def test_with_nan_phen(ctx, golden):
 
 
 @pytest.mark.parametrize("n,m,p,miss,stream", [(1000, 70, 4, 0.0, 61), (777, 150, 5, 0.01, 62), (4100, 300, 3, 0.0, 63),
-                                                (130, 45, 2, 0.05, 64), (515, 129, 0, 0.0, 65)])
+                                                (130, 45, 2, 0.05, 64), (515, 129, 0, 0.0, 65),
+                                                # ceil(n / 4) % 4 == 0: 4-byte aligned columns (32-bit decode loads, the
+                                                # shared-memory staged statistics kernel), with and without a ragged tail
+                                                (4093, 97, 3, 0.01, 66), (1024, 64, 2, 0.0, 67)])
 def test_random_block_vs_oracle(ctx, oracle, n, m, p, miss, stream):
     from cigwas_b200 import synth
 
@@ -172,3 +175,23 @@ def test_corr_to_skeleton_device_pipeline(ctx, oracle):
     Co = np.triu(Co) + np.triu(Co, 1).T
     _close(Cg, Co)
     assert (Cg == Cg.T).all()
+
+
+@pytest.mark.parametrize("n,m,miss", [(61, 40, 0.1), (2048, 33, 0.0), (2049, 31, 0.02), (8177, 100, 0.3), (16, 1, 0.0),
+                                      (3, 5, 0.0), (6000, 257, 1.0)])
+def test_marker_stats_shapes(ctx, oracle, n, m, miss):
+    """prep-bed statistics on shapes that take each path of the round-2 kernels: 16-byte loads with a byte-wise head and
+    tail in the counting kernel (columns at any alignment), the staged statistics kernel (ceil(n/4) % 4 == 0; several
+    tiles, ragged last word, fewer than 32 markers in the last warp, all calls missing) and the byte-wise one (the rest):
+    counts, means, standard deviations (the reference's sequential float sum) and modes equal the oracle's bit for bit"""
+    from cigwas_b200 import synth
+
+    bed = synth.random_bed(n, m, stream=300 + n % 97, missing_rate=min(miss, 0.99))
+    if miss >= 1.0:
+        bed = np.full_like(bed, 0x55)  # every call missing: mean = 0 / 0
+    means, stds, modes, counts = ctx.bed_marker_stats(bed, m, n)
+    om, os_, omo, oc = oracle.bed_col_stats(bed, m, n)
+    assert (counts == oc).all()
+    assert ((means == om) | (np.isnan(means) & np.isnan(om))).all()
+    assert ((stds == os_) | (np.isnan(stds) & np.isnan(os_))).all()
+    assert (modes == omo).all()
