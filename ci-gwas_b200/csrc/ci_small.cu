@@ -30,7 +30,7 @@
 #define CS_NTHREADS(LT) (CS_NWARPS(LT) * 32)
 #define CS_STRIDE (CS_DMAX + 1)
 #define FULLMASK 0xffffffffu
-#define CS_WARP_SETS 4  // multi-level kernel: a level with at most this many sets per warp of the launch runs a warp per set
+#define CS_WARP_SETS 1  // multi-level kernel: a level with at most this many sets per warp of the launch runs a warp per set (measured: 21 against 37 us at one set per warp, a tie at two)
 static_assert(CI_SELF_DMAX < 32, "the warp-per-set form keeps X in lane d");
 
 struct CsWarp {
@@ -507,8 +507,9 @@ __device__ __forceinline__ void cs_self_items(const CiParams &p, int l, LevelCtl
 template <int LT>
 __device__ __forceinline__ void cs_warp_body(const CiParams &p, LevelCtl *ctl, int *work_counter, const CiItem *items,
                                              const int *adj, int item_cap, int nitems, double T2u, CsWarp *s_w,
-                                             const unsigned *s_binom)
+                                             const unsigned *s_binom, double *s_L)
 {
+    static_assert(LT > CS_LREG, "the warp-per-set form keeps its columns in the dynamic shared memory of the deep levels");
     constexpr int LM = LT;
     constexpr int NT = CS_NTHREADS(LT);
     constexpr int l = LT;
@@ -516,6 +517,12 @@ __device__ __forceinline__ void cs_warp_body(const CiParams &p, LevelCtl *ctl, i
     const int n = p.n;
     const bool use_time = p.time_index != nullptr;
     CsWarp &S = s_w[warp];
+    // per warp: W[LM][32] doubles, Dv[LM] doubles, P[LM] ints -- inside the launch's LT (LT - 1) / 2 doubles per thread
+    constexpr int WSTRIDE = 32 * CUSK_ML + CUSK_ML + (CUSK_ML + 1) / 2;
+    static_assert(WSTRIDE <= 32 * ((CS_LREG + 1) * CS_LREG / 2), "per-warp scratch must fit the shallowest deep level's share");
+    double *W = s_L + warp * WSTRIDE;
+    double *Dv = W + 32 * CUSK_ML;
+    int *P = (int *)(Dv + CUSK_ML);
     unsigned my_tests = 0, my_sing = 0;  // per warp (lane 0's copy is the warp's)
     __shared__ unsigned long long s_tot[2];
     if (tid == 0) s_tot[0] = s_tot[1] = 0ull;
@@ -596,38 +603,47 @@ __device__ __forceinline__ void cs_warp_body(const CiParams &p, LevelCtl *ctl, i
         const bool is_nb = lane < d, is_x = lane == d;
         const double cxy = is_nb ? (double)S.cx[lane] : 0.0;
         for (unsigned R = R0; R < R1; R++) {
-            double w[LM], invD[LM];
+            // The elimination as ROLLED loops over shared memory (W[j][c] = w_j[c], Dv[j] = 1 / D_j, P[j] = s_j): a set is
+            // run once per warp, so straight-line code unrolled over l (l + 1) / 2 steps would mostly wait for its own
+            // instruction fetches.
             int tS = -2147483647 - 1;
             unsigned inS = 0;
-            bool any_drop = false;
 #pragma unroll
             for (int j = 0; j < LM; j++) {
-                const int sj = pos[j];
+                if (lane == j) P[j] = pos[j];
+                inS |= 1u << pos[j];
+                if (use_time) tS = max(tS, S.time[pos[j]]);
+            }
+            __syncwarp();
+            bool any_drop = false;
+#pragma unroll 1
+            for (int j = 0; j < LM; j++) {
+                const int sj = P[j];
                 double acc = is_nb ? (double)S.csub[sj * CS_STRIDE + lane] : (is_x ? (double)S.cx[sj] : 0.0);
-#pragma unroll
+#pragma unroll 2
                 for (int i = 0; i < j; i++) {
-                    const double g = __shfl_sync(FULLMASK, w[i], sj);  // w_i[s_j]
-                    const double lji = g * invD[i];
-                    acc -= lji * w[i];
+                    const double g = W[i * 32 + sj];  // w_i[s_j]
+                    const double lji = g * Dv[i];
+                    acc -= lji * W[i * 32 + lane];
                 }
-                w[j] = acc;
-                const double D = __shfl_sync(FULLMASK, acc, sj);
+                W[j * 32 + lane] = acc;
+                __syncwarp();
+                const double D = W[j * 32 + sj];
                 const bool drop = fabs(D) < CI_PIVOT_TOL;
-                invD[j] = drop ? 0.0 : 1.0 / D;
+                if (lane == 0) Dv[j] = drop ? 0.0 : 1.0 / D;
                 if (drop && j < LM - 1) any_drop = true;
-                inS |= 1u << sj;
-                if (use_time) tS = max(tS, S.time[sj]);
+                __syncwarp();
             }
             if (any_drop) my_sing++;
             // X's column (lane d) gives t_x; every lane then has its own column's h01 / h11 against it
             double h00 = 1.0, h01 = cxy, h11 = 1.0;
-#pragma unroll
+#pragma unroll 1
             for (int j = 0; j < LM; j++) {
-                const double t = __shfl_sync(FULLMASK, w[j], d);
-                const double txd = t * invD[j];
+                const double t = W[j * 32 + d], inv = Dv[j], wj = W[j * 32 + lane];
+                const double txd = t * inv;
                 h00 -= t * txd;
-                h01 -= w[j] * txd;
-                h11 -= w[j] * w[j] * invD[j];
+                h01 -= wj * txd;
+                h11 -= wj * wj * inv;
             }
             const double c2 = fabs(h00);
             bool todo = is_nb && !((inS >> lane) & 1u) && !((*(volatile unsigned *)&S.skipmask >> lane) & 1u);
@@ -676,10 +692,15 @@ __device__ __forceinline__ void cs_multi_dispatch(int l, bool warp_mode, const C
 {
     if constexpr (L0 <= L1) {
         if (l == L0) {
-            if (warp_mode)
-                cs_warp_body<L0>(p, ctl, p.work_counter_small + L0, p.self_items, p.self_adj, p.item_cap, nitems, T2u, s_w,
-                                 s_binom);
-            else
+            bool done_here = false;
+            if constexpr (L0 > CS_LREG) {
+                if (warp_mode) {
+                    cs_warp_body<L0>(p, ctl, p.work_counter_small + L0, p.self_items, p.self_adj, p.item_cap, nitems, T2u, s_w,
+                                     s_binom, s_L);
+                    done_here = true;
+                }
+            }
+            if (!done_here)
                 cs_body<true, L0, true>(p, ctl, p.work_counter_small + L0, p.self_items, p.self_adj, p.item_cap, nitems, T2u, 0,
                                         1, s_w, s_binom, s_L);
         } else {
@@ -712,7 +733,8 @@ __global__ void __launch_bounds__(CS_NTHREADS(L0), (L1 <= 6 || L0 > CS_LREG) ? 2
     unsigned *bar = &base[l_first].ticket;  // zero at the start of a call; counts arrivals of all barriers of this launch
     unsigned epoch = 0;
     const u64 lanes = (u64)gridDim.x * blockDim.x, warps = lanes / 32;
-    const bool warp_ok = p.N == nullptr && p.warp_sets;  // uniform N only; CUSK_WARP_SETS=0 keeps a thread per set
+    // uniform N only, levels above CS_LREG (their launch has the dynamic shared memory); CUSK_WARP_SETS=0: a thread per set
+    const bool warp_ok = p.N == nullptr && p.warp_sets && L0 > CS_LREG;
     for (int l = l_first; l <= l_last; l++) {
         LevelCtl *ctl = base + l;
         if (lead) ctl->t_begin = cs_globaltimer();

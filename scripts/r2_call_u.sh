@@ -23,3 +23,4 @@ import json
 d=json.loads([l for l in open('gpurun_out/r2_u/corr.json') if l.startswith('{')][-1])
 print({k:d[k] for k in d if k in ('ms_per_block','bed_gbps','stages_ms')})
 PY
+timeout 200 python scripts/bench_prep.py > "$OUT/prep.json" 2> "$OUT/prep.err"; tail -n 1 "$OUT/prep.json"; tail -n 2 "$OUT/prep.err"
