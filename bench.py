@@ -719,7 +719,8 @@ def main():
                             "into the caller's int matrix by host threads"},
             "gpu_launches": launches_all,
             "roofline": {"bound": "hbm", "kernel": "level-l CI kernels of the step (ci_mid_kernel<HET,1|2>, "
-                         "ci_small_kernel<HET,l>, ci_dfs_kernel<MODE,l,NS>, ci_level_kernel<HET>)", "achieved": achieved,
+                         "ci_small_kernel<HET,l>, the test phases of ci_small_multi_kernel<L0,L1> (levels 4..14), "
+                         "ci_dfs_kernel<MODE,l,NS>, ci_level_kernel<HET>)", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                          "bound_measured": ncu_ci.get("bound_measured", "issue slots / FP64 latency (not HBM)"),

@@ -32,7 +32,9 @@ def main():
     ix = {n: i for i, n in enumerate(h)}
 
     def val(row, k):
-        x = float(row[ix[k]])
+        if k not in ix or row[ix[k]] == "":  # e.g. lts__t_bytes.sum is not in ncu's full set
+            return 0.0
+        x = float(row[ix[k]].replace(",", ""))
         return x * MULT.get(u[ix[k]], 1.0)
 
     if count <= 0:  # one step = up to the second launch of the first kernel seen (the capture may hold several steps)
