@@ -726,7 +726,8 @@ def main():
                          "bound_measured": ncu_ci.get("bound_measured", "issue slots / FP64 latency (not HBM)"),
                          "issue_slot": ncu_ci.get("issue_slot"), "l2": ncu_ci.get("l2"),
                          "note": "algorithmic bytes = sum_l tests_l * 4 (l+2), time = sum of the CI kernels' "
-                                 "durations (CUDA events on the engine's stream, taken in a repeat of the timed steps "
+                                 "durations (CUDA events on the engine's stream, %globaltimer stamps for the test phases inside the "
+                                 "multi-level launches; taken in a repeat of the timed steps "
                                  "with the engine's per-level event records switched on: the records cost ~0.2 ms per "
                                  "step and are off in the timed region).  The matrix (36 MB) is L2-resident, so "
                                  "DRAM traffic (ncu) is ~3 % of the algorithmic bytes and HBM is not what bounds these "
