@@ -27,6 +27,8 @@ void launch_bed_counts(cudaStream_t st, const unsigned char *bed, int m, int n, 
 // tensor-core route (corr_kernels.cu, corr_gram.cu)
 void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int parts, int MI,
                    size_t Kp, unsigned char *ind);
+cudaError_t clear_indicator_padding(cudaStream_t st, unsigned char *ind, size_t m, int parts, int MI, size_t Kp,
+                                    size_t rows_total);
 int launch_gram(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMap &map_b, const GramParams &p, int grid);
 int gram_make_maps(const unsigned char *ind, size_t rows, size_t Kp, CUtensorMap *map_a, CUtensorMap *map_b);
 cusk_ctx *cusk_default_ctx();
@@ -225,7 +227,7 @@ static int banded_chunk_device_tc(cusk_ctx *ctx, const unsigned char *d_bed, int
     for (int i = 0; i < Mc; i++) any_missing |= h_scratch[4 * (size_t)i + 3] != 0;
     const int parts = any_missing ? 3 : 2, MI = 128 / parts;
     const size_t rows = tc_ind_rows((size_t)Mc, (size_t)MI);
-    CUSK_CUDA(cudaMemsetAsync(d_ind, 0, rows * Kp, s));  // padding rows of every group and the tail of K must be zero
+    CUSK_CUDA(clear_indicator_padding(s, d_ind, (size_t)Mc, parts, MI, Kp, rows));  // only the rows no marker owns
     launch_decode(s, d_bed, Mc, (int)n, col_bytes, parts, MI, Kp, d_ind);
     const size_t ntiles = bandc_gram_tiles((size_t)Mc, (size_t)R, (size_t)W, (size_t)MI, h_scratch.data(), tiles_cap);
     if (ntiles > tiles_cap) {

@@ -409,6 +409,24 @@ void launch_bed_stats(cudaStream_t st, const unsigned char *bed, int m, int n, s
     else
         bed_stats_kernel<<<(m + 127) / 128, 128, 0, st>>>(bed, m, n, col_bytes, counts, means, stds, modes);
 }
+// The rows of the padded indicator matrix that no marker owns must be zero: the padding rows of every 128-row group
+// (parts = 3 uses 126), the unused part of the last group and every row from groups * 128 on (up to the multiple of 256,
+// plus whatever block the caller appended).  All other rows -- the tail of K included -- are written by
+// decode_indicators_kernel itself.
+cudaError_t clear_indicator_padding(cudaStream_t st, unsigned char *ind, size_t m, int parts, int MI, size_t Kp,
+                                    size_t rows_total)
+{
+    const size_t groups = (m + MI - 1) / MI, used = (size_t)MI * parts;
+    cudaError_t e = cudaSuccess;
+    if (groups && used < 128) e = cudaMemset2DAsync(ind + used * Kp, 128 * Kp, 0, (128 - used) * Kp, groups, st);
+    const size_t last_markers = groups ? m - (groups - 1) * (size_t)MI : (size_t)MI;
+    if (e == cudaSuccess && last_markers < (size_t)MI)
+        e = cudaMemsetAsync(ind + ((groups - 1) * 128 + last_markers * parts) * Kp, 0, (used - last_markers * parts) * Kp, st);
+    if (e == cudaSuccess && rows_total > groups * 128)
+        e = cudaMemsetAsync(ind + groups * 128 * Kp, 0, (rows_total - groups * 128) * Kp, st);
+    return e;
+}
+
 void launch_decode(cudaStream_t st, const unsigned char *bed, int m, int n, size_t col_bytes, int parts, int MI,
                    size_t Kp, unsigned char *ind)
 {
