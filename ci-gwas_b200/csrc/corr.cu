@@ -24,6 +24,7 @@ void launch_pack_upper(cudaStream_t st, const float *Csq, int m, int ldc, float 
 void launch_set_diag(cudaStream_t st, float *Csq, int nvar, int ldc);
 // corr_gram.cu
 int launch_gram(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMap &map_b, const GramParams &p, int grid);
+int launch_gram_pair(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMap &map_b, const GramParams &p, int grid);
 int gram_make_maps(const unsigned char *ind, size_t rows, size_t Kp, CUtensorMap *map_a, CUtensorMap *map_b);
 cusk_ctx *cusk_default_ctx();
 
@@ -209,8 +210,34 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         const bool ksync_on = KSYNC > 0 && mxm_tiles && (size_t)n_tm * (size_t)n_tn > (size_t)2 * grid_full;
         const int SB_M = SB_M_ENV ? SB_M_ENV : (ksync_on ? 16 : 1 << 20);
         const int SB_N = SB_N_ENV ? SB_N_ENV : (ksync_on ? 9 : 1);
+        // CTA pairs (cta_group::2, CUSK_GRAM_PAIR=0 for one CTA per tile): a pair of CTAs takes the two A groups 2 tm2,
+        // 2 tm2 + 1 against one B block -- a 256 x 256 tile whose B rows each CTA loads only half of -- so a CTA fills
+        // 32 KB of shared memory per k-step instead of 48 KB for the same 128 x 256 outputs.  The list carries the
+        // pair's two entries next to each other; the grid is even, so entries 2c, 2c + 1 go to CTAs 2c, 2c + 1 = one
+        // cluster.  Used with the K-panel meeting (large blocks); small blocks keep the one-CTA form.
+        const char *pair_e = getenv("CUSK_GRAM_PAIR");  // read on every call: the tests compare the two forms
+        const bool pair_on = !(pair_e && atoi(pair_e) == 0) && ksync_on && (grid_full % 2 == 0);
         std::vector<int> wave_tiles;
-        if (!ksync_on) {
+        if (pair_on) {
+            tiles.clear();
+            const int n_tm2 = (n_tm + 1) / 2;
+            if (tc_traits)
+                for (int tm2 = 0; tm2 < n_tm2; tm2++) {
+                    tiles.push_back({2 * tm2, trait_tn});
+                    tiles.push_back({2 * tm2 + 1, trait_tn});
+                }
+            const int SB_M2 = std::max(1, SB_M / 2);
+            for (int sn = ((n_tn - 1) / SB_N) * SB_N; sn >= 0; sn -= SB_N)
+                for (int sm = 0; sm < n_tm2; sm += SB_M2)
+                    for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
+                        for (int tm2 = sm; tm2 < std::min(sm + SB_M2, n_tm2); tm2++)
+                            if ((size_t)(2 * tn + 2) * MI > (size_t)(2 * tm2) * MI + 1 && (size_t)(2 * tm2) * MI < m) {
+                                tiles.push_back({2 * tm2, tn});
+                                tiles.push_back({2 * tm2 + 1, tn});
+                            }
+            for (size_t w = 0; w * (size_t)grid_full < tiles.size(); w++)
+                wave_tiles.push_back((int)std::min<size_t>((size_t)grid_full, tiles.size() - w * (size_t)grid_full));
+        } else if (!ksync_on) {
             for (int sn = ((n_tn - 1) / SB_N) * SB_N; mxm_tiles && sn >= 0; sn -= SB_N)  // long rows of the triangle first
                 for (int sm = 0; sm < n_tm; sm += SB_M)
                     for (int tn = sn; tn < std::min(sn + SB_N, n_tn); tn++)
@@ -277,7 +304,7 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
             gp.l0_th = l0->th;
         }
         t_gram.start();
-        rc = launch_gram(s, map_a, map_b, gp, launch_grid);
+        rc = pair_on ? launch_gram_pair(s, map_a, map_b, gp, launch_grid) : launch_gram(s, map_a, map_b, gp, launch_grid);
         if (rc) return rc;
         t_gram.stop();
         CUSK_CUDA(cudaGetLastError());

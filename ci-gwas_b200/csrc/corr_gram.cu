@@ -23,14 +23,21 @@ namespace {
 
 constexpr int BK = 128;                 // bytes of K per stage (= one 128 B swizzle span)
 constexpr int TILE_M = 128, TILE_N = 256;
-constexpr int STAGES = 4;
-constexpr int A_BYTES = TILE_M * BK, B_BYTES = TILE_N * BK;
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int A_BYTES = TILE_M * BK;
 constexpr int EPI_MARKERS = 16;         // markers (column side) staged per epilogue chunk
 constexpr int EPI_STRIDE = 16 * 3 + 1;  // ints per staged row (worst case parts = 3), padded
 constexpr int EPI_BYTES = TILE_M * EPI_STRIDE * 4;
 constexpr int GRAM_THREADS = 256;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+// One CTA per tile (PAIR = false): a stage holds the tile's 128 A rows and 256 B rows, 4 stages.  CTA pair
+// (PAIR = true, cta_group::2): a stage holds this CTA's 128 A rows and ITS HALF of the 256 B rows, 6 stages.
+template <bool PAIR>
+struct GramGeom {
+    static constexpr int STAGES = PAIR ? 6 : 4;
+    static constexpr int B_BYTES = (PAIR ? TILE_N / 2 : TILE_N) * BK;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;  // shared::cluster address of the same location in the pair's even CTA
 
 // ---- PTX helpers -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -70,12 +77,57 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, u
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+// CTA-pair forms: the load lands in THIS CTA's shared memory and completes on the even CTA's barrier
+__device__ __forceinline__ void tma_load_2d_pair(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar) & PEER_MASK), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_even_cta(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & PEER_MASK) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t *bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
+}
+// the same arrival on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void tc_commit_pair(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"((uint16_t)3)
+                 : "memory");
+}
+// D[tmem of both CTAs] (+)= A[128 rows in each CTA] * B[128 rows in each CTA]^T: M = 256, N = 256 over the pair
+__device__ __forceinline__ void mma_i8_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 // D[tmem] (+)= A[smem] * B[smem]^T, uint8 x uint8 -> int32
 __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
@@ -116,10 +168,16 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // ---------------------------------------------------------------------------------------------
 // The kernel
 // ---------------------------------------------------------------------------------------------
+template <bool PAIR>
 __global__ void __launch_bounds__(GRAM_THREADS, 1)
 gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const GramParams p)
 {
+    constexpr int STAGES = GramGeom<PAIR>::STAGES, STAGE_BYTES = GramGeom<PAIR>::STAGE_BYTES;
+    // CTA pair: the even CTA of the cluster issues the MMAs for both and owns the barriers the producers / the
+    // accumulator hand-back complete on; tile entries 2c, 2c + 1 of the list are the pair's two A groups of one B block
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
     extern __shared__ unsigned char smem_raw[];
     // SWIZZLE_128B operand tiles need 1024 B alignment
     unsigned char *smem = (unsigned char *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -145,24 +203,32 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
         for (int i = 0; i < 2; i++) {
             mbar_init(&tfull[i], 1);
-            mbar_init(&tempty[i], 4);  // one arrival per epilogue warp
+            mbar_init(&tempty[i], PAIR ? 8 : 4);  // one arrival per epilogue warp (of both CTAs)
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "n"(512)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if constexpr (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "n"(512)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "n"(512)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (PAIR) cluster_sync_all();  // both CTAs' barriers exist before a load or an arrival crosses over
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    // instruction descriptor: D = S32, A/B = unsigned 8 bit, both K-major, N = 256, M = 128
+    // instruction descriptor: D = S32, A/B = unsigned 8 bit, both K-major, N = 256, M = 128 (256 over a CTA pair)
     const uint32_t idesc = (2u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(TILE_N >> 3) << 17) |
-                           ((uint32_t)(TILE_M >> 4) << 24);
+                           ((uint32_t)((PAIR ? 2 * TILE_M : TILE_M) >> 4) << 24);
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -184,9 +250,18 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     }
                     mbar_wait(&empty[stage], phase ^ 1);
                     unsigned char *sa = stage_base + stage * STAGE_BYTES;
-                    mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
-                    tma_load_2d(sa, &map_a, &full[stage], kb * BK, tile.x * TILE_M);
-                    tma_load_2d(sa + A_BYTES, &map_b, &full[stage], kb * BK, tile.y * TILE_N);
+                    if constexpr (PAIR) {
+                        // both CTAs load (their A group, their half of the B block: the 128-row box of map_a serves
+                        // both); the bytes of all four loads complete on the even CTA's barrier
+                        if (leader) mbar_arrive_expect_tx(&full[stage], 2 * STAGE_BYTES);
+                        tma_load_2d_pair(sa, &map_a, &full[stage], kb * BK, tile.x * TILE_M);
+                        tma_load_2d_pair(sa + A_BYTES, &map_a, &full[stage], kb * BK,
+                                         tile.y * TILE_N + (int)rank * (TILE_N / 2));
+                    } else {
+                        mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
+                        tma_load_2d(sa, &map_a, &full[stage], kb * BK, tile.x * TILE_M);
+                        tma_load_2d(sa + A_BYTES, &map_b, &full[stage], kb * BK, tile.y * TILE_N);
+                    }
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -196,7 +271,7 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
-        if (lane == 0) {
+        if (lane == 0 && leader) {
             int stage = 0;
             uint32_t phase = 0;
             int as = 0;
@@ -214,16 +289,21 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
                     for (int k4 = 0; k4 < BK / 32; k4++) {
                         // advance 32 bytes of K inside the 128 B swizzle span: +2 in 16 B units
-                        mma_i8(tmem_d, da + (uint64_t)(k4 * 2), db + (uint64_t)(k4 * 2), idesc,
-                               (uint32_t)((kb | k4) != 0));
+                        if constexpr (PAIR)
+                            mma_i8_pair(tmem_d, da + (uint64_t)(k4 * 2), db + (uint64_t)(k4 * 2), idesc,
+                                        (uint32_t)((kb | k4) != 0));
+                        else
+                            mma_i8(tmem_d, da + (uint64_t)(k4 * 2), db + (uint64_t)(k4 * 2), idesc,
+                                   (uint32_t)((kb | k4) != 0));
                     }
-                    tc_commit(&empty[stage]);  // frees the slot when these MMAs have read it
+                    // frees the slot (in both CTAs of a pair) when these MMAs have read it
+                    if constexpr (PAIR) tc_commit_pair(&empty[stage]); else tc_commit(&empty[stage]);
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                tc_commit(&tfull[as]);  // accumulator complete
+                if constexpr (PAIR) tc_commit_pair(&tfull[as]); else tc_commit(&tfull[as]);  // accumulator complete
                 if (++as == 2) {
                     as = 0;
                     aphase ^= 1;
@@ -370,7 +450,9 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[as]);
+            if (lane == 0) {
+                if constexpr (PAIR) mbar_arrive_even_cta(&tempty[as]); else mbar_arrive(&tempty[as]);
+            }
             if (++as == 2) {
                 as = 0;
                 aphase ^= 1;
@@ -380,8 +462,12 @@ gram_i8_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // ---- teardown ------------------------------------------------------------------------------
     tc_fence_before();
     __syncthreads();
+    if constexpr (PAIR) cluster_sync_all();  // the peer may still read its accumulator / receive an arrival
     if (warp == 2) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+        if constexpr (PAIR)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
     }
 }
 
@@ -435,11 +521,47 @@ int gram_make_maps(const unsigned char *ind, size_t rows, size_t Kp, CUtensorMap
 int launch_gram(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMap &map_b, const GramParams &p, int grid)
 {
     if (grid < 1) return CUSK_OK;
-    cudaError_t e = cudaFuncSetAttribute(gram_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    constexpr int SMEM = GramGeom<false>::SMEM_BYTES;
+    cudaError_t e = cudaFuncSetAttribute(gram_i8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) {
-        cusk_set_error("cudaFuncSetAttribute(gram_i8_kernel, %d B): %s", SMEM_BYTES, cudaGetErrorString(e));
+        cusk_set_error("cudaFuncSetAttribute(gram_i8_kernel, %d B): %s", SMEM, cudaGetErrorString(e));
         return CUSK_E_CUDA;
     }
-    gram_i8_kernel<<<grid, GRAM_THREADS, SMEM_BYTES, st>>>(map_a, map_b, p);
+    gram_i8_kernel<false><<<grid, GRAM_THREADS, SMEM, st>>>(map_a, map_b, p);
+    return CUSK_OK;
+}
+
+// CTA-pair form: clusters of two CTAs (one TPC), `grid` even; tile entries 2c, 2c + 1 are the A groups 2 tm2, 2 tm2 + 1 of
+// one B block (see the kernel).  map_b is unused: both operands come in 128-row boxes.
+int launch_gram_pair(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMap &map_b, const GramParams &p, int grid)
+{
+    if (grid < 2) return CUSK_OK;
+    if (grid & 1) {
+        cusk_set_error("launch_gram_pair: odd grid %d", grid);
+        return CUSK_E_ARG;
+    }
+    constexpr int SMEM = GramGeom<true>::SMEM_BYTES;
+    cudaError_t e = cudaFuncSetAttribute(gram_i8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) {
+        cusk_set_error("cudaFuncSetAttribute(gram_i8_kernel<pair>, %d B): %s", SMEM, cudaGetErrorString(e));
+        return CUSK_E_CUDA;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(GRAM_THREADS);
+    cfg.dynamicSmemBytes = SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, gram_i8_kernel<true>, map_a, map_b, p);
+    if (e != cudaSuccess) {
+        cusk_set_error("launch of gram_i8_kernel<pair>: %s", cudaGetErrorString(e));
+        return CUSK_E_CUDA;
+    }
     return CUSK_OK;
 }

@@ -195,3 +195,38 @@ def test_marker_stats_shapes(ctx, oracle, n, m, miss):
     assert ((means == om) | (np.isnan(means) & np.isnan(om))).all()
     assert ((stds == os_) | (np.isnan(stds) & np.isnan(os_))).all()
     assert (modes == omo).all()
+
+
+@pytest.mark.parametrize("n,m,miss,stream", [(4100, 1700, 0.0, 71), (2100, 1100, 0.004, 72)])
+def test_gram_cta_pair_form_equals_one_cta_form(ctx, oracle, n, m, miss, stream):
+    """blocks large enough for the K-panel meeting run the Gram kernel on CTA pairs (tcgen05.mma.cta_group::2, each CTA
+    holding its A group and half of the B block; an odd number of 128-row groups, so the last pair's second CTA works on
+    zero rows): every contingency table and every correlation equals the one-CTA-per-tile form's, and sampled tables
+    the oracle's"""
+    import os
+
+    from cigwas_b200 import synth
+
+    bed = synth.random_bed(n, m, stream=stream, missing_rate=miss)
+    means, stds, modes, counts = ctx.bed_marker_stats(bed, m, n)
+    ph = synth.rng_for(stream + 500).standard_normal((3, n)).astype(np.float32)
+    saved = os.environ.get("CUSK_GRAM_PAIR")
+    try:
+        os.environ["CUSK_GRAM_PAIR"] = "0"
+        r0 = ctx.corr_block(bed, ph, m, n, 3, means, stds, want_tables=True)
+        os.environ["CUSK_GRAM_PAIR"] = "1"
+        r1 = ctx.corr_block(bed, ph, m, n, 3, means, stds, want_tables=True)
+    finally:
+        if saved is None:
+            os.environ.pop("CUSK_GRAM_PAIR", None)
+        else:
+            os.environ["CUSK_GRAM_PAIR"] = saved
+    assert r1["stats"]["parts"] == (3 if miss > 0 else 2)
+    assert (r1["tables"] == r0["tables"]).all()
+    assert np.array_equal(r1["mxm"], r0["mxm"], equal_nan=True)
+    assert np.array_equal(r1["mxp"], r0["mxp"], equal_nan=True)
+    rs = np.random.default_rng(stream)
+    for _ in range(200):
+        a, b = sorted(rs.choice(m, size=2, replace=False).tolist())
+        lin = a * (2 * m - a - 1) // 2 + (b - a - 1)
+        assert (r1["tables"][lin] == oracle.pair_table(bed, n, a, b)).all(), (a, b)
