@@ -305,6 +305,8 @@ int corr_block_device(cusk_ctx *ctx, const unsigned char *d_bed, const float *d_
         }
         t_gram.start();
         rc = pair_on ? launch_gram_pair(s, map_a, map_b, gp, launch_grid) : launch_gram(s, map_a, map_b, gp, launch_grid);
+        // a device that cannot hold the grid's clusters at once: the pair list is also a valid list of 128 x 256 tiles
+        if (rc == CUSK_E_UNSUPPORTED_PAIR) rc = launch_gram(s, map_a, map_b, gp, launch_grid);
         if (rc) return rc;
         t_gram.stop();
         CUSK_CUDA(cudaGetLastError());

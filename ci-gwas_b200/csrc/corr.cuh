@@ -6,6 +6,8 @@
 // PLINK BED 2-bit codes (include/mps/bed_lut_gpu.h:3,1030): 00 -> genotype 2, 01 -> missing,
 // 10 -> genotype 1, 11 -> genotype 0; sample j of a marker sits in bits 2(j&3).. of byte j>>2.
 
+#define CUSK_E_UNSUPPORTED_PAIR (-1000)  // internal: launch_gram_pair cannot place the grid; the caller takes the one-CTA form
+
 struct GramParams {
     int parts;        // indicator rows per marker: 2 (no missing call in the block) or 3
     int MI;           // markers per 128-row group: 64 (parts 2) or 42 (parts 3)

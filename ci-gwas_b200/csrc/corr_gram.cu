@@ -13,6 +13,7 @@
 //            K=32 per instruction), accumulators in TMEM (2 x 256 columns, double buffered),
 //            tcgen05.commit releases ring slots / publishes the accumulator
 //   warp 2   TMEM allocation
+//   (CTA-pair form, gram_i8_kernel<true>: two CTAs of a cluster on a 256 x 256 tile, cta_group::2 -- see the kernel)
 //   warps 4-7 epilogue: tcgen05.ld the accumulator, stage 16 markers' columns through shared
 //            memory, contingency table -> tau_b -> sin, write both triangles of the dense matrix
 #include <cuda.h>
@@ -558,6 +559,12 @@ int launch_gram_pair(cudaStream_t st, const CUtensorMap &map_a, const CUtensorMa
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
+    // the wave's producers meet at counters (K-panel meeting): every cluster of the grid must be resident at once
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, gram_i8_kernel<true>, &cfg) != cudaSuccess || clusters * 2 < grid) {
+        cudaGetLastError();
+        return CUSK_E_UNSUPPORTED_PAIR;
+    }
     e = cudaLaunchKernelEx(&cfg, gram_i8_kernel<true>, map_a, map_b, p);
     if (e != cudaSuccess) {
         cusk_set_error("launch of gram_i8_kernel<pair>: %s", cudaGetErrorString(e));
