@@ -1,8 +1,8 @@
 #!/bin/bash
-# GPU call W (1 GPU): final state of the round: full GPU suite, smoke, the bench as the driver runs it, the reference arm,
+# GPU call W (second run, final) (1 GPU): final state of the round: full GPU suite, smoke, the bench as the driver runs it, the reference arm,
 # launch list and ncu --set full of the level loop's kernels.
 set -u
-OUT=gpurun_out/r2_w
+OUT=gpurun_out/r2_w2
 mkdir -p "$OUT"
 export PYTHONUNBUFFERED=1
 timeout 1800 python -m pytest tests -m gpu -q -x > "$OUT/tests_gpu.log" 2>&1
@@ -16,11 +16,11 @@ timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > "$OUT/bench_
 echo "reference arm: exit $?" | tee -a "$OUT/summary.txt"
 python - <<'PY' | tee -a "$OUT/summary.txt"
 import json
-d=json.loads([l for l in open('gpurun_out/r2_w/bench_full_default.json') if l.startswith('{')][-1])
+d=json.loads([l for l in open('gpurun_out/r2_w2/bench_full_default.json') if l.startswith('{')][-1])
 print('ms', round(d['ms_per_step'],4), 'value', d['value'], 'e2e', round(d['e2e']['ms_per_step'],3), 'launches', d['gpu_launches'], 'roofline', round(d['roofline']['frac'],3), d['config']['level_ms'])
 for k in ('het_n','workload_dense','corr','merged','ref_gpu','e2e_pipelined','cpu_baseline'):
     print(k, json.dumps(d.get(k))[:300])
-r=json.loads([l for l in open('gpurun_out/r2_w/bench_reference.json') if l.startswith('{')][-1])
+r=json.loads([l for l in open('gpurun_out/r2_w2/bench_reference.json') if l.startswith('{')][-1])
 print('reference', r.get('value'), r.get('ms_per_step'))
 PY
 timeout 300 python bench.py --steps 1 --warmup 1 --no-extras --no-pipelined-probe --no-cpu-baseline --no-ref-gpu > /dev/null 2>&1 && \
