@@ -339,3 +339,53 @@ def test_cuskss_all_scheduler(tmp_path, oracle):
         for key in ("ixs", "adj", "corr"):
             assert (a[key] == b[key]).all()
         assert a["mdim"] == b["mdim"]
+
+
+def test_cusk_one_marker_block_after_a_larger_one(tmp_path, oracle):
+    """on the tensor-core mxp route a ONE-marker block has no Gram tile at all, and its marker x trait values
+    must still reach the square matrix (they used to be scattered only inside the Gram branch, so the skeleton read what
+    the previous block had left in the arena).  One scheduler slot, larger block first, then the one-marker block whose
+    marker carries the strongest trait signal: both equal the oracle-driven restatement."""
+    n, ms, p = 3000, [60], 3
+    d, stem, beds = _make_cusk_inputs(tmp_path, n, ms, p, stream=431)
+    run_mps(["prep", stem])
+    b = beds[0]
+    codes = np.stack([(b >> (2 * j)) & 3 for j in range(4)], axis=-1).reshape(b.shape[0], -1)[:, :n]
+    G = np.where(codes == 0, 2.0, np.where(codes == 2, 1.0, 0.0))
+    rows = [ln.split()[2:] for ln in open(os.path.join(d, "traits.phen")).read().split("\n")[1:] if ln.split()]
+    y = np.array([[np.nan if v == "NA" else float(v) for v in r] for r in rows]).T
+    ok = ~np.isnan(y).any(axis=0)
+    r_abs = np.abs(np.corrcoef(np.vstack([G[:, ok], y[:, ok]]))[:60, 60:]).max(axis=1)
+    k = int(np.argmax(r_abs))  # the marker with the strongest trait signal
+    a0, a1 = (0, k - 1) if k >= 20 else (k + 1, 59)  # the larger block: everything on one side of it
+    open(os.path.join(d, "b.blocks"), "w").write(f"1\t{a0}\t{a1}\n1\t{k}\t{k}\n")
+    out = os.path.join(d, "out")
+    os.makedirs(out)
+    alpha, L1, L2, depth = 1e-4, 3, 2, 1
+    r = run_mps(["cusk-all", os.path.join(d, "traits.phen"), stem, os.path.join(d, "b.blocks"), alpha, L1, L2, depth, out],
+                env={"CUSK_SLOTS_PER_GPU": "1", "CUSK_DEVICES": "0"})
+    assert '"failed": 0' in r.stdout
+    exp = _expected_cusk_block(oracle, stem, beds, n, p, 0, k, k, alpha, L1, L2, depth)
+    assert exp is not None, "the chosen marker must pass the marker x trait screen"
+    _check_cusk_outputs(host_ref.read_outputs(os.path.join(out, f"1_{k}_{k}")), exp)
+    exp0 = _expected_cusk_block(oracle, stem, beds, n, p, 0, a0, a1, alpha, L1, L2, depth)
+    if exp0 is not None:
+        _check_cusk_outputs(host_ref.read_outputs(os.path.join(out, f"1_{a0}_{a1}")), exp0)
+
+
+def test_cusk_truncated_bed_fails(tmp_path):
+    """a .bed cut short must end the run with an error -- code 00 is a valid genotype, so a zero-filled tail
+    would give plausible wrong correlations"""
+    n, ms, p = 1000, [40], 2
+    d, stem, beds = _make_cusk_inputs(tmp_path, n, ms, p, stream=441)
+    run_mps(["prep", stem])
+    open(os.path.join(d, "b.blocks"), "w").write("1\t0\t39\n")
+    size = os.path.getsize(stem + ".bed")
+    with open(stem + ".bed", "r+b") as f:
+        f.truncate(size - 5 * ((n + 3) // 4))  # the last five markers are gone
+    out = os.path.join(d, "out")
+    os.makedirs(out)
+    r = run_mps(["cusk", os.path.join(d, "traits.phen"), stem, os.path.join(d, "b.blocks"), 1e-4, 3, 2, 1, out, 0],
+                check=False)
+    assert r.returncode != 0
+    assert not os.path.exists(os.path.join(out, "1_0_39.mdim"))
