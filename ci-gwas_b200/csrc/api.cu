@@ -301,6 +301,81 @@ int fetch_adjacency(cusk_ctx *ctx, const uint32_t *dbits, int n, int rw, int *G,
     return CUSK_OK;
 }
 
+// One helper thread per context for host work that runs BESIDE the engine (the calling thread drives the level loop and
+// its read-backs).  The helper owns the OpenMP team of the host scans -- a team belongs to the thread that opens the
+// parallel region -- so in the speculative flow below every parallel host job of a call goes through it.
+class HostHelper
+{
+public:
+    HostHelper() : th_([this] { loop(); }) {}
+    ~HostHelper()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        th_.join();
+    }
+    void submit(std::function<void()> f)
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            job_ = std::move(f);
+            busy_ = true;
+        }
+        cv_.notify_all();
+    }
+    void wait()
+    {
+        std::unique_lock<std::mutex> lk(mu_);
+        done_cv_.wait(lk, [&] { return !busy_; });
+    }
+
+private:
+    void loop()
+    {
+        for (;;) {
+            std::function<void()> f;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || (busy_ && job_); });
+                if (stop_) return;
+                f = std::move(job_);
+                job_ = nullptr;
+            }
+            f();
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                busy_ = false;
+            }
+            done_cv_.notify_all();
+        }
+    }
+    std::mutex mu_;
+    std::condition_variable cv_, done_cv_;
+    std::function<void()> job_;
+    bool busy_ = false, stop_ = false;
+    std::thread th_;  // last: started when everything above exists
+};
+
+HostHelper *host_helper(cusk_ctx *ctx)
+{
+    if (!ctx->host_helper) ctx->host_helper = std::shared_ptr<void>(new HostHelper, [](void *p) { delete (HostHelper *)p; });
+    return (HostHelper *)ctx->host_helper.get();
+}
+
+// Speculation of the host-buffer het call (below): worth starting only when a glance says the inputs are the usual ones --
+// the first entries of G are ones, the first row of N is one non-negative constant
+bool glance_trivial(const int *G, bool G_known_ones, const float *N, int n, size_t nn)
+{
+    if (n < 2 || !(N[1] >= 0.f)) return false;
+    uint32_t ref;
+    memcpy(&ref, &N[1], 4);
+    if (xor_or_u32((const uint32_t *)N + 1, (size_t)n - 1, ref)) return false;
+    return G_known_ones || !xor_or_u32((const uint32_t *)G, std::min<size_t>(nn, 4096), 1u);
+}
+
 }  // namespace
 
 extern "C" int cusk_skeleton(cusk_ctx *ctx, const float *C, int n, int *G, const float *Th, int maxlevel,
@@ -396,6 +471,93 @@ extern "C" int cusk_hetcor_skeleton(cusk_ctx *ctx, const float *C, int n, int *G
     bool zeroed = false;
     cusk_stats local;
     cusk_stats *sp = stats ? stats : &local;
+    // Speculation (CUSK_SPECULATE=0: off).  The scans of G and N (72 MB of host memory at the C2 shape) take longer than
+    // the upload of C they hide behind, and the engine cannot start before it knows their outcome -- unless it assumes the
+    // usual one (G all ones, N one constant: what `mps cuskss` passes without standard-error files) and starts at once.
+    // The helper thread scans beside the level loop and, when the assumption holds, zero-fills the caller's G; when it
+    // does not (a glance at the first entries filters the obvious cases out beforehand) the call runs again the slow way.
+    static const bool speculate_env = [] { const char *e = getenv("CUSK_SPECULATE"); return !(e && atoi(e) == 0); }();
+    if (scan && speculate_env && glance_trivial(G, G_in_all_ones != 0, N, n, nn)) {
+        CUSK_CUDA(cudaMemcpyAsync(dC, C, nn * 4, cudaMemcpyHostToDevice, st));
+        if (use_time) {
+            CUSK_CUDA(cudaMemcpyAsync(dT, time_index, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)n * 4;
+        }
+        th2d.stop();
+        const float cand = N[1];
+        bool all_ones = false, uniform = false, held = false;
+        float nu = 0.f;
+        HostHelper *hh = host_helper(ctx);
+        hh->submit([&] {
+            all_ones = G_in_all_ones || host_all_ones(G, nn);
+            uniform = host_constant_offdiag(N, n, &nu);
+            held = all_ones && uniform && memcmp(&nu, &cand, 4) == 0;
+            if (held) {  // nothing reads the caller's G any more: zero it for the scatter of the surviving edges
+                host_zero_fill(G, nn);
+                zeroed = true;
+            }
+        });
+        int rc = hetcor_engine(ctx, dC, n, dbits, nullptr, false, nullptr, cand, th, maxlevel, dT, l_out, sp);
+        hh->wait();  // the job refers to this frame: always joined before leaving it
+        if (rc) return rc;
+        if (held) {
+            int64_t down = 0;
+            int rc2 = CUSK_OK;
+            td2h.start();
+            hh->submit([&] {  // the bitmap's way back: D2H, then the helper's team writes the surviving edges
+                if (cudaSetDevice(ctx->device) != cudaSuccess) {
+                    rc2 = CUSK_E_CUDA;
+                    return;
+                }
+                rc2 = fetch_adjacency(ctx, dbits, n, rw, G, &down, zeroed);
+            });
+            hh->wait();
+            if (rc2) return rc2;
+            td2h.stop();
+            sp->h2d_ms = th2d.ms();
+            sp->d2h_ms = td2h.ms();
+            sp->h2d_bytes = up;
+            sp->d2h_bytes = down;
+            return CUSK_OK;
+        }
+        // the assumption did not hold: G and N are as the caller left them (nothing was zeroed); run the call again
+        // with what the scans found (C and the time index are already on the device)
+        th2d.start();
+        if (!uniform) {
+            dN = (float *)arena_take(ctx->io, nn * 4);
+            if (!dN) return CUSK_E_CUDA;
+            CUSK_CUDA(cudaMemcpyAsync(dN, N, nn * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)(nn * 4);
+        } else {
+            n_uniform = nu;
+        }
+        if (!all_ones) {
+            dG = (int *)arena_take(ctx->io, nn * 4);
+            if (!dG) return CUSK_E_CUDA;
+            CUSK_CUDA(cudaMemcpyAsync(dG, G, nn * 4, cudaMemcpyHostToDevice, st));
+            up += (int64_t)(nn * 4);
+        }
+        CUSK_CUDA(cudaEventRecord(ctx->ev_inputs, st));
+        th2d.stop();
+        ctx->idle_job = [&] {
+            if (cudaEventSynchronize(ctx->ev_inputs) != cudaSuccess) return;
+            host_zero_fill(G, nn);
+            zeroed = true;
+        };
+        rc = hetcor_engine(ctx, dC, n, dbits, dG, false, dN, n_uniform, th, maxlevel, dT, l_out, sp);
+        ctx->idle_job = nullptr;
+        if (rc) return rc;
+        int64_t down = 0;
+        td2h.start();
+        rc = fetch_adjacency(ctx, dbits, n, rw, G, &down, zeroed);
+        if (rc) return rc;
+        td2h.stop();
+        sp->h2d_ms = th2d.ms();
+        sp->d2h_ms = td2h.ms();
+        sp->h2d_bytes = up;
+        sp->d2h_bytes = down;
+        return CUSK_OK;
+    }
     if (!scan) {
         // Few host threads (several ranks share the host): everything goes over this GPU's own PCIe link, G first, and the
         // caller's G is zero-filled as soon as it has left while C and N are still travelling.

@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <functional>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -89,6 +90,9 @@ struct cusk_ctx {
     // matrix): the engine runs it once, just before one of its stream synchronisations, while the device is busy
     std::function<void()> idle_job;
     bool level_timing = false;  // record the per-level / per-kernel-group events behind cusk_stats.level_ms and ci_kernel_ms
+    // helper thread of the host-buffer entry points (api.cu): host scans and fills that run BESIDE the engine; created on
+    // first use, joined when the context goes
+    std::shared_ptr<void> host_helper;
 };
 
 inline void run_idle_job(cusk_ctx *ctx)
